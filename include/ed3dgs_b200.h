@@ -1,0 +1,139 @@
+/*
+ * ed3dgs_b200 -- C ABI of the B200-native E-D3DGS training hot path.
+ *
+ * Everything here is plain C: device pointers, sizes, a cudaStream_t passed as void*, int status
+ * codes. No torch types. Each entry point names the reference interface it replaces
+ * (paths relative to the reference checkout, vladb99/E-D3DGS).
+ *
+ * All data pointers are DEVICE pointers unless stated otherwise. "Absent" optional inputs are NULL
+ * (the reference passes empty tensors whose data pointer is null, rasterize_points.cu:94-98).
+ * Every call enqueues on `stream` (NULL = the legacy default stream, which is what the reference
+ * uses for everything).
+ */
+#ifndef ED3DGS_B200_H_
+#define ED3DGS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  ED3DGS_OK = 0,
+  ED3DGS_ERR_ARG = 1,   /* bad argument (reference: AT_ERROR / std::runtime_error) */
+  ED3DGS_ERR_CUDA = 2,  /* a CUDA call or kernel failed */
+  ED3DGS_ERR_ALLOC = 3  /* a resize callback returned NULL */
+};
+
+/* Last error message of the calling thread ("" when none). */
+const char* ed3dgs_last_error(void);
+/* "major.minor.patch (sm_100a)" */
+const char* ed3dgs_version(void);
+
+/*
+ * Resize callback for the three opaque state buffers (geometry, binning, image).
+ * Replaces std::function<char*(size_t)> of CudaRasterizer::Rasterizer::forward
+ * (cuda_rasterizer/rasterizer.h:31-34) which the reference binds to torch resize_()
+ * (rasterize_points.cu:27-33). Must return a device pointer to at least `bytes` bytes,
+ * 256-byte aligned, valid until the matching backward has run.
+ */
+typedef char* (*ed3dgs_alloc_fn)(void* user, size_t bytes);
+
+/*
+ * Forward rasterization. Replaces CudaRasterizer::Rasterizer::forward
+ * (cuda_rasterizer/rasterizer.h:30-65, rasterizer_impl.cu:255-432) as called from
+ * RasterizeGaussiansCUDA (rasterize_points.cu:35-137; pybind name `rasterize_gaussians`,
+ * ext.cpp:16). Same argument meaning and order; outputs need NOT be zero-filled by the caller
+ * except `radii` semantics are identical (0 for culled Gaussians).
+ *   means3D[P,3] shs[P,M,3] colors_precomp[P,3]|NULL opacities[P] tongue_class[P] scales[P,3]
+ *   rotations[P,4] cov3D_precomp[P,6]|NULL viewmatrix[16] projmatrix[16] cam_pos[3] background[3]
+ *   out_color[3,H,W] out_coord[3,H,W] out_mcoord[3,H,W] out_depth[H,W] out_mdepth[H,W]
+ *   out_alpha[H,W] out_tongue[H,W] out_normal[3,H,W] radii[P] (int32)
+ * out_coord/out_mcoord are written only when require_coord, out_depth/out_mdepth only when
+ * require_depth, out_normal when either (forward.cu:863-870); otherwise they are left untouched.
+ * *num_rendered receives the number of (Gaussian, tile) instances (host int), needed by backward.
+ */
+int ed3dgs_rasterize_forward(
+    ed3dgs_alloc_fn geom_alloc, void* geom_user, ed3dgs_alloc_fn binning_alloc, void* binning_user,
+    ed3dgs_alloc_fn image_alloc, void* image_user, int P, int D, int M, const float* background,
+    int width, int height, const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* tongue_class, const float* scales, float scale_modifier,
+    const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+    const float* projmatrix, const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size,
+    int prefiltered, float* out_color, float* out_coord, float* out_mcoord, float* out_depth,
+    float* out_mdepth, float* out_alpha, float* out_tongue, float* out_normal, int* radii,
+    int require_coord, int require_depth, int debug, void* stream, int* num_rendered);
+
+/*
+ * Backward rasterization. Replaces CudaRasterizer::Rasterizer::backward
+ * (cuda_rasterizer/rasterizer.h:67-115, rasterizer_impl.cu:436-578) as called from
+ * RasterizeGaussiansBackwardCUDA (rasterize_points.cu:139-250; pybind name
+ * `rasterize_gaussians_backward`). The eight returned gradients are the eight tensors that
+ * function returns; they are fully written here (no caller zero-fill needed):
+ *   dL_dmean2D[P,3] dL_dcolor[P,3] dL_dopacity[P] dL_dmean3D[P,3] dL_dcov3D[P,6] dL_dsh[P,M,3]
+ *   dL_dscale[P,3] dL_drot[P,4]
+ * The reference's eight intermediate gradient tensors (dL_dview_points, dL_dconic, dL_dts,
+ * dL_dcamera_planes, dL_dray_planes, dL_dnormals, ...; rasterize_points.cu:184-197) become one
+ * packed scratch buffer: grad_scratch, ed3dgs_rasterize_backward_scratch_bytes(P, require_coord)
+ * bytes, contents on entry irrelevant.
+ */
+size_t ed3dgs_rasterize_backward_scratch_bytes(int P, int require_coord);
+int ed3dgs_rasterize_backward(
+    int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+    const float* shs, const float* colors_precomp, const float* alphas, const float* scales,
+    float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+    const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, float kernel_size,
+    const int* radii, const float* normalmap, char* geom_buffer, char* binning_buffer,
+    char* image_buffer, const float* dL_dpix, const float* dL_dpix_coord, const float* dL_dpix_mcoord,
+    const float* dL_dpix_depth, const float* dL_dpix_mdepth, const float* dL_dalphas,
+    const float* dL_dpixel_normals, float* dL_dmean2D, float* dL_dcolor, float* dL_dopacity,
+    float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+    float* grad_scratch, int require_coord, int require_depth, int debug, void* stream);
+
+/*
+ * Copies the intermediate state of a finished forward out of its opaque buffers, in the
+ * reference's own layouts, for bit-exact comparison (tests; the reference has no equivalent
+ * because its buffers are raw SoA: rasterizer_impl.h:29-87). Any destination may be NULL.
+ *   depths[P] means2D[P,2] tiles_touched[P] point_offsets[P] conic_opacity[P,4] rgb[P,3]
+ *   keys_unsorted[R] vals_unsorted[R] keys_sorted[R] point_list[R] ranges[tiles,2]
+ *   n_contrib[2,H,W] normals[P,3] ray_planes[P,2] ts[P] camera_planes[P,6] view_points[P,3]
+ * Entries of culled Gaussians are unspecified (as in the reference).
+ */
+int ed3dgs_rasterize_get_state(
+    int P, int R, int width, int height, int require_coord, const char* geom_buffer,
+    const char* binning_buffer, const char* image_buffer, float* depths, float* means2D,
+    uint32_t* tiles_touched, uint32_t* point_offsets, float* conic_opacity, float* rgb,
+    uint64_t* keys_unsorted, uint32_t* vals_unsorted, uint64_t* keys_sorted, uint32_t* point_list,
+    uint32_t* ranges, uint32_t* n_contrib, float* normals, float* ray_planes, float* ts,
+    float* camera_planes, float* view_points, void* stream);
+
+/*
+ * Near-plane visibility mask. Replaces CudaRasterizer::Rasterizer::markVisible
+ * (cuda_rasterizer/rasterizer.h:24-29, rasterizer_impl.cu:54-66,176-188; pybind `mark_visible`).
+ * present[P] is one byte per Gaussian (torch.bool storage).
+ */
+int ed3dgs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                        const float* projmatrix, uint8_t* present, void* stream);
+
+/*
+ * Mean squared distance to the 3 nearest neighbours. Replaces SimpleKNN::knn / distCUDA2
+ * (submodules/simple-knn/simple_knn.cu:185-221, spatial.cu:16-25; pybind `distCUDA2`).
+ * workspace: ed3dgs_dist_cuda2_workspace_bytes(P) bytes of device scratch.
+ */
+size_t ed3dgs_dist_cuda2_workspace_bytes(int P);
+int ed3dgs_dist_cuda2(int P, const float* points, float* mean_dists, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/*
+ * Per-Gaussian deformation network (coarse + fine stage), fused. Replaces the torch module
+ * scene/deformation.py:15-148 (deform_network.forward :108-141, query_time :72-88, deform :90-106,
+ * create_net :38-51). See include/ed3dgs_deform.h.
+ */
+#include "ed3dgs_deform.h"
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ED3DGS_B200_H_ */

@@ -1,0 +1,185 @@
+"""Shared driver of the GPU parity tests: runs the product (through its C ABI) and the unmodified
+reference CUDA kernels (oracle/_ref) on the same seeded synthetic scene and compares
+  - bit-exact: radii, tiles_touched, point_offsets, unsorted keys/values, sorted keys, point_list,
+    tile ranges, depths, means2D
+  - <= 1e-5 abs: the eight rendered planes
+  - <= 1e-4 rel (of the tensor's max magnitude, atomic-order noise floor): all eight gradients
+"""
+import math
+
+import torch
+
+import ref_binding
+from ed3dgs_b200 import synthetic
+from ed3dgs_b200.rasterizer import rasterize_backward_raw, rasterize_forward_raw
+
+RENDER_ATOL = 1e-5
+GRAD_RTOL = 1e-4
+
+
+def make_case(P, W, H, sh_degree=3, splat_scale=0.3, focal=None, seed=synthetic.SEED, cam_k=3, n_cams=16,
+              kernel_size=0.0, require_coord=False, require_depth=True, device="cuda", bg=(0.1, 0.2, 0.3),
+              precomp_color=False, precomp_cov=False):
+    g = synthetic.make_gaussians(P, seed=seed, splat_scale=splat_scale, device=device)
+    if focal is None:
+        focal = 8200.0 * W / 3208.0
+    cam = synthetic.make_camera(cam_k, n_cams, W, H, focal, device=device)
+    act = synthetic.activate(g)
+    rs = synthetic.raster_settings(cam, sh_degree, kernel_size=kernel_size, require_coord=require_coord,
+                                   require_depth=require_depth, bg=torch.tensor(bg, device=device))
+    inputs = dict(means3D=act["means3D"].contiguous(), opacities=act["opacities"].contiguous(),
+                  tongue_class=act["tongue_class"].contiguous(), shs=act["shs"].contiguous(),
+                  colors_precomp=None, scales=act["scales"].contiguous(), rotations=act["rotations"].contiguous(),
+                  cov3D_precomp=None)
+    if precomp_color:
+        inputs["colors_precomp"] = torch.rand(P, 3, device=device, generator=torch.Generator(device).manual_seed(1))
+        inputs["shs"] = None
+    if precomp_cov:
+        S = torch.diag_embed(act["scales"])
+        q = act["rotations"]
+        r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                          2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                          2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).view(-1, 3, 3)
+        L = Rm @ S
+        cov = L @ L.transpose(1, 2)
+        inputs["cov3D_precomp"] = torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2],
+                                               cov[:, 2, 2]], -1).contiguous()
+        inputs["scales"] = None
+        inputs["rotations"] = None
+    return rs, inputs
+
+
+def upstream_grads(rs, out, seed=7):
+    """Seeded upstream gradients for every differentiable output plane."""
+    dev = out["color"].device
+    gen = torch.Generator(dev).manual_seed(seed)
+    H, W = int(rs.image_height), int(rs.image_width)
+    r = lambda c: (torch.rand(c, H, W, device=dev, generator=gen) - 0.5) / (H * W) * 1e3  # noqa: E731
+    g = dict(color=r(3), alpha=r(1) * 0.1)
+    g["coord"] = r(3) * 0.1 if rs.require_coord else torch.zeros(3, H, W, device=dev)
+    g["mcoord"] = r(3) * 0.1 if rs.require_coord else torch.zeros(3, H, W, device=dev)
+    g["depth"] = r(1) * 0.1 if rs.require_depth else torch.zeros(1, H, W, device=dev)
+    g["mdepth"] = r(1) * 0.1 if rs.require_depth else torch.zeros(1, H, W, device=dev)
+    g["normal"] = r(3) * 0.1 if (rs.require_depth or rs.require_coord) else torch.zeros(3, H, W, device=dev)
+    return g
+
+
+def run_product(rs, inp, grads_fn=None):
+    e = torch.empty(0)
+    nz = lambda t: e if t is None else t  # noqa: E731
+    res = rasterize_forward_raw(rs.bg, inp["means3D"], nz(inp["colors_precomp"]), inp["opacities"],
+                                inp["tongue_class"], nz(inp["scales"]), nz(inp["rotations"]), rs.scale_modifier,
+                                nz(inp["cov3D_precomp"]), rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                                rs.kernel_size, rs.image_height, rs.image_width, nz(inp["shs"]), rs.sh_degree,
+                                rs.campos, rs.prefiltered, rs.require_coord, rs.require_depth, rs.debug)
+    (R, color, coord, mcoord, alpha, tongue, normal, depth, mdepth, radii, geom, binning, img) = res
+    out = dict(color=color, coord=coord, mcoord=mcoord, depth=depth, mdepth=mdepth, alpha=alpha, tongue=tongue,
+               normal=normal, radii=radii)
+    state = ref_binding.product_state(rs, inp["means3D"].shape[0], R, geom, binning, img)
+    grads = None
+    if grads_fn is not None:
+        g = grads_fn(rs, out)
+        r = rasterize_backward_raw(rs.bg, inp["means3D"], radii, nz(inp["colors_precomp"]), nz(inp["scales"]),
+                                   nz(inp["rotations"]), rs.scale_modifier, nz(inp["cov3D_precomp"]), rs.viewmatrix,
+                                   rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.kernel_size, g["color"], g["coord"],
+                                   g["mcoord"], g["depth"], g["mdepth"], g["alpha"], g["normal"], normal,
+                                   nz(inp["shs"]), rs.sh_degree, rs.campos, geom, R, binning, img, alpha,
+                                   rs.require_coord, rs.require_depth, rs.debug)
+        names = ["dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+                 "dL_drotations"]
+        grads = dict(zip(names, r))
+    torch.cuda.synchronize()
+    return R, out, state, grads
+
+
+def run_reference(rs, inp, grads_fn=None):
+    ref = ref_binding.RefRasterizer()
+    R, out = ref.forward(rs, inp["means3D"], inp["opacities"], inp["tongue_class"], shs=inp["shs"],
+                         colors_precomp=inp["colors_precomp"], scales=inp["scales"], rotations=inp["rotations"],
+                         cov3D_precomp=inp["cov3D_precomp"])
+    state = ref.state()
+    grads = None
+    if grads_fn is not None:
+        grads = ref.backward(grads_fn(rs, out))
+    return R, out, state, grads
+
+
+EXACT_STATE = ["tiles_touched", "point_offsets", "keys_unsorted", "vals_unsorted", "keys_sorted", "point_list",
+               "ranges"]
+
+
+def compare(rs, a, b):
+    """a = product (R, out, state, grads), b = reference. Returns a report dict."""
+    Ra, oa, sa, ga = a
+    Rb, ob, sb, gb = b
+    rep = {"num_rendered": (Ra, Rb)}
+    vis = ob["radii"] > 0
+    rep["radii_mismatch"] = int((oa["radii"] != ob["radii"]).sum())
+    rep["visible"] = int(vis.sum())
+    for k in EXACT_STATE:
+        if sa[k].shape != sb[k].shape:
+            rep[k + "_mismatch"] = f"shape {tuple(sa[k].shape)} vs {tuple(sb[k].shape)}"
+        else:
+            rep[k + "_mismatch"] = int((sa[k] != sb[k]).sum())
+    # per-Gaussian float state is only defined for visible Gaussians
+    for k in ("depths", "means2D"):
+        x, y = sa[k][vis], sb[k][vis]
+        rep[k + "_bits_mismatch"] = int((x.view(torch.int32) != y.view(torch.int32)).sum())
+    for k in ("conic_opacity", "rgb", "normals", "ray_planes", "ts"):
+        x, y = sa[k][vis], sb[k][vis]
+        rep[k + "_maxabs"] = float((x - y).abs().max()) if x.numel() else 0.0
+        rep[k + "_bits_mismatch"] = int((x.view(torch.int32) != y.view(torch.int32)).sum())
+    if rs.require_coord:
+        for k in ("camera_planes", "view_points"):
+            x, y = sa[k][vis], sb[k][vis]
+            rep[k + "_maxabs"] = float((x - y).abs().max()) if x.numel() else 0.0
+    if rs.require_depth or rs.require_coord:
+        rep["n_contrib_mismatch"] = int((sa["n_contrib"] != sb["n_contrib"]).sum())
+    else:
+        rep["n_contrib_mismatch"] = int((sa["n_contrib"][0] != sb["n_contrib"][0]).sum())
+    for k in ("color", "coord", "mcoord", "depth", "mdepth", "alpha", "tongue", "normal"):
+        d = (oa[k] - ob[k]).abs()
+        rep["render_" + k + "_maxabs"] = float(d.max())
+        rep["render_" + k + "_nonfinite"] = int((~torch.isfinite(oa[k])).sum()) - int((~torch.isfinite(ob[k])).sum())
+    if ga is not None and gb is not None:
+        for k in ga:
+            x, y = ga[k], gb[k]
+            fin = torch.isfinite(y)
+            scale = float(y[fin].abs().max()) if fin.any() else 0.0
+            err = float((x[fin] - y[fin]).abs().max()) if fin.any() else 0.0
+            rep["grad_" + k + "_relerr"] = err / scale if scale > 0 else err
+            rep["grad_" + k + "_scale"] = scale
+            rep["grad_" + k + "_nonfinite_diff"] = int((torch.isfinite(x) != fin).sum())
+    return rep
+
+
+def assert_report(rep, rs):
+    assert rep["num_rendered"][0] == rep["num_rendered"][1], rep
+    assert rep["radii_mismatch"] == 0, rep
+    for k in EXACT_STATE:
+        assert rep[k + "_mismatch"] == 0, (k, rep)
+    assert rep["depths_bits_mismatch"] == 0 and rep["means2D_bits_mismatch"] == 0, rep
+    assert rep["n_contrib_mismatch"] == 0, rep
+    for k in ("color", "coord", "mcoord", "depth", "mdepth", "alpha", "tongue", "normal"):
+        assert rep["render_" + k + "_maxabs"] <= RENDER_ATOL, (k, rep)
+    for k, v in rep.items():
+        if k.startswith("grad_") and k.endswith("_relerr"):
+            assert v <= GRAD_RTOL, (k, rep)
+        if k.endswith("_nonfinite_diff"):
+            assert v == 0, (k, rep)
+
+
+def fmt(rep):
+    return "\n".join(f"  {k}: {v}" for k, v in rep.items())
+
+
+def tile_stats(state, R, P):
+    lens = (state["ranges"][:, 1] - state["ranges"][:, 0]).float()
+    return dict(R=R, R_over_P=R / max(P, 1), tile_len_mean=float(lens.mean()), tile_len_max=float(lens.max()),
+                tile_len_p50=float(lens.median()), nonempty_tiles=int((lens > 0).sum()),
+                log2_hist=[int(((lens >= 2 ** i) & (lens < 2 ** (i + 1))).sum()) for i in range(0, 16)])
+
+
+def _unused():
+    return math.pi
