@@ -9,6 +9,7 @@
 namespace ed3dgs {
 
 static thread_local char g_error[1024] = "";
+static thread_local int g_packed_is_input = 0;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -107,6 +108,11 @@ int ed3dgs_rasterize_forward(
   return raster_forward(a, static_cast<cudaStream_t>(stream));
 }
 
+// Test hook (not in the public header): the NEXT ed3dgs_rasterize_backward call of this thread
+// treats grad_scratch as input ([P][16|32] packed rows, raster_state.cuh) and runs only the
+// per-Gaussian stage. Lets the tests check that stage on the reference's own intermediates.
+void ed3dgs_test_packed_gradients_are_input(int on) { g_packed_is_input = on; }
+
 size_t ed3dgs_rasterize_backward_scratch_bytes(int P, int require_coord) {
   return (size_t)(P > 0 ? P : 0) * (require_coord ? 32 : 16) * sizeof(float) + 256;
 }
@@ -132,7 +138,8 @@ int ed3dgs_rasterize_backward(
                   kernel_size, radii, normalmap, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_dpix_coord,
                   dL_dpix_mcoord, dL_dpix_depth, dL_dpix_mdepth, dL_dalphas, dL_dpixel_normals, dL_dmean2D,
                   dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, grad_scratch,
-                  require_coord, require_depth, debug};
+                  require_coord, require_depth, debug, g_packed_is_input};
+  g_packed_is_input = 0;
   return raster_backward(a, static_cast<cudaStream_t>(stream));
 }
 
@@ -167,8 +174,8 @@ int ed3dgs_rasterize_get_state(
     char* bp = const_cast<char*>(binning_buffer);
     BinningState bin = carve_binning(bp, (size_t)R);
     const int sel = sorted_half((size_t)R, 32 + (int)id_bits(gx * gy));
-    cp(keys_unsorted, bin.keys[0], (size_t)R * 8);
-    cp(vals_unsorted, bin.vals[0], (size_t)R * 4);
+    cp(keys_unsorted, bin.keys[2], (size_t)R * 8);
+    cp(vals_unsorted, bin.vals[2], (size_t)R * 4);
     cp(keys_sorted, bin.keys[sel], (size_t)R * 8);
     cp(point_list, bin.vals[sel], (size_t)R * 4);
   }

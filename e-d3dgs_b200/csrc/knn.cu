@@ -220,7 +220,7 @@ int dist_cuda2(int P, const float* points, float* mean_dists, void* workspace, s
   KnnWork w = carve_knn(p, (size_t)P);
   cudaMemsetAsync(w.bounds, 0, 8 * sizeof(float), stream);
   knn_bounds<<<min((P + 255) / 256, 1184), 256, 0, stream>>>(P, points, w.bounds);
-  knn_morton<<<(P + 255) / 256, 256, 0, stream>>>(P, points, w.bounds, w.bin.keys[0], w.bin.vals[0]);
+  knn_morton<<<(P + 255) / 256, 256, 0, stream>>>(P, points, w.bounds, w.bin.keys[2], w.bin.vals[2]);
   const int sel = radix_sort_pairs(w.bin, (uint32_t)P, 30, stream);
   const int nboxes = (P + KNN_BOX - 1) / KNN_BOX;
   knn_gather_boxes<<<nboxes, KNN_BOX, 0, stream>>>(P, points, w.bin.vals[sel], w.sorted_pts, w.box_min, w.box_max);

@@ -85,6 +85,64 @@ __global__ void __launch_bounds__(1024) scan_exclusive_1cta(uint32_t* __restrict
   if (total_out && threadIdx.x == 0) *total_out = s_carry;
 }
 
+// Parallel in-place exclusive scan: 2048-element chunks scanned by 256-thread CTAs, the chunk
+// totals by one CTA, then the chunk prefix is added back. `sums` needs ceil(n/2048)+1 words.
+constexpr int XS_TILE = 2048;
+constexpr int XS_THREADS = 256;
+constexpr int XS_ITEMS = XS_TILE / XS_THREADS;
+
+__global__ void __launch_bounds__(XS_THREADS)
+scan_chunk_exclusive(uint32_t* __restrict__ data, uint32_t n, uint32_t* __restrict__ sums) {
+  __shared__ uint32_t s_warp[XS_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t i0 = blockIdx.x * XS_TILE + threadIdx.x * XS_ITEMS;
+  uint32_t v[XS_ITEMS];
+  uint32_t tsum = 0;
+#pragma unroll
+  for (int k = 0; k < XS_ITEMS; ++k) {
+    v[k] = (i0 + k < n) ? data[i0 + k] : 0u;
+    tsum += v[k];
+  }
+  uint32_t inc = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  uint32_t before = 0;
+#pragma unroll
+  for (int w = 0; w < XS_THREADS / 32; ++w)
+    if (w < warp) before += s_warp[w];
+  uint32_t run = before + inc - tsum;
+#pragma unroll
+  for (int k = 0; k < XS_ITEMS; ++k) {
+    if (i0 + k < n) data[i0 + k] = run;
+    run += v[k];
+  }
+  if (threadIdx.x == XS_THREADS - 1) sums[blockIdx.x] = run;
+}
+
+__global__ void __launch_bounds__(XS_THREADS)
+scan_chunk_add(uint32_t* __restrict__ data, uint32_t n, const uint32_t* __restrict__ prefix) {
+  const uint32_t add = prefix[blockIdx.x];
+  if (add == 0) return;
+  const uint32_t i0 = blockIdx.x * XS_TILE + threadIdx.x * XS_ITEMS;
+#pragma unroll
+  for (int k = 0; k < XS_ITEMS; ++k)
+    if (i0 + k < n) data[i0 + k] += add;
+}
+
+void exclusive_scan_inplace(uint32_t* data, uint32_t n, uint32_t* sums, cudaStream_t stream) {
+  const uint32_t nchunks = (n + XS_TILE - 1) / XS_TILE;
+  scan_chunk_exclusive<<<nchunks, XS_THREADS, 0, stream>>>(data, n, sums);
+  if (nchunks > 1) {
+    scan_exclusive_1cta<<<1, 1024, 0, stream>>>(sums, nchunks, nullptr);
+    scan_chunk_add<<<nchunks, XS_THREADS, 0, stream>>>(data, n, sums);
+  }
+}
+
 struct ScatterSmem {
   uint64_t keys[SORT_TILE];
   uint32_t vals[SORT_TILE];
@@ -196,15 +254,16 @@ int radix_sort_pairs(BinningState& b, uint32_t n, int end_bit, cudaStream_t stre
     attr_set = true;
   }
   const uint32_t nblocks = (uint32_t)sort_blocks(n);
-  int cur = 0;
+  int cur = 2, dst = 0;  // first pass reads the (preserved) emission buffers
   for (int shift = 0; shift < end_bit; shift += 8) {
     const int nbits = min(8, end_bit - shift);
     const uint32_t mask = (1u << nbits) - 1u;
     radix_hist<<<nblocks, SORT_THREADS, 0, stream>>>(b.keys[cur], n, shift, mask, nblocks, b.hist);
-    scan_exclusive_1cta<<<1, 1024, 0, stream>>>(b.hist, 256u * nblocks, nullptr);
+    exclusive_scan_inplace(b.hist, 256u * nblocks, b.hist + 256u * nblocks, stream);
     radix_scatter<<<nblocks, SORT_THREADS, sizeof(ScatterSmem), stream>>>(
-        b.keys[cur], b.vals[cur], b.keys[cur ^ 1], b.vals[cur ^ 1], n, shift, mask, nblocks, b.hist);
-    cur ^= 1;
+        b.keys[cur], b.vals[cur], b.keys[dst], b.vals[dst], n, shift, mask, nblocks, b.hist);
+    cur = dst;
+    dst ^= 1;
   }
   return cur;
 }

@@ -42,6 +42,7 @@ struct RasterBwdArgs {
   float *dL_dmean2D, *dL_dcolor, *dL_dopacity, *dL_dmean3D, *dL_dcov3D, *dL_dsh, *dL_dscale, *dL_drot;
   float* grad_scratch;  // [P][16 or 32] packed per-Gaussian gradients, any contents
   int require_coord, require_depth, debug;
+  int packed_is_input;  // test hook: grad_scratch already holds the packed per-Gaussian gradients
 };
 
 int raster_forward(const RasterFwdArgs& a, cudaStream_t stream);

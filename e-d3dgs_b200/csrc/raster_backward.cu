@@ -856,10 +856,12 @@ int raster_backward(const RasterBwdArgs& a, cudaStream_t stream) {
   const float focal_x = W / (2.0f * a.tan_fovx);
   const int V = coord ? 32 : 16;
 
-  cudaError_t err = cudaMemsetAsync(a.grad_scratch, 0, (size_t)P * V * sizeof(float), stream);
+  cudaError_t err = a.packed_is_input
+                        ? cudaSuccess
+                        : cudaMemsetAsync(a.grad_scratch, 0, (size_t)P * V * sizeof(float), stream);
   if (err != cudaSuccess) { set_error("memset of gradient scratch failed: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
 
-  if (a.R > 0) {
+  if (a.R > 0 && !a.packed_is_input) {
     const dim3 grid(gx, gy, 1);
     const uint32_t* plist = bin.vals[sel];
     if (coord && depth) launch_blend_bwd<true, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);

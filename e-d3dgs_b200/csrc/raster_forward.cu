@@ -594,7 +594,7 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
   int sel = 0;
   if (R > 0) {
     emit_keys<<<(P + 255) / 256, 256, 0, stream>>>(P, geom.rec, geom.depths, geom.point_offsets, a.radii,
-                                                  bin.keys[0], bin.vals[0], gx, gy);
+                                                  bin.keys[2], bin.vals[2], gx, gy);
     ED_DEBUG_SYNC("emit_keys");
     const int bit = (int)tile_id_bits(gx * gy);
     sel = radix_sort_pairs(bin, R, 32 + bit, stream);

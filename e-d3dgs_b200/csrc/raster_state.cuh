@@ -49,9 +49,9 @@ struct ImageState {
 };
 
 struct BinningState {
-  uint64_t* keys[2];       // ping-pong; keys[0] = unsorted emission order
-  uint32_t* vals[2];
-  uint32_t* hist;          // [256][nblocks] radix digit histograms / offsets
+  uint64_t* keys[3];       // [0],[1] = sort ping-pong; [2] = unsorted emission order (kept intact)
+  uint32_t* vals[3];
+  uint32_t* hist;          // [256][nblocks] radix digit histograms / offsets, then scan chunk sums
 };
 
 constexpr int SCAN_TILE = 2048;
@@ -106,11 +106,14 @@ inline BinningState carve_binning(char*& p, size_t R) {
   carve(p, b.keys[1], R);
   carve(p, b.vals[0], R);
   carve(p, b.vals[1], R);
-  carve(p, b.hist, 256 * sort_blocks(R) + 1);
+  carve(p, b.keys[2], R);
+  carve(p, b.vals[2], R);
+  carve(p, b.hist, 256 * sort_blocks(R) + (256 * sort_blocks(R) + 2047) / 2048 + 2);  // table + scan chunk sums
   return b;
 }
 // Which ping-pong half holds the sorted list after sorting key bits [0, end_bit).
-inline int sorted_half(size_t R, int end_bit) { return R == 0 ? 0 : (((end_bit + 7) / 8) & 1); }
+// (pass 0 reads the emission buffers [2] and writes [0]; later passes alternate [0] <-> [1].)
+inline int sorted_half(size_t R, int end_bit) { return (R == 0 || (((end_bit + 7) / 8) & 1)) ? 0 : 1; }
 
 inline size_t binning_bytes(size_t R) {
   char* p = nullptr;

@@ -18,6 +18,7 @@
 #include "cuda_rasterizer/rasterizer.h"
 #include "cuda_rasterizer/rasterizer_impl.h"
 #include "simple_knn.h"
+#include "cuda_rasterizer/backward.h"
 
 namespace {
 struct Buf {
@@ -154,6 +155,34 @@ int ref_get_state(void* c, float* depths, float* means2D, uint32_t* tiles_touche
     cp(keys_sorted, bin.point_list_keys, R * 8);
     cp(point_list, bin.point_list, R * 4);
   }
+  return cudaDeviceSynchronize() == cudaSuccess ? 0 : -1;
+}
+
+// Only the per-Gaussian half of the reference backward, i.e. the BACKWARD::preprocess call of
+// Rasterizer::backward (rasterizer_impl.cu:544-577) on caller-supplied intermediate gradients,
+// argument for argument -- including dL_dconic travelling in the conic_opacity slot (:576).
+// Lets the tests feed identical intermediates to the reference and the product.
+int ref_backward_preprocess(void* c, int P, int D, int M, int W, int H, const float* means3D,
+                            const float* shs, const float* scales, float scale_modifier,
+                            const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                            const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                            float kernel_size, const int* radii, float* dL_dmean2D, float* dL_dconic,
+                            float* dL_dview_points, float* dL_dopacity, float* dL_dcolor, float* dL_dts,
+                            float* dL_dcamera_planes, float* dL_dray_planes, float* dL_dnormals,
+                            float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                            float* dL_drot) {
+  Ctx* ctx = static_cast<Ctx*>(c);
+  char* gp = ctx->geom.ptr;
+  CudaRasterizer::GeometryState geomState = CudaRasterizer::GeometryState::fromChunk(gp, P);
+  const float focal_y = H / (2.0f * tan_fovy);
+  const float focal_x = W / (2.0f * tan_fovx);
+  const float* cov3D_ptr = (cov3D_precomp != nullptr) ? cov3D_precomp : geomState.cov3D;
+  BACKWARD::preprocess(P, D, M, (float3*)means3D, radii, shs, geomState.clamped, (glm::vec3*)scales,
+                       (glm::vec4*)rotations, scale_modifier, cov3D_ptr, viewmatrix, projmatrix, focal_x,
+                       focal_y, tan_fovx, tan_fovy, kernel_size, (glm::vec3*)campos, (float3*)dL_dmean2D,
+                       dL_dconic, (float3*)dL_dview_points, (glm::vec3*)dL_dmean3D, dL_dcolor, dL_dts,
+                       (float2*)dL_dcamera_planes, (float2*)dL_dray_planes, dL_dnormals, dL_dcov3D, dL_dsh,
+                       (glm::vec3*)dL_dscale, (glm::vec4*)dL_drot, (float4*)dL_dconic, dL_dopacity);
   return cudaDeviceSynchronize() == cudaSuccess ? 0 : -1;
 }
 

@@ -35,6 +35,12 @@ def main():
         a = pu.run_product(rs, inp, pu.upstream_grads)
         b = pu.run_reference(rs, inp, pu.upstream_grads)
         rep = pu.compare(rs, a, b)
+        b2 = pu.run_reference(rs, inp, pu.upstream_grads)
+        noise = pu.compare(rs, b2, b)
+        rep.update({"REFNOISE_" + k: v for k, v in noise.items() if k.startswith("grad_") and k.endswith("_relerr")})
+        import stage_util as su
+        for k, v in su.stage_report(rs, inp).items():
+            print(f"  STAGE {k}: max_rel={v['max_rel']:.3e} l2_rel={v['l2_rel']:.3e}")
         print(f"=== {name} {c} ({time.time() - t0:.1f}s)")
         print(pu.fmt(rep))
         print("  tiles:", json.dumps(pu.tile_stats(b[2], b[0], c["P"])))

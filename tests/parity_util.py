@@ -181,5 +181,12 @@ def tile_stats(state, R, P):
                 log2_hist=[int(((lens >= 2 ** i) & (lens < 2 ** (i + 1))).sum()) for i in range(0, 16)])
 
 
-def _unused():
-    return math.pi
+def worst_gaussian(ga, gb, gb2, inp, key):
+    """Index and context of the Gaussian with the largest product-vs-reference error in `key`."""
+    err = (ga[key] - gb[key]).abs().flatten(1).max(1).values
+    i = int(err.argmax())
+    out = dict(idx=i, err=float(err[i]), mine=ga[key][i].flatten().tolist(), ref=gb[key][i].flatten().tolist(),
+               ref2=gb2[key][i].flatten().tolist())
+    if inp.get("scales") is not None:
+        out["scales"] = inp["scales"][i].tolist()
+    return out

@@ -165,3 +165,33 @@ def product_state(rs, P, R, geom, binning, img):
     L.check(L.lib().ed3dgs_rasterize_get_state(P, R, W, H, int(rs.require_coord), _p(geom), _p(binning), _p(img),
                                                *[_p(st[k]) for k in order], L.stream_handle()))
     return st
+
+
+def ref_backward_preprocess(ref, inter):
+    """Per-Gaussian half of the reference backward on caller-supplied intermediates (dict of
+    reference-layout tensors; dL_dopacity is updated in place). Returns the final gradients."""
+    s = ref.saved
+    rs = s["rs"]
+    dev = s["means3D"].device
+    P, M = s["means3D"].shape[0], s["M"]
+    H, W = int(rs.image_height), int(rs.image_width)
+    z = lambda *sh: torch.zeros(*sh, dtype=torch.float32, device=dev)  # noqa: E731
+    res = dict(dL_dmeans3D=z(P, 3), dL_dcov3D=z(P, 6), dL_dsh=z(P, M, 3), dL_dscales=z(P, 3), dL_drotations=z(P, 4))
+    L = lib()
+    L.ref_backward_preprocess.restype = c_int
+    L.ref_backward_preprocess.argtypes = ([c_void_p] + [c_int] * 5 + [c_void_p] * 3 + [c_float] + [c_void_p] * 5
+                                          + [c_float] * 3 + [c_void_p] * 15)
+    torch.cuda.synchronize()
+    rc = L.ref_backward_preprocess(
+        ref.ctx, P, int(rs.sh_degree), M, W, H, _p(s["means3D"]), _p(s["shs"]), _p(s["scales"]),
+        float(rs.scale_modifier), _p(s["rotations"]), _p(s["cov3D_precomp"]), _p(rs.viewmatrix), _p(rs.projmatrix),
+        _p(rs.campos), float(rs.tanfovx), float(rs.tanfovy), float(rs.kernel_size), _p(s["out"]["radii"]),
+        _p(inter["dL_dmeans2D"]), _p(inter["dL_dconic"]), _p(inter["dL_dview_points"]), _p(inter["dL_dopacity"]),
+        _p(inter["dL_dcolors"]), _p(inter["dL_dts"]), _p(inter["dL_dcamera_planes"]), _p(inter["dL_dray_planes"]),
+        _p(inter["dL_dnormals"]), _p(res["dL_dmeans3D"]), _p(res["dL_dcov3D"]), _p(res["dL_dsh"]),
+        _p(res["dL_dscales"]), _p(res["dL_drotations"]))
+    assert rc == 0
+    res["dL_dopacity"] = inter["dL_dopacity"]
+    res["dL_dmeans2D"] = inter["dL_dmeans2D"]
+    res["dL_dcolors"] = inter["dL_dcolors"]
+    return res
