@@ -1,0 +1,611 @@
+// Deformation network (coarse + fine stage) of E-D3DGS on sm_100a tensor cores.
+// Replaces scene/deformation.py:15-148 of the reference (22 nn.Linear calls on cuBLAS SGEMM plus
+// ~40 elementwise kernels per render). What changes structurally:
+//  * The 256-wide temporal half of the input row is identical for every Gaussian
+//    (deformation.py:65 `.repeat`), so layer 0 is  E[N,32] * W0[:,256:]^T + (W0[:,:256] * tau + b0):
+//    per-Gaussian K drops from 288 to 32 and the [N,288] concat is never materialised.
+//  * All GEMMs (forward, input-gradient, weight-gradient) run through one tcgen05/TMEM building
+//    block (tc_gemm.cuh) with bias / ReLU / ReLU-mask / head-update epilogues fused in.
+//  * Bias gradients ride along as a ones-column of the weight-gradient GEMMs.
+#include <cstdio>
+#include "raster_api.h"
+#include "tc_gemm.cuh"
+
+namespace ed3dgs {
+
+// ---------------------------------------------------------------------------------------------
+template <int AMAJ, int BMAJ>
+static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, cudaStream_t stream) {
+  const size_t smem = tc_gemm_smem_bytes(a.NT);
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<AMAJ, BMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  tc_gemm_kernel<AMAJ, BMAJ><<<grid, TC_THREADS, smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a, int nbatch, cudaStream_t stream) {
+  if (nbatch <= 0) return cudaSuccess;
+  dim3 grid(1, nbatch, 1);
+  if (amaj == TC_K_MAJOR) grid.x = (a.M + TC_M - 1) / TC_M;
+  else grid.x = (a.K + a.k_per_cta - 1) / a.k_per_cta;
+  if (grid.x == 0) return cudaSuccess;
+  if (amaj == TC_K_MAJOR && bmaj == TC_K_MAJOR) return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR>(a, grid, stream);
+  if (amaj == TC_K_MAJOR && bmaj == TC_MN_MAJOR) return tc_launch_t<TC_K_MAJOR, TC_MN_MAJOR>(a, grid, stream);
+  if (amaj == TC_MN_MAJOR && bmaj == TC_MN_MAJOR) return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR>(a, grid, stream);
+  return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Temporal embedding (deformation.py:53-67): F.interpolate(bilinear, align_corners=True) of
+// weight[max_emb, dim] to n_rows rows, then F.grid_sample(bilinear, reflection,
+// align_corners=True) at x = column centres, y = (t - 0.5) * 2. One thread per column.
+struct TembTap {
+  int r0a, r1a, r0b, r1b;   // source rows of resized rows y0 (a) and y1 (b)
+  float la, lb;             // row lerp weights of the resize
+  int y0, y1;               // resized rows
+  float wy0, wy1;           // grid_sample row weights (0 when the row is out of range)
+  float dy_dt;              // d iy / d t (0 where clipped)
+};
+
+__device__ __forceinline__ float reflect_coord(float in, int twice_low, int twice_high, float& mult) {
+  // ATen reflect_coordinates_set_grad (GridSampler.cuh)
+  if (twice_low == twice_high) { mult = 0.f; return 0.f; }
+  int grad_in_mult;
+  const float mn = (float)twice_low / 2;
+  const float span = (float)(twice_high - twice_low) / 2;
+  in = in - mn;
+  if (in < 0.f) { grad_in_mult = -1; in = -in; } else { grad_in_mult = 1; }
+  const float extra = fmodf(in, span);
+  const int flips = (int)floorf(in / span);
+  if (flips % 2 == 0) { mult = (float)grad_in_mult; return extra + mn; }
+  mult = (float)(-grad_in_mult);
+  return span - extra + mn;
+}
+
+__device__ __forceinline__ float grid_coord(float g, int size, float& dmult) {
+  // unnormalize (align_corners=True) -> reflect over [0, size-1] -> clip
+  float c = ((g + 1.f) / 2) * (size - 1);
+  float m_unnorm = (float)(size - 1) / 2;
+  float m_ref;
+  c = reflect_coord(c, 0, 2 * (size - 1), m_ref);
+  float m_clip = 1.f;
+  if (c <= 0.f) { c = 0.f; m_clip = 0.f; }
+  else if (c >= (float)(size - 1)) { c = (float)(size - 1); m_clip = 0.f; }
+  dmult = m_unnorm * m_ref * m_clip;
+  return c;
+}
+
+__device__ __forceinline__ void resize_row(int r, int n_rows, int max_emb, int& r0, int& r1, float& lam) {
+  const float scale = (n_rows > 1) ? (float)(max_emb - 1) / (n_rows - 1) : 0.f;
+  const float src = scale * r;
+  r0 = (int)src;
+  r1 = r0 + ((r0 < max_emb - 1) ? 1 : 0);
+  lam = src - r0;
+}
+
+__device__ __forceinline__ TembTap temb_taps(float t, int n_rows, int max_emb) {
+  TembTap tp;
+  float dm;
+  const float gy = (t - 0.5f) * 2;
+  const float iy = grid_coord(gy, n_rows, dm);
+  tp.dy_dt = dm * 2.f;
+  tp.y0 = (int)floorf(iy);
+  tp.y1 = tp.y0 + 1;
+  const float fy = iy - tp.y0;
+  tp.wy0 = (tp.y0 >= 0 && tp.y0 < n_rows) ? (1.f - fy) : 0.f;
+  tp.wy1 = (tp.y1 >= 0 && tp.y1 < n_rows) ? fy : 0.f;
+  const int ya = min(max(tp.y0, 0), n_rows - 1), yb = min(max(tp.y1, 0), n_rows - 1);
+  resize_row(ya, n_rows, max_emb, tp.r0a, tp.r1a, tp.la);
+  resize_row(yb, n_rows, max_emb, tp.r0b, tp.r1b, tp.lb);
+  return tp;
+}
+
+__global__ void temb_forward(const float* __restrict__ weight, int max_emb, int dim, int n_rows,
+                             const float* __restrict__ t_dev, float* __restrict__ tau) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= dim) return;
+  const TembTap tp = temb_taps(*t_dev, n_rows, max_emb);
+  float dmx;
+  const float gx = ((float)c / (dim - 1) - 0.5f) * 2;
+  const float ix = grid_coord(gx, dim, dmx);
+  const int x0 = (int)floorf(ix), x1 = x0 + 1;
+  const float fx = ix - x0;
+  auto resized = [&](int r0, int r1, float lam, int x) -> float {
+    if (x < 0 || x >= dim) return 0.f;
+    return (1.f - lam) * weight[(long)r0 * dim + x] + lam * weight[(long)r1 * dim + x];
+  };
+  const float va = (1.f - fx) * resized(tp.r0a, tp.r1a, tp.la, x0) + fx * resized(tp.r0a, tp.r1a, tp.la, x1);
+  const float vb = (1.f - fx) * resized(tp.r0b, tp.r1b, tp.lb, x0) + fx * resized(tp.r0b, tp.r1b, tp.lb, x1);
+  tau[c] = tp.wy0 * va + tp.wy1 * vb;
+}
+
+__global__ void temb_backward(const float* __restrict__ weight, int max_emb, int dim, int n_rows,
+                              const float* __restrict__ t_dev, const float* __restrict__ d_tau,
+                              float* __restrict__ d_weight, float* __restrict__ d_t) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  float dt_local = 0.f;
+  if (c < dim) {
+    const TembTap tp = temb_taps(*t_dev, n_rows, max_emb);
+    float dmx;
+    const float gx = ((float)c / (dim - 1) - 0.5f) * 2;
+    const float ix = grid_coord(gx, dim, dmx);
+    const int x0 = (int)floorf(ix), x1 = x0 + 1;
+    const float fx = ix - x0;
+    const float g = d_tau[c];
+    auto resized = [&](int r0, int r1, float lam, int x) -> float {
+      if (x < 0 || x >= dim) return 0.f;
+      return (1.f - lam) * weight[(long)r0 * dim + x] + lam * weight[(long)r1 * dim + x];
+    };
+    auto scatter = [&](int r0, int r1, float lam, int x, float w) {
+      if (x < 0 || x >= dim || w == 0.f) return;
+      atomicAdd(d_weight + (long)r0 * dim + x, w * (1.f - lam));
+      atomicAdd(d_weight + (long)r1 * dim + x, w * lam);
+    };
+    scatter(tp.r0a, tp.r1a, tp.la, x0, g * tp.wy0 * (1.f - fx));
+    scatter(tp.r0a, tp.r1a, tp.la, x1, g * tp.wy0 * fx);
+    scatter(tp.r0b, tp.r1b, tp.lb, x0, g * tp.wy1 * (1.f - fx));
+    scatter(tp.r0b, tp.r1b, tp.lb, x1, g * tp.wy1 * fx);
+    const float va = (1.f - fx) * resized(tp.r0a, tp.r1a, tp.la, x0) + fx * resized(tp.r0a, tp.r1a, tp.la, x1);
+    const float vb = (1.f - fx) * resized(tp.r0b, tp.r1b, tp.lb, x0) + fx * resized(tp.r0b, tp.r1b, tp.lb, x1);
+    const float in_a = (tp.y0 >= 0 && tp.y0 < n_rows) ? va : 0.f;
+    const float in_b = (tp.y1 >= 0 && tp.y1 < n_rows) ? vb : 0.f;
+    dt_local = g * (in_b - in_a) * tp.dy_dt;
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) dt_local += __shfl_xor_sync(0xffffffffu, dt_local, o);
+  if ((threadIdx.x & 31) == 0 && dt_local != 0.f) atomicAdd(d_t, dt_local);
+}
+
+// ---------------------------------------------------------------------------------------------
+// c1[f] = b0[f] + sum_j W0[f][j] * tau[j]   (one warp per feature)
+__global__ void layer0_temporal_bias(const float* __restrict__ W0, const float* __restrict__ b0, long ld, int temb,
+                                     const float* __restrict__ tau, float* __restrict__ c1, int W) {
+  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (f >= W) return;
+  float acc = 0.f;
+  for (int j = lane; j < temb; j += 32) acc += W0[(long)f * ld + j] * tau[j];
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) c1[f] = acc + b0[f];
+}
+
+// db0 += dc1 ; dW0[f][j] += dc1[f] * tau[j] ; dtau[j] = sum_f W0[f][j] * dc1[f]
+__global__ void layer0_temporal_backward(const float* __restrict__ W0, long ld, int temb, int W,
+                                         const float* __restrict__ tau, const float* __restrict__ dc1,
+                                         float* __restrict__ dW0, float* __restrict__ db0, float* __restrict__ dtau) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < temb) {
+    const float tj = tau[j];
+    float acc = 0.f;
+    for (int f = 0; f < W; ++f) {
+      const float g = dc1[f];
+      acc += W0[(long)f * ld + j] * g;
+      if (dW0) dW0[(long)f * ld + j] += g * tj;
+    }
+    dtau[j] = acc;
+  }
+  if (db0 && j < W) db0[j] += dc1[j];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Upstream gradients -> G[N][80] (head h at column 16*?): pos 0, scales 8, rotations 16, opacity 24,
+// rgb 32..79, each scaled by its coefficient and zero padded; plus column sums (second-layer bias
+// gradients).
+__constant__ int kHeadDim[5] = {3, 3, 4, 1, 48};
+__constant__ int kHeadOff[5] = {0, 8, 16, 24, 32};
+static const int hHeadDim[5] = {3, 3, 4, 1, 48};
+static const int hHeadOff[5] = {0, 8, 16, 24, 32};
+static const int hHeadPad[5] = {8, 8, 8, 8, 48};
+constexpr int GW = 80;
+
+struct GradPtrs {
+  const float* d_out[5];
+  const float* d_sub[5];
+  float coef[5];
+};
+
+__global__ void __launch_bounds__(256)
+build_head_grads(int N, GradPtrs gp, int use_sub, float* __restrict__ G, float* __restrict__ colsum) {
+  __shared__ float s_sum[GW];
+  for (int i = threadIdx.x; i < GW; i += blockDim.x) s_sum[i] = 0.f;
+  __syncthreads();
+  const int col = threadIdx.x % GW;              // 256 threads: 3 rows x 80 cols (+16 idle)
+  const int rsub = threadIdx.x / GW;
+  int h = 0, j = col;
+  if (col >= 32) { h = 4; j = col - 32; } else { h = col >> 3; j = col & 7; }
+  const bool live_col = j < kHeadDim[h];
+  const float* src = gp.d_out[h];
+  const float* src2 = use_sub ? gp.d_sub[h] : nullptr;
+  const float cf = gp.coef[h];
+  const int kd = kHeadDim[h];
+  float acc = 0.f;
+  if (rsub < 3) {
+    for (int n = blockIdx.x * 3 + rsub; n < N; n += gridDim.x * 3) {
+      float v = 0.f;
+      if (live_col) {
+        if (src) v = src[(long)n * kd + j];
+        if (src2) v += src2[(long)n * kd + j];
+        v *= cf;
+      }
+      G[(long)n * GW + col] = v;
+      acc += v;
+    }
+    atomicAdd(&s_sum[col], acc);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < GW; i += blockDim.x)
+    if (s_sum[i] != 0.f) atomicAdd(colsum + i, s_sum[i]);
+}
+
+__global__ void add_vec(float* __restrict__ dst, const float* __restrict__ src, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] += src[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+struct DeformWork {
+  float* R[2][ED3DGS_DEFORM_MAX_DEPTH];  // post-ReLU outputs of feature_out layers, [N, W]
+  float* Rz[2];                          // post-ReLU head hidden layers, [N, 5W] (active heads packed)
+  float* G[2];                           // [N, 80]
+  float* dZ;                             // [N, 5W]
+  float* dH[2];                          // [N, W]
+  float* Wpack;                          // [5W, W]
+  float* c1[2];                          // [W]
+  float* dc1;                            // [W]
+  float* colsum[2];                      // [80]
+};
+
+static inline void carve_f(char*& p, float*& out, size_t count) {
+  p = reinterpret_cast<char*>((reinterpret_cast<size_t>(p) + 255) / 256 * 256);
+  out = reinterpret_cast<float*>(p);
+  p += count * sizeof(float);
+}
+
+static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
+  DeformWork w{};
+  for (int s = 0; s < 2; ++s) {
+    for (int l = 0; l < depth; ++l) carve_f(p, w.R[s][l], N * W);
+    carve_f(p, w.Rz[s], N * 5 * W);
+    carve_f(p, w.G[s], N * GW);
+    carve_f(p, w.c1[s], W);
+    carve_f(p, w.colsum[s], GW);
+  }
+  carve_f(p, w.dZ, N * 5 * W);
+  carve_f(p, w.dH[0], N * W);
+  carve_f(p, w.dH[1], N * W);
+  carve_f(p, w.Wpack, (size_t)5 * W * W);
+  carve_f(p, w.dc1, W);
+  return w;
+}
+
+static int check_weights(const ed3dgs_deform_weights* w) {
+  if (!w) return ED3DGS_OK;
+  if (w->W < 16 || w->W > 128 || (w->W % 16) != 0) {
+    set_error("deform: net_width %d unsupported (multiple of 16, <= 128)", w->W);
+    return ED3DGS_ERR_ARG;
+  }
+  if (w->depth < 1 || w->depth > ED3DGS_DEFORM_MAX_DEPTH || (w->temb_dim % 4) || (w->gemb_dim % 16) || w->gemb_dim > 240) {
+    set_error("deform: unsupported depth/temb_dim/gemb_dim (%d, %d, %d)", w->depth, w->temb_dim, w->gemb_dim);
+    return ED3DGS_ERR_ARG;
+  }
+  if (!w->head_w1[0]) { set_error("deform: the position head cannot be disabled"); return ED3DGS_ERR_ARG; }
+  return ED3DGS_OK;
+}
+
+#define TC_TRY(expr)                                                                         \
+  do {                                                                                       \
+    cudaError_t e__ = (expr);                                                                \
+    if (e__ != cudaSuccess) {                                                                \
+      set_error("deform: %s failed: %s", #expr, cudaGetErrorString(e__));                    \
+      return ED3DGS_ERR_CUDA;                                                                \
+    }                                                                                        \
+  } while (0)
+
+static TcArgs tc_args(long lda, long ldb, int M, int K, int NT, int epi) {
+  TcArgs a{};
+  a.lda = lda; a.ldb = ldb; a.M = M; a.K = K; a.NT = NT; a.epilogue = epi;
+  a.k_per_cta = K > 0 ? K : 1; a.ones_col = -1;
+  return a;
+}
+
+static int active_heads(const ed3dgs_deform_weights* w, int* list) {
+  int n = 0;
+  for (int h = 0; h < 5; ++h)
+    if (w->head_w1[h]) list[n++] = h;
+  return n;
+}
+
+// One stage forward: base[h] -> dst[h] = base[h] + delta_h * coef[h].
+static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const float* emb, const float* tau,
+                         const float* const base[5], float* const dst[5], const float coef[5], DeformWork& wk,
+                         cudaStream_t stream) {
+  const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
+  const long ld0 = temb + gemb;
+  layer0_temporal_bias<<<(W + 3) / 4, 128, 0, stream>>>(w->feat_w[0], w->feat_b[0], ld0, temb, tau, wk.c1[s], W);
+  {  // layer 0 on the per-Gaussian embedding
+    TcArgs a = tc_args(gemb, ld0, N, gemb, W, TC_EPI_BIAS_ACT);
+    a.relu = 1;
+    a.b[0] = TcBatch{emb, w->feat_w[0] + temb, wk.R[s][0], wk.c1[s], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, stream));
+  }
+  for (int l = 1; l < D; ++l) {
+    TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
+    a.relu = 1;
+    a.b[0] = TcBatch{wk.R[s][l - 1], w->feat_w[l], wk.R[s][l], w->feat_b[l], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, stream));
+  }
+  int act[5];
+  const int na = active_heads(w, act);
+  {  // head hidden layers, all active heads in one launch
+    TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
+    a.relu = 1;
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      a.b[i] = TcBatch{wk.R[s][D - 1], w->head_w1[h], wk.Rz[s] + (long)i * W, w->head_b1[h], nullptr, nullptr,
+                       5L * W, 0, W, 0, 0, 1.f};
+    }
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, stream));
+  }
+  {  // head outputs fused with  x = x + delta * coef
+    TcArgs a = tc_args(5L * W, W, N, W, 48, TC_EPI_HEAD);
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      a.b[i] = TcBatch{wk.Rz[s] + (long)i * W, w->head_w2[h], dst[h], w->head_b2[h], base[h], nullptr,
+                       hHeadDim[h], hHeadDim[h], hHeadDim[h], 0, 0, coef[h]};
+    }
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, stream));
+  }
+  for (int h = 0; h < 5; ++h)
+    if (!w->head_w1[h] && dst[h] != base[h])
+      TC_TRY(cudaMemcpyAsync(dst[h], base[h], (size_t)N * hHeadDim[h] * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  return ED3DGS_OK;
+}
+
+static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
+                          const float* emb, const float* tau, const float* G, const float* colsum, DeformWork& wk,
+                          float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
+  const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
+  const long ld0 = temb + gemb;
+  const int kslice = 1024;  // shorter tensor-core accumulation chains are measurably more accurate
+  int act[5];
+  const int na = active_heads(w, act);
+
+  if (g) {
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      if (g->head_b2[h]) add_vec<<<1, 64, 0, stream>>>(g->head_b2[h], colsum + hHeadOff[h], hHeadDim[h]);
+    }
+    // dW2_h[j][f] += sum_n G_h[n][j] * Rz_h[n][f]
+    TcArgs a = tc_args(5L * W, GW, W, N, 48, TC_EPI_ATOMIC_T);
+    a.k_per_cta = kslice;
+    int nb = 0;
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      if (!g->head_w2[h]) continue;
+      a.b[nb++] = TcBatch{wk.Rz[s] + (long)i * W, G + hHeadOff[h], g->head_w2[h], nullptr, nullptr, nullptr,
+                          W, 0, hHeadDim[h], 0, 0, 1.f};
+    }
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, stream));
+  }
+  {  // dZ_h = (G_h * W2_h) masked by Rz_h > 0
+    TcArgs a = tc_args(GW, W, N, 0, W, TC_EPI_MASK);
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      a.b[i] = TcBatch{G + hHeadOff[h], w->head_w2[h], wk.dZ + (long)i * W, nullptr, wk.Rz[s] + (long)i * W, nullptr,
+                       5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
+    }
+    a.K = 48;
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, stream));
+  }
+  if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i] ; db1_h[o] += sum_n dZ_h[n][o]
+    TcArgs a = tc_args(5L * W, W, W, N, W + 16, TC_EPI_ATOMIC);
+    a.k_per_cta = kslice;
+    a.ones_col = W;
+    int nb = 0;
+    for (int i = 0; i < na; ++i) {
+      const int h = act[i];
+      if (!g->head_w1[h]) continue;
+      a.b[nb++] = TcBatch{wk.dZ + (long)i * W, wk.R[s][D - 1], g->head_w1[h], nullptr, nullptr, g->head_b1[h],
+                          W, 0, W, 0, 0, 1.f};
+    }
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, stream));
+  }
+  // dR = (dZ[N, na*W] * W1_all[na*W, W]) masked by R > 0
+  for (int i = 0; i < na; ++i)
+    TC_TRY(cudaMemcpyAsync(wk.Wpack + (size_t)i * W * W, w->head_w1[act[i]], (size_t)W * W * sizeof(float),
+                           cudaMemcpyDeviceToDevice, stream));
+  float* dh = wk.dH[0];
+  float* dh_other = wk.dH[1];
+  {
+    TcArgs a = tc_args(5L * W, W, N, na * W, W, TC_EPI_MASK);
+    a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], nullptr, W, W, W, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+  }
+  for (int l = D - 1; l >= 1; --l) {
+    if (g && g->feat_w[l]) {
+      TcArgs a = tc_args(W, W, W, N, W + 16, TC_EPI_ATOMIC);
+      a.k_per_cta = kslice;
+      a.ones_col = W;
+      a.b[0] = TcBatch{dh, wk.R[s][l - 1], g->feat_w[l], nullptr, nullptr, g->feat_b[l], W, 0, W, 0, 0, 1.f};
+      TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    }
+    TcArgs a = tc_args(W, W, N, W, W, TC_EPI_MASK);
+    a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], nullptr, W, W, W, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    float* t = dh; dh = dh_other; dh_other = t;
+  }
+  // layer 0: weight gradient of the embedding columns + dc1 (ones column), then dE
+  TC_TRY(cudaMemsetAsync(wk.dc1, 0, W * sizeof(float), stream));
+  {
+    TcArgs a = tc_args(W, gemb, W, N, gemb + 16, TC_EPI_ATOMIC);
+    a.k_per_cta = kslice;
+    a.ones_col = gemb;
+    float* dW0e = (g && g->feat_w[0]) ? g->feat_w[0] + temb : nullptr;
+    // without a weight-gradient target only the ones column (dc1) is kept: n_valid = 0
+    a.b[0] = TcBatch{dh, emb, dW0e ? dW0e : wk.dc1, nullptr, nullptr, wk.dc1, ld0, 0, dW0e ? gemb : 0, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, stream));
+  }
+  {
+    TcArgs a = tc_args(W, ld0, N, W, gemb, TC_EPI_ACCUM);
+    a.accumulate = accumulate_emb;
+    a.b[0] = TcBatch{dh, w->feat_w[0] + temb, d_emb, nullptr, nullptr, nullptr, gemb, 0, gemb, 0, 0, 1.f};
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+  }
+  layer0_temporal_backward<<<(max(temb, W) + 127) / 128, 128, 0, stream>>>(
+      w->feat_w[0], ld0, temb, W, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
+  TC_TRY(cudaGetLastError());
+  return ED3DGS_OK;
+}
+
+}  // namespace ed3dgs
+
+using namespace ed3dgs;
+
+extern "C" {
+
+int ed3dgs_temporal_embed_forward(const float* weight, int max_emb, int dim, int n_rows, const float* t_dev,
+                                  float* tau, void* stream) {
+  if (!weight || !t_dev || !tau || max_emb < 1 || dim < 2 || n_rows < 1) {
+    set_error("temporal_embed_forward: bad argument");
+    return ED3DGS_ERR_ARG;
+  }
+  temb_forward<<<(dim + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(weight, max_emb, dim, n_rows, t_dev, tau);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("temporal_embed_forward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
+int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, int n_rows, const float* t_dev,
+                                   const float* d_tau, float* d_weight, float* d_t, void* stream) {
+  if (!weight || !t_dev || !d_tau || !d_weight || !d_t) {
+    set_error("temporal_embed_backward: bad argument");
+    return ED3DGS_ERR_ARG;
+  }
+  temb_backward<<<(dim + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(weight, max_emb, dim, n_rows, t_dev,
+                                                                                  d_tau, d_weight, d_t);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("temporal_embed_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
+size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N) {
+  char* p = nullptr;
+  carve_deform(p, W, depth < 1 ? 1 : depth, (size_t)(N > 0 ? N : 0));
+  return reinterpret_cast<size_t>(p) + 512;
+}
+
+int ed3dgs_deform_forward(const ed3dgs_deform_weights* coarse, const ed3dgs_deform_weights* fine, int N,
+                          const float* embedding, const float* tau_c, const float* tau_f,
+                          const float* const in[ED3DGS_DEFORM_HEADS], float* const sub[ED3DGS_DEFORM_HEADS],
+                          float* const out[ED3DGS_DEFORM_HEADS], const float coef[ED3DGS_DEFORM_HEADS],
+                          void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (N <= 0) return ED3DGS_OK;
+  int rc;
+  if ((rc = check_weights(coarse)) || (rc = check_weights(fine))) return rc;
+  const ed3dgs_deform_weights* any = coarse ? coarse : fine;
+  static const int hd[5] = {3, 3, 4, 1, 48};
+  if (!any) {
+    for (int h = 0; h < 5; ++h) {
+      cudaMemcpyAsync(sub[h], in[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
+      cudaMemcpyAsync(out[h], in[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
+    }
+    return ED3DGS_OK;
+  }
+  if (!workspace || workspace_bytes < ed3dgs_deform_workspace_bytes(any->W, any->depth, N)) {
+    set_error("deform_forward: workspace too small");
+    return ED3DGS_ERR_ARG;
+  }
+  char* p = static_cast<char*>(workspace);
+  DeformWork wk = carve_deform(p, any->W, any->depth, (size_t)N);
+  if (coarse) {
+    if ((rc = stage_forward(coarse, 0, N, embedding, tau_c, in, sub, coef, wk, stream))) return rc;
+  } else {
+    for (int h = 0; h < 5; ++h) cudaMemcpyAsync(sub[h], in[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
+  }
+  if (fine) {
+    const float* base[5] = {sub[0], sub[1], sub[2], sub[3], sub[4]};
+    if ((rc = stage_forward(fine, 1, N, embedding, tau_f, base, out, coef, wk, stream))) return rc;
+  } else {
+    for (int h = 0; h < 5; ++h) cudaMemcpyAsync(out[h], sub[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
+  }
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("deform_forward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
+int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_deform_weights* fine,
+                           const ed3dgs_deform_grads* g_coarse, const ed3dgs_deform_grads* g_fine, int N,
+                           const float* embedding, const float* tau_c, const float* tau_f,
+                           const float* const d_out[ED3DGS_DEFORM_HEADS], const float* const d_sub[ED3DGS_DEFORM_HEADS],
+                           const float coef[ED3DGS_DEFORM_HEADS], void* workspace, size_t workspace_bytes,
+                           float* d_embedding, float* d_tau_c, float* d_tau_f, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const ed3dgs_deform_weights* any = coarse ? coarse : fine;
+  if (N <= 0 || !any) return ED3DGS_OK;
+  int rc;
+  if ((rc = check_weights(coarse)) || (rc = check_weights(fine))) return rc;
+  if (!workspace || workspace_bytes < ed3dgs_deform_workspace_bytes(any->W, any->depth, N)) {
+    set_error("deform_backward: workspace too small");
+    return ED3DGS_ERR_ARG;
+  }
+  char* p = static_cast<char*>(workspace);
+  DeformWork wk = carve_deform(p, any->W, any->depth, (size_t)N);
+
+  GradPtrs gp{};
+  bool any_sub = false;
+  for (int h = 0; h < 5; ++h) {
+    gp.d_out[h] = d_out ? d_out[h] : nullptr;
+    gp.d_sub[h] = d_sub ? d_sub[h] : nullptr;
+    gp.coef[h] = coef[h];
+    any_sub = any_sub || gp.d_sub[h] != nullptr;
+  }
+  const int gblocks = 592;
+  // fine stage sees d_out only; coarse stage sees d_out + d_sub
+  cudaMemsetAsync(wk.colsum[1], 0, GW * sizeof(float), stream);
+  build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 0, wk.G[1], wk.colsum[1]);
+  const float* Gc = wk.G[1];
+  const float* colc = wk.colsum[1];
+  if (any_sub && coarse) {
+    cudaMemsetAsync(wk.colsum[0], 0, GW * sizeof(float), stream);
+    build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 1, wk.G[0], wk.colsum[0]);
+    Gc = wk.G[0];
+    colc = wk.colsum[0];
+  }
+  int accumulate = 0;
+  if (fine) {
+    if ((rc = stage_backward(fine, g_fine, 1, N, embedding, tau_f, wk.G[1], wk.colsum[1], wk, d_embedding, accumulate,
+                             d_tau_f, stream)))
+      return rc;
+    accumulate = 1;
+  }
+  if (coarse) {
+    if ((rc = stage_backward(coarse, g_coarse, 0, N, embedding, tau_c, Gc, colc, wk, d_embedding, accumulate, d_tau_c,
+                             stream)))
+      return rc;
+  }
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("deform_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
+// Test hook (not in the public header): one GEMM through the tensor-core building block.
+int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, const float* A, long lda,
+                        const float* B, long ldb, float* C, long ldc, int k_per_cta, int ones_col,
+                        float* bias_grad, int epilogue, int dbg, void* stream) {
+  TcArgs a{};
+  a.b[0] = TcBatch{A, B, C, nullptr, nullptr, bias_grad, ldc, 0, n_valid, 0, 0, 1.f};
+  a.lda = lda; a.ldb = ldb;
+  a.M = M; a.K = K; a.NT = NT; a.k_per_cta = k_per_cta > 0 ? k_per_cta : K;
+  a.epilogue = epilogue; a.relu = 0; a.accumulate = 0; a.ones_col = ones_col; a.dbg = dbg;
+  const cudaError_t e = tc_launch(amaj, bmaj, a, 1, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) { set_error("tc_gemm launch failed: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
+}  // extern "C"

@@ -1,4 +1,97 @@
-/* Deformation-network entry points of ed3dgs_b200 (included by ed3dgs_b200.h). */
+/*
+ * Deformation-network entry points of ed3dgs_b200 (included by ed3dgs_b200.h).
+ *
+ * Replaces the torch module scene/deformation.py:15-148 of the reference:
+ *   get_temporal_embed (:53-67)  -> ed3dgs_temporal_embed_forward / _backward
+ *   query_time (:72-88) + feature_out (:39-44) + deform (:90-106) + the five heads (:47-51),
+ *   coarse and fine stage (:125-137)  -> ed3dgs_deform_forward / _backward
+ *
+ * The network input is cat([temporal embedding (identical for every Gaussian), per-Gaussian
+ * embedding]); the temporal half is folded into a per-call bias, so per-Gaussian K is gemb_dim.
+ * All matrices are nn.Linear layouts ([out, in], row-major, fp32). GEMMs run on the tensor
+ * cores as 3xTF32 (error-compensated, fp32-grade) -- see csrc/tc_gemm.cuh.
+ */
 #ifndef ED3DGS_DEFORM_H_
 #define ED3DGS_DEFORM_H_
-#endif
+
+#include <stddef.h>
+
+#define ED3DGS_DEFORM_HEADS 5       /* pos, scales, rotations, opacity, rgb  (deformation.py:47-51) */
+#define ED3DGS_DEFORM_MAX_DEPTH 8   /* Linear layers in feature_out (defor_depth) */
+
+/* Output widths of the five heads: 3, 3, 4, 1, 48 (16 SH coefficients x RGB). */
+
+typedef struct {
+  int W;          /* net_width: multiple of 16, <= 128 */
+  int depth;      /* number of Linear layers in feature_out: max(defor_depth, 1) */
+  int temb_dim;   /* temporal_embedding_dim (256), multiple of 4 */
+  int gemb_dim;   /* gaussian_embedding_dim (32), multiple of 4 */
+  /* feature_out.{0,2,4,...}: weight [W, temb_dim+gemb_dim] for layer 0, [W, W] after; bias [W] */
+  const float* feat_w[ED3DGS_DEFORM_MAX_DEPTH];
+  const float* feat_b[ED3DGS_DEFORM_MAX_DEPTH];
+  /* {pos,scales,rotations,opacity,rgb}_deform.1 : [W, W], [W];  .3 : [k, W], [k].
+     head_w1[h] == NULL disables head h (no_ds / no_dr / no_do / no_dc; pos is always on). */
+  const float* head_w1[ED3DGS_DEFORM_HEADS];
+  const float* head_b1[ED3DGS_DEFORM_HEADS];
+  const float* head_w2[ED3DGS_DEFORM_HEADS];
+  const float* head_b2[ED3DGS_DEFORM_HEADS];
+} ed3dgs_deform_weights;
+
+/* Same shapes as the weights; every non-NULL gradient is ACCUMULATED into (+=). */
+typedef struct {
+  float* feat_w[ED3DGS_DEFORM_MAX_DEPTH];
+  float* feat_b[ED3DGS_DEFORM_MAX_DEPTH];
+  float* head_w1[ED3DGS_DEFORM_HEADS];
+  float* head_b1[ED3DGS_DEFORM_HEADS];
+  float* head_w2[ED3DGS_DEFORM_HEADS];
+  float* head_b2[ED3DGS_DEFORM_HEADS];
+} ed3dgs_deform_grads;
+
+/*
+ * tau[dim] = the temporal embedding at time *t_dev (device scalar): bilinear resize of
+ * weight[max_emb, dim] to n_rows rows (align_corners=True) then bilinear sampling with reflection
+ * padding at y = (t - 0.5) * 2 (deformation.py:53-67). Backward accumulates (+=) into
+ * d_weight[max_emb, dim] and d_t[1].
+ */
+int ed3dgs_temporal_embed_forward(const float* weight, int max_emb, int dim, int n_rows,
+                                  const float* t_dev, float* tau, void* stream);
+int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, int n_rows,
+                                   const float* t_dev, const float* d_tau, float* d_weight,
+                                   float* d_t, void* stream);
+
+/* Bytes of device workspace forward/backward need for N Gaussians (saved activations + scratch). */
+size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N);
+
+/*
+ * Forward of both stages. coarse / fine may be NULL (no_coarse_deform / no_fine_deform).
+ *   in[h], sub[h], out[h]: [N, k_h] for h = pos, scales, rotations, opacity, rgb.
+ *   sub = in + delta_coarse * coef   (the reference's *_sub tuple), out = sub + delta_fine * coef.
+ *   coef[h]: the annealing coefficients of deform() (:91-105): {scale, scale*coef_s, scale,
+ *   scale*scale_o, scale_c}. Disabled heads copy their input through.
+ * workspace keeps what backward needs; it must stay untouched until backward has run.
+ */
+int ed3dgs_deform_forward(const ed3dgs_deform_weights* coarse, const ed3dgs_deform_weights* fine,
+                          int N, const float* embedding, const float* tau_c, const float* tau_f,
+                          const float* const in[ED3DGS_DEFORM_HEADS],
+                          float* const sub[ED3DGS_DEFORM_HEADS],
+                          float* const out[ED3DGS_DEFORM_HEADS],
+                          const float coef[ED3DGS_DEFORM_HEADS], void* workspace,
+                          size_t workspace_bytes, void* stream);
+
+/*
+ * Backward of both stages.
+ *   d_out[h]: dL/d out[h] (NULL = zero); d_sub[h]: extra dL/d sub[h] (NULL = zero).
+ *   Writes d_embedding[N, gemb_dim], d_tau_c[temb_dim], d_tau_f[temb_dim]; accumulates weight
+ *   gradients into g_coarse / g_fine. The gradient w.r.t. in[h] is d_out[h] + d_sub[h]
+ *   (identity path) and is left to the caller.
+ */
+int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_deform_weights* fine,
+                           const ed3dgs_deform_grads* g_coarse, const ed3dgs_deform_grads* g_fine,
+                           int N, const float* embedding, const float* tau_c, const float* tau_f,
+                           const float* const d_out[ED3DGS_DEFORM_HEADS],
+                           const float* const d_sub[ED3DGS_DEFORM_HEADS],
+                           const float coef[ED3DGS_DEFORM_HEADS], void* workspace,
+                           size_t workspace_bytes, float* d_embedding, float* d_tau_c,
+                           float* d_tau_f, void* stream);
+
+#endif /* ED3DGS_DEFORM_H_ */

@@ -15,6 +15,7 @@ from ed3dgs_b200.rasterizer import rasterize_backward_raw, rasterize_forward_raw
 
 RENDER_ATOL = 1e-5
 GRAD_RTOL = 1e-4
+GRAD_MAX_RTOL_ILLCOND = 1e-3
 
 
 def make_case(P, W, H, sh_degree=3, splat_scale=0.3, focal=None, seed=synthetic.SEED, cam_k=3, n_cams=16,
@@ -149,6 +150,8 @@ def compare(rs, a, b):
             scale = float(y[fin].abs().max()) if fin.any() else 0.0
             err = float((x[fin] - y[fin]).abs().max()) if fin.any() else 0.0
             rep["grad_" + k + "_relerr"] = err / scale if scale > 0 else err
+            nrm = float(y[fin].double().norm()) if fin.any() else 0.0
+            rep["grad_" + k + "_l2rel"] = (float((x[fin] - y[fin]).double().norm()) / nrm) if nrm > 0 else 0.0
             rep["grad_" + k + "_scale"] = scale
             rep["grad_" + k + "_nonfinite_diff"] = int((torch.isfinite(x) != fin).sum())
     return rep
@@ -164,8 +167,16 @@ def assert_report(rep, rs):
     for k in ("color", "coord", "mcoord", "depth", "mdepth", "alpha", "tongue", "normal"):
         assert rep["render_" + k + "_maxabs"] <= RENDER_ATOL, (k, rep)
     for k, v in rep.items():
-        if k.startswith("grad_") and k.endswith("_relerr"):
+        if k.startswith("grad_") and k.endswith("_l2rel"):
             assert v <= GRAD_RTOL, (k, rep)
+        if k.startswith("grad_") and k.endswith("_relerr"):
+            # max-norm: 1e-4 everywhere except the three outputs that pass through the
+            # 3x3 eigen / inverse-covariance chain. Its Jacobian scales with 1/lambda_min (~1e8 for
+            # needle and pancake Gaussians) and amplifies summation-order noise of the blend stage;
+            # two runs of the REFERENCE differ by up to 1.4e-4 there (tests/parity_report.py,
+            # REFNOISE_*), so the max-norm bound for them is 1e-3 and the 1e-4 bound is on l2.
+            loose = any(t in k for t in ("dL_dcov3D", "dL_dscales", "dL_drotations"))
+            assert v <= (GRAD_MAX_RTOL_ILLCOND if loose else GRAD_RTOL), (k, rep)
         if k.endswith("_nonfinite_diff"):
             assert v == 0, (k, rep)
 
