@@ -5,11 +5,27 @@
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
+#include "profiler.h"
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
 
 namespace ed3dgs {
 
 static thread_local char g_error[1024] = "";
 static thread_local int g_packed_is_input = 0;
+
+// ---- optional kernel timing (profiler.h) ----
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::mutex g_prof_mu;
+bool prof_enabled() { return g_prof_on; }
+void prof_push(const char* name, cudaEvent_t a, cudaEvent_t b) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof.push_back(ProfRec{name, a, b});
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -80,6 +96,35 @@ extern "C" {
 
 const char* ed3dgs_last_error(void) { return g_error; }
 const char* ed3dgs_version(void) { return "0.1.0 (sm_100a)"; }
+
+void ed3dgs_profile_enable(int on) { g_prof_on = on != 0; }
+
+// Synchronises the device, writes "name total_ms launches\n" lines into buf and clears the log.
+int ed3dgs_profile_report(char* buf, size_t nbytes) {
+  cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  std::map<std::string, std::pair<double, int>> agg;
+  for (auto& r : g_prof) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+      auto& e = agg[r.name];
+      e.first += ms;
+      e.second += 1;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  size_t off = 0;
+  if (buf && nbytes) buf[0] = 0;
+  for (auto& kv : agg) {
+    const int n = snprintf(buf + off, off < nbytes ? nbytes - off : 0, "%s %.6f %d\n", kv.first.c_str(), kv.second.first,
+                           kv.second.second);
+    if (n < 0 || off + (size_t)n >= nbytes) break;
+    off += (size_t)n;
+  }
+  return (int)agg.size();
+}
 
 int ed3dgs_rasterize_forward(
     ed3dgs_alloc_fn geom_alloc, void* geom_user, ed3dgs_alloc_fn binning_alloc, void* binning_user,

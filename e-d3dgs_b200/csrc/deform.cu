@@ -10,6 +10,7 @@
 #include <cstdio>
 #include "raster_api.h"
 #include "tc_gemm.cuh"
+#include "profiler.h"
 
 namespace ed3dgs {
 
@@ -23,6 +24,7 @@ static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, cudaStream_t stream) 
     if (e != cudaSuccess) return e;
     configured = smem;
   }
+  ProfScope ps(AMAJ == TC_MN_MAJOR ? "tc_gemm_kernel<wgrad>" : (BMAJ == TC_MN_MAJOR ? "tc_gemm_kernel<dgrad>" : "tc_gemm_kernel<fwd>"), stream);
   tc_gemm_kernel<AMAJ, BMAJ><<<grid, TC_THREADS, smem, stream>>>(a);
   return cudaGetLastError();
 }
@@ -568,7 +570,8 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
   const int gblocks = 592;
   // fine stage sees d_out only; coarse stage sees d_out + d_sub
   cudaMemsetAsync(wk.colsum[1], 0, GW * sizeof(float), stream);
-  build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 0, wk.G[1], wk.colsum[1]);
+  { ProfScope ps("build_head_grads", stream);
+  build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 0, wk.G[1], wk.colsum[1]); }
   const float* Gc = wk.G[1];
   const float* colc = wk.colsum[1];
   if (any_sub && coarse) {

@@ -11,6 +11,7 @@
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
+#include "profiler.h"
 
 namespace ed3dgs {
 
@@ -862,6 +863,7 @@ int raster_backward(const RasterBwdArgs& a, cudaStream_t stream) {
   if (err != cudaSuccess) { set_error("memset of gradient scratch failed: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
 
   if (a.R > 0 && !a.packed_is_input) {
+    ProfScope ps("blend_bwd", stream);
     const dim3 grid(gx, gy, 1);
     const uint32_t* plist = bin.vals[sel];
     if (coord && depth) launch_blend_bwd<true, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);
@@ -880,7 +882,10 @@ int raster_backward(const RasterBwdArgs& a, cudaStream_t stream) {
       a.cov3D_precomp, a.viewmatrix, a.projmatrix, focal_x, focal_y, a.tan_fovx, a.tan_fovy, a.kernel_size,  \
       a.campos, a.grad_scratch, a.dL_dmean2D, a.dL_dcolor, a.dL_dopacity, a.dL_dmean3D, a.dL_dcov3D,         \
       a.dL_dsh, a.dL_dscale, a.dL_drot)
+  {
+  ProfScope ps("gaussian_bwd", stream);
   if (coord) ED_GBWD(true); else ED_GBWD(false);
+  }
 #undef ED_GBWD
   err = a.debug ? cudaStreamSynchronize(stream) : cudaSuccess;
   if (err == cudaSuccess) err = cudaGetLastError();

@@ -7,6 +7,7 @@
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
+#include "profiler.h"
 
 namespace ed3dgs {
 
@@ -569,16 +570,22 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
   GeomState geom = carve_geom(gp, P, coord);
   ImageState img = carve_image(ip, npix, ntiles, coord);
 
+  {
+  ProfScope ps("preprocess_fwd", stream);
   preprocess_fwd<<<(P + 255) / 256, 256, 0, stream>>>(
       P, a.D, a.M, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.tongue_class, a.shs,
       a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.cam_pos, W, H, a.tan_fovx, a.tan_fovy,
       focal_x, focal_y, a.kernel_size, a.radii, geom, gx, gy, coord ? 1 : 0);
+  }
   ED_DEBUG_SYNC("preprocess");
 
   const uint32_t nsb = (P + SCAN_TILE - 1) / SCAN_TILE;
+  {
+  ProfScope ps("scan_tiles", stream);
   scan_tiles_local<<<nsb, SCAN_THREADS, 0, stream>>>(geom.tiles_touched, geom.point_offsets, P, geom.block_sums);
   scan_exclusive_1cta<<<1, 1024, 0, stream>>>(geom.block_sums, nsb, geom.block_sums + nsb);
   scan_tiles_add<<<nsb, SCAN_THREADS, 0, stream>>>(geom.point_offsets, P, geom.block_sums);
+  }
   ED_DEBUG_SYNC("scan");
 
   // The host needs R to size the binning buffers (as rasterizer_impl.cu:359).
@@ -593,15 +600,21 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
 
   int sel = 0;
   if (R > 0) {
+    {
+    ProfScope ps("emit_keys", stream);
     emit_keys<<<(P + 255) / 256, 256, 0, stream>>>(P, geom.rec, geom.depths, geom.point_offsets, a.radii,
                                                   bin.keys[2], bin.vals[2], gx, gy);
+    }
     ED_DEBUG_SYNC("emit_keys");
     const int bit = (int)tile_id_bits(gx * gy);
+    {
+    ProfScope ps("radix_sort_pairs", stream);
     sel = radix_sort_pairs(bin, R, 32 + bit, stream);
+    }
     ED_DEBUG_SYNC("radix_sort");
   }
   ED_CHECK(cudaMemsetAsync(img.ranges, 0, ntiles * sizeof(uint2), stream));
-  if (R > 0) tile_ranges<<<(R + 255) / 256, 256, 0, stream>>>(R, bin.keys[sel], img.ranges);
+  if (R > 0) { ProfScope ps("tile_ranges", stream); tile_ranges<<<(R + 255) / 256, 256, 0, stream>>>(R, bin.keys[sel], img.ranges); }
   ED_DEBUG_SYNC("tile_ranges");
 
   const dim3 grid(gx, gy, 1);
@@ -610,10 +623,13 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
   launch_render_fwd<C_, D_>(grid, stream, img, plist, W, H, geom, focal_x, focal_y, a.background,        \
                             a.out_color, a.out_coord, a.out_mcoord, a.out_depth, a.out_mdepth, a.out_alpha, \
                             a.out_tongue, a.out_normal)
+  {
+  ProfScope ps("render_fwd", stream);
   if (coord && depth) ED_RENDER(true, true);
   else if (coord) ED_RENDER(true, false);
   else if (depth) ED_RENDER(false, true);
   else ED_RENDER(false, false);
+  }
 #undef ED_RENDER
   ED_DEBUG_SYNC("render");
   ED_CHECK(cudaGetLastError());

@@ -1,0 +1,57 @@
+"""CPU, world size 2 over gloo: the data-parallel plumbing of ed3dgs_b200/dp.py (view sharding,
+gradient arena whose slices are the parameters' .grad, one all-reduce per step, densification
+reductions)."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from ed3dgs_b200 import dp
+    r, _l, w = dp.init_from_env("gloo")
+    assert (r, w) == (rank, world)
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(4, 3)
+    emb = torch.nn.Parameter(torch.ones(5, 2))
+    arena = dp.GradArena(list(lin.parameters()) + [emb])
+    assert lin.weight.grad.data_ptr() == arena.flat.data_ptr()
+    views = dp.shard_views(5, rank, world)
+    arena.zero()
+    loss = sum((lin(torch.full((1, 4), float(v + 1))).sum() + (emb * (v + 1)).sum()) for v in views)
+    loss.backward()
+    flat = arena.allreduce(1.0 / 5)
+    # every rank now holds the mean gradient over all 5 views
+    expect_emb = sum(v + 1 for v in range(5)) / 5.0
+    ok = torch.allclose(emb.grad, torch.full((5, 2), expect_emb)) and emb.grad.data_ptr() != 0
+    expect_w = torch.full((3, 4), sum(v + 1 for v in range(5)) / 5.0)
+    ok = ok and torch.allclose(lin.weight.grad, expect_w) and flat.numel() == 12 + 3 + 10
+    radii, vis, g2d = dp.reduce_densification_stats(torch.tensor([rank, 3 - rank]), torch.tensor([rank == 0, False]),
+                                                    torch.ones(2, 3) * (rank + 1))
+    ok = ok and radii.tolist() == [1, 3] and vis.tolist() == [True, False] and float(g2d.sum()) == 18.0
+    out[rank] = bool(ok) and views == ([0, 1, 2] if rank == 0 else [3, 4])
+    dist.destroy_process_group()
+
+
+def test_grad_arena_allreduce_world2():
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    assert dict(out) == {0: True, 1: True}
+
+
+def test_shard_views_ragged():
+    from ed3dgs_b200 import dp
+    assert [dp.shard_views(8, r, 8) for r in range(8)] == [[i] for i in range(8)]
+    assert dp.shard_views(3, 3, 4) == [] and dp.shard_views(3, 2, 4) == [2]
