@@ -11,36 +11,11 @@
 #include "raster_api.h"
 #include "tc_gemm.cuh"
 #include "profiler.h"
+#include "tc_launch.cuh"
 
 namespace ed3dgs {
 
 // ---------------------------------------------------------------------------------------------
-template <int AMAJ, int BMAJ>
-static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, cudaStream_t stream) {
-  const size_t smem = tc_gemm_smem_bytes(a.NT);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<AMAJ, BMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
-  ProfScope ps(AMAJ == TC_MN_MAJOR ? "tc_gemm_kernel<wgrad>" : (BMAJ == TC_MN_MAJOR ? "tc_gemm_kernel<dgrad>" : "tc_gemm_kernel<fwd>"), stream);
-  tc_gemm_kernel<AMAJ, BMAJ><<<grid, TC_THREADS, smem, stream>>>(a);
-  return cudaGetLastError();
-}
-
-cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a, int nbatch, cudaStream_t stream) {
-  if (nbatch <= 0) return cudaSuccess;
-  dim3 grid(1, nbatch, 1);
-  if (amaj == TC_K_MAJOR) grid.x = (a.M + TC_M - 1) / TC_M;
-  else grid.x = (a.K + a.k_per_cta - 1) / a.k_per_cta;
-  if (grid.x == 0) return cudaSuccess;
-  if (amaj == TC_K_MAJOR && bmaj == TC_K_MAJOR) return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR>(a, grid, stream);
-  if (amaj == TC_K_MAJOR && bmaj == TC_MN_MAJOR) return tc_launch_t<TC_K_MAJOR, TC_MN_MAJOR>(a, grid, stream);
-  if (amaj == TC_MN_MAJOR && bmaj == TC_MN_MAJOR) return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR>(a, grid, stream);
-  return cudaErrorInvalidValue;
-}
-
 // ---------------------------------------------------------------------------------------------
 // Temporal embedding (deformation.py:53-67): F.interpolate(bilinear, align_corners=True) of
 // weight[max_emb, dim] to n_rows rows, then F.grid_sample(bilinear, reflection,
@@ -257,6 +232,7 @@ struct DeformWork {
   float* dZ;                             // [N, 5W]
   float* dH[2];                          // [N, W]
   float* Wpack;                          // [5W, W]
+  float* Wprep;                          // per-launch hi/lo UMMA images of the weight operand
   float* c1[2];                          // [W]
   float* dc1;                            // [W]
   float* colsum[2];                      // [80]
@@ -281,6 +257,7 @@ static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
   carve_f(p, w.dH[0], N * W);
   carve_f(p, w.dH[1], N * W);
   carve_f(p, w.Wpack, (size_t)5 * W * W);
+  carve_f(p, w.Wprep, tc_prep_scratch_floats());
   carve_f(p, w.dc1, W);
   return w;
 }
@@ -333,13 +310,13 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
     TcArgs a = tc_args(gemb, ld0, N, gemb, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
     a.b[0] = TcBatch{emb, w->feat_w[0] + temb, wk.R[s][0], wk.c1[s], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
   }
   for (int l = 1; l < D; ++l) {
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
     a.b[0] = TcBatch{wk.R[s][l - 1], w->feat_w[l], wk.R[s][l], w->feat_b[l], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
   }
   int act[5];
   const int na = active_heads(w, act);
@@ -351,7 +328,7 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
       a.b[i] = TcBatch{wk.R[s][D - 1], w->head_w1[h], wk.Rz[s] + (long)i * W, w->head_b1[h], nullptr, nullptr,
                        5L * W, 0, W, 0, 0, 1.f};
     }
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
   }
   {  // head outputs fused with  x = x + delta * coef
     TcArgs a = tc_args(5L * W, W, N, W, 48, TC_EPI_HEAD);
@@ -360,7 +337,7 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
       a.b[i] = TcBatch{wk.Rz[s] + (long)i * W, w->head_w2[h], dst[h], w->head_b2[h], base[h], nullptr,
                        hHeadDim[h], hHeadDim[h], hHeadDim[h], 0, 0, coef[h]};
     }
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
   }
   for (int h = 0; h < 5; ++h)
     if (!w->head_w1[h] && dst[h] != base[h])
@@ -392,7 +369,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       a.b[nb++] = TcBatch{wk.Rz[s] + (long)i * W, G + hHeadOff[h], g->head_w2[h], nullptr, nullptr, nullptr,
                           W, 0, hHeadDim[h], 0, 0, 1.f};
     }
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, stream));
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, nullptr, stream));
   }
   {  // dZ_h = (G_h * W2_h) masked by Rz_h > 0
     TcArgs a = tc_args(GW, W, N, 0, W, TC_EPI_MASK);
@@ -402,7 +379,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
                        5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
     }
     a.K = 48;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, wk.Wprep, stream));
   }
   if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i] ; db1_h[o] += sum_n dZ_h[n][o]
     TcArgs a = tc_args(5L * W, W, W, N, W + 16, TC_EPI_ATOMIC);
@@ -415,7 +392,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       a.b[nb++] = TcBatch{wk.dZ + (long)i * W, wk.R[s][D - 1], g->head_w1[h], nullptr, nullptr, g->head_b1[h],
                           W, 0, W, 0, 0, 1.f};
     }
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, stream));
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, nullptr, stream));
   }
   // dR = (dZ[N, na*W] * W1_all[na*W, W]) masked by R > 0
   for (int i = 0; i < na; ++i)
@@ -426,7 +403,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   {
     TcArgs a = tc_args(5L * W, W, N, na * W, W, TC_EPI_MASK);
     a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], nullptr, W, W, W, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
   }
   for (int l = D - 1; l >= 1; --l) {
     if (g && g->feat_w[l]) {
@@ -434,11 +411,11 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       a.k_per_cta = kslice;
       a.ones_col = W;
       a.b[0] = TcBatch{dh, wk.R[s][l - 1], g->feat_w[l], nullptr, nullptr, g->feat_b[l], W, 0, W, 0, 0, 1.f};
-      TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, stream));
+      TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, nullptr, stream));
     }
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_MASK);
     a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], nullptr, W, W, W, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
     float* t = dh; dh = dh_other; dh_other = t;
   }
   // layer 0: weight gradient of the embedding columns + dc1 (ones column), then dE
@@ -450,13 +427,13 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     float* dW0e = (g && g->feat_w[0]) ? g->feat_w[0] + temb : nullptr;
     // without a weight-gradient target only the ones column (dc1) is kept: n_valid = 0
     a.b[0] = TcBatch{dh, emb, dW0e ? dW0e : wk.dc1, nullptr, nullptr, wk.dc1, ld0, 0, dW0e ? gemb : 0, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, nullptr, stream));
   }
   {
     TcArgs a = tc_args(W, ld0, N, W, gemb, TC_EPI_ACCUM);
     a.accumulate = accumulate_emb;
     a.b[0] = TcBatch{dh, w->feat_w[0] + temb, d_emb, nullptr, nullptr, nullptr, gemb, 0, gemb, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, stream));
+    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
   }
   layer0_temporal_backward<<<(max(temb, W) + 127) / 128, 128, 0, stream>>>(
       w->feat_w[0], ld0, temb, W, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
@@ -606,7 +583,12 @@ int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, c
   a.lda = lda; a.ldb = ldb;
   a.M = M; a.K = K; a.NT = NT; a.k_per_cta = k_per_cta > 0 ? k_per_cta : K;
   a.epilogue = epilogue; a.relu = 0; a.accumulate = 0; a.ones_col = ones_col; a.dbg = dbg;
-  const cudaError_t e = tc_launch(amaj, bmaj, a, 1, static_cast<cudaStream_t>(stream));
+  static float* scratch = nullptr;
+  if (!scratch && cudaMalloc(&scratch, tc_prep_scratch_floats() * sizeof(float)) != cudaSuccess) {
+    set_error("tc_gemm test scratch allocation failed");
+    return ED3DGS_ERR_CUDA;
+  }
+  const cudaError_t e = tc_launch(amaj, bmaj, a, 1, scratch, static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) { set_error("tc_gemm launch failed: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
   return ED3DGS_OK;
 }

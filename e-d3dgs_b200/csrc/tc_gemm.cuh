@@ -4,12 +4,16 @@
 //
 // Every product is evaluated as  A_lo*B_hi + A_hi*B_lo + A_hi*B_hi  with hi = rna_tf32(x) and
 // lo = rna_tf32(x - hi), so the result carries ~22 mantissa bits per factor: fp32-grade, which
-// is what the reference computes (nn.Linear on cuBLAS SGEMM, TF32 off). Operands are staged by
-// the CTA's threads into the canonical no-swizzle K-major UMMA shared-memory layout, one elected
-// thread issues tcgen05.mma.kind::tf32, tcgen05.commit signals an mbarrier per stage, and the 128
-// threads read their own accumulator row back with tcgen05.ld for the fused epilogue.
-// Operands whose contraction index is the slow one in global memory (weight gradients, W^T) are
-// transposed while staging, so no transposed copy is ever written to HBM.
+// is what the reference computes (nn.Linear on cuBLAS SGEMM, TF32 off).
+//
+// Pipeline of one CTA (256 threads, 2 CTAs per SM):
+//   global --cp.async 16 B, 2-3 chunks ahead--> raw fp32 ring in shared memory
+//   raw ring --all threads: split hi/lo (+ transpose when the contraction index is the slow one
+//             in global memory)--> two UMMA operand stages (canonical no-swizzle K-major layout)
+//   one elected thread: 6 x tcgen05.mma.kind::tf32 per 16-wide K chunk, tcgen05.commit -> mbarrier
+//   epilogue: 8 warps read the accumulator from TMEM (tcgen05.ld 32x32b.x16), fused
+//             bias/ReLU | ReLU-mask | x += delta*coef | atomic weight-gradient (+ ones column = bias)
+// No transposed or split copy of any operand is ever written to HBM.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -33,8 +37,8 @@ enum TcEpilogue : int {
 
 constexpr int TC_MAX_BATCH = 5;
 constexpr int TC_M = 128;        // rows per CTA = TMEM lanes
-constexpr int TC_KC = 16;        // K elements staged per pipeline stage (two UMMA k-steps)
-constexpr int TC_THREADS = 128;
+constexpr int TC_KC = 16;        // K elements per pipeline chunk (two UMMA k-steps)
+constexpr int TC_THREADS = 256;
 
 struct TcBatch {
   const float* A;
@@ -48,6 +52,7 @@ struct TcBatch {
   int K;                 // contraction length of this batch entry (0: TcArgs::K)
   int kb_valid;          // MN-major B: rows of B along k that exist (0: same as K)
   float scale;           // HEAD
+  const float4* Bprep;   // set by tc_launch: per-chunk UMMA images of B (weights), see tc_prepare_b
 };
 
 struct TcArgs {
@@ -56,7 +61,8 @@ struct TcArgs {
   int M;          // K-major A: number of valid rows (Gaussians). MN-major A: valid rows of D (features)
   int K;          // contraction length (MN-major A: number of Gaussians)
   int NT;         // tile width, multiple of 16, <= 256
-  int k_per_cta;  // MN-major A only: contraction slice per CTA (split over blockIdx.x)
+  int k_per_cta;  // MN-major A only: contraction slice per CTA
+  int nbatch;     // batch entries; blockIdx.x = tile * nbatch + batch (entries of a tile run adjacently -> L2 reuse of A)
   int epilogue;
   int relu;       // BIAS_ACT
   int accumulate; // ACCUM
@@ -132,6 +138,15 @@ __device__ __forceinline__ float tf32_rna(float x) {
   return __uint_as_float(r);
 }
 
+// 16-byte async copy global -> shared; src_bytes = 0 zero-fills the destination (predication).
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gmem_src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // Shared-memory matrix descriptor, no swizzle (cute/arch/mma_sm100_desc.hpp: SmemDescriptor).
 //  bits [0,14) start address >> 4, [16,30) leading byte offset >> 4, [32,46) stride byte offset >> 4,
 //  [46,48) version = 1 on sm_100, [61,64) layout type = 0 (SWIZZLE_NONE / interleave)
@@ -144,8 +159,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 
-// Instruction descriptor for kind::tf32, fp32 accumulate, both operands K-major
-// (InstrDescriptor in the same header).
+// Instruction descriptor for kind::tf32, fp32 accumulate, both operands K-major.
 __device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N) {
   uint32_t d = 0;
   d |= 1u << 4;                       // D format F32
@@ -156,9 +170,6 @@ __device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N) {
   return d;
 }
 
-// ---- operand staging ---------------------------------------------------------------------------
-// K-major tile [ROWS x 16k] in shared memory: float index = ((k/4) * ROWS + row) * 4 + k%4
-//   -> core matrix (8 rows x 16 B) contiguous, LBO (next K chunk) = ROWS*16 B, SBO (next 8 rows) = 128 B.
 __device__ __forceinline__ void split_store(float4 x, float4* hi, float4* lo) {
   float4 h, l;
   h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
@@ -167,237 +178,108 @@ __device__ __forceinline__ void split_store(float4 x, float4* hi, float4* lo) {
   *lo = l;
 }
 
-// Source K-major: element (row, k) = src[row * ld + k]. rows = tile rows (128 for A, NT for B).
-__device__ __forceinline__ void stage_k_major(const float* __restrict__ src, long ld, int rows, int rows_valid,
-                                              int k0, int K, float4* hi, float4* lo) {
-  const int total = rows * (TC_KC / 4);
+// ---- stage 1: global -> raw ring (cp.async) ----------------------------------------------------
+// K-major source, tile [rows x 16k]: raw float index = row*16 + ((c4 ^ ((row>>1)&3)) << 2)
+//   (16-byte pieces XOR-swizzled inside the 64-byte row so the conversion pass reads conflict-free)
+// MN-major source, tile [16k x rows]: raw float index = kl*rows + row  (straight lines)
+// ROWS_T > 0 makes the tile height a compile-time constant (no integer divisions, loops unrolled).
+template <int MAJ, int ROWS_T>
+__device__ __forceinline__ void raw_issue(float* raw, const float* __restrict__ src, long ld, int rows_rt,
+                                          int rows_valid, int k0, int kend) {
+  const int rows = ROWS_T ? ROWS_T : rows_rt;
+  if (MAJ == TC_K_MAJOR) {
+    const int total = rows * 4;
+#pragma unroll
+    for (int q = threadIdx.x; q < total; q += TC_THREADS) {
+      const int row = q >> 2, c4 = q & 3;
+      const int k = k0 + c4 * 4;
+      const bool ok = row < rows_valid && k < kend;
+      const float* s = ok ? (src + (long)row * ld + k) : src;
+      cp_async16_zfill(raw + row * 16 + ((c4 ^ ((row >> 1) & 3)) << 2), s, ok ? 16 : 0);
+    }
+  } else {
+    const int groups = rows >> 2;
+    const int total = TC_KC * groups;
+#pragma unroll
+    for (int q = threadIdx.x; q < total; q += TC_THREADS) {
+      const int kl = q / groups, g = q - kl * groups;
+      const int k = k0 + kl;
+      const bool ok = k < kend && g * 4 < rows_valid;
+      const float* s = ok ? (src + (long)k * ld + g * 4) : src;
+      cp_async16_zfill(raw + kl * rows + g * 4, s, ok ? 16 : 0);
+    }
+  }
+}
+
+// ---- stage 2: raw ring -> UMMA operand stage (hi / lo), K-major tile ----------------------------
+// UMMA tile [rows x 16k]: float4 index = (k/4) * rows + row -> LBO (next K chunk) = rows*16 B, SBO = 128 B.
+template <int MAJ, int ROWS_T>
+__device__ __forceinline__ void raw_convert(const float* raw, int rows_rt, int k0, int kend, int ones_row, float4* hi,
+                                            float4* lo) {
+  const int rows = ROWS_T ? ROWS_T : rows_rt;
+  const int total = rows * 4;
+#pragma unroll
   for (int q = threadIdx.x; q < total; q += TC_THREADS) {
     const int c4 = q / rows, row = q - c4 * rows;
-    const int k = k0 + c4 * 4;
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row < rows_valid && k < K) x = *reinterpret_cast<const float4*>(src + (long)row * ld + k);
+    float4 x;
+    if (MAJ == TC_K_MAJOR) {
+      x = *reinterpret_cast<const float4*>(raw + row * 16 + ((c4 ^ ((row >> 1) & 3)) << 2));
+    } else {
+      const float* r0 = raw + (c4 * 4) * rows + row;
+      x = make_float4(r0[0], r0[rows], r0[2 * rows], r0[3 * rows]);
+      if (row == ones_row) {
+        const int k = k0 + c4 * 4;
+        x = make_float4(k < kend ? 1.f : 0.f, k + 1 < kend ? 1.f : 0.f, k + 2 < kend ? 1.f : 0.f, k + 3 < kend ? 1.f : 0.f);
+      }
+    }
     split_store(x, hi + q, lo + q);
   }
 }
 
-// Source MN-major: element (row, k) = src[k * ld + row] (rows contiguous). The tensor core only
-// accepted K-major tf32 operands without swizzle in our probes (MN-major descriptors produced
-// zeros), so this stager transposes on the fly into the same K-major tile: a float4 of 4
-// consecutive rows is scattered as 4 scalars. Lanes are mapped (k%4, row-group) and each lane
-// rotates its store order so that a warp's 32 scalar stores hit 32 distinct banks.
-__device__ __forceinline__ void stage_transposed(const float* __restrict__ src, long ld, int rows, int rows_valid,
-                                                 int k0, int K, int ones_row, float* hi, float* lo) {
-  const int groups = rows / 4;
-  const int total = TC_KC * groups;
-  for (int q = threadIdx.x; q < total; q += TC_THREADS) {
-    const int kq = q & 3;
-    const int g = (q >> 2) % groups;
-    const int k4 = (q >> 2) / groups;
-    const int k = k0 + k4 * 4 + kq;
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (k < K) {
-      if (g * 4 < rows_valid) x = *reinterpret_cast<const float4*>(src + (long)k * ld + g * 4);
-      if (ones_row >= 0 && (ones_row >> 2) == g) (&x.x)[ones_row & 3] = 1.0f;
-    }
-    const float xs[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int i = (j + (g >> 1)) & 3;
-      const float v = xs[i];
-      const float h = tf32_rna(v);
-      const int idx = (k4 * rows + g * 4 + i) * 4 + kq;
-      hi[idx] = h;
-      lo[idx] = tf32_rna(v - h);
-    }
-  }
-}
-
-template <int AMAJ, int BMAJ>
-__global__ void __launch_bounds__(TC_THREADS) tc_gemm_kernel(const TcArgs p) {
-  extern __shared__ __align__(128) unsigned char tc_smem[];
-  __shared__ __align__(8) uint64_t s_bar[2];
-  __shared__ uint32_t s_tmem;
-
-  const int tid = threadIdx.x, warp = tid >> 5;
+// ---- weights: split once per launch into per-chunk UMMA images ---------------------------------
+// image of chunk c (NT*8 float4 = NT*128 B): [hi: (k/4)*NT + row][lo: same], so the GEMM CTAs copy
+// it into shared memory with plain 16-byte cp.async and never touch it with the ALU.
+template <int MAJ>
+__global__ void __launch_bounds__(256) tc_prepare_b(const TcArgs p, float4* __restrict__ dst, long batch_stride_f4) {
   const TcBatch bt = p.b[blockIdx.y];
   const int NT = p.NT;
   const int Ktot = bt.K > 0 ? bt.K : p.K;
   const int Kb = bt.kb_valid > 0 ? min(bt.kb_valid, Ktot) : Ktot;
-  const uint32_t a_f4 = TC_M * (TC_KC / 4);          // float4s per A stage half (hi or lo)
-  const uint32_t b_f4 = (uint32_t)NT * (TC_KC / 4);
-  float4* sA_hi = reinterpret_cast<float4*>(tc_smem);            // [2][a_f4]
-  float4* sA_lo = sA_hi + 2 * a_f4;
-  float4* sB_hi = sA_lo + 2 * a_f4;                              // [2][b_f4]
-  float4* sB_lo = sB_hi + 2 * b_f4;
-
-  uint32_t ncols = 32;
-  while (ncols < (uint32_t)NT) ncols <<= 1;
-  if (warp == 0) tmem_alloc(&s_tmem, ncols);
-  if (tid == 0) {
-    mbar_init(&s_bar[0], 1);
-    mbar_init(&s_bar[1], 1);
-    fence_mbar_init();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = s_tmem;
-
-  // Tile origin and contraction range.
-  int m0 = 0, kbeg = 0, kend = Ktot;
-  const float* Abase = bt.A;
-  if (AMAJ == TC_K_MAJOR) {
-    m0 = blockIdx.x * TC_M;
-    Abase += (long)m0 * p.lda;
-  } else {
-    kbeg = blockIdx.x * p.k_per_cta;
-    kend = min(Ktot, kbeg + p.k_per_cta);
-  }
-  const int a_rows_valid = (AMAJ == TC_K_MAJOR) ? max(0, min(TC_M, p.M - m0)) : min(TC_M, p.M);
-  const int nchunks = (kend - kbeg + TC_KC - 1) / TC_KC;
-  const int kend_b = min(kend, Kb);
-
-  const uint32_t idesc = umma_idesc_tf32(TC_M, NT);
-  const uint32_t a_lbo = TC_M * 16u, b_lbo = (uint32_t)NT * 16u;
-  const uint32_t sbo = 128u;
-  // bytes to advance the descriptor start address per UMMA k-step (8 tf32 = two 16-byte K chunks)
-  const uint32_t a_kstep = 2u * TC_M * 16u;
-  const uint32_t b_kstep = 2u * (uint32_t)NT * 16u;
-
-  for (int c = 0; c < nchunks; ++c) {
-    const int s = c & 1;
-    if (c >= 2) mbar_wait(&s_bar[s], (uint32_t)(((c >> 1) - 1) & 1));  // MMAs of chunk c-2 done with stage s
-    const int k0 = kbeg + c * TC_KC;
-    if (AMAJ == TC_K_MAJOR)
-      stage_k_major(Abase, p.lda, TC_M, a_rows_valid, k0, kend, sA_hi + s * a_f4, sA_lo + s * a_f4);
-    else
-      stage_transposed(Abase, p.lda, TC_M, a_rows_valid, k0, kend, -1, reinterpret_cast<float*>(sA_hi + s * a_f4),
-                       reinterpret_cast<float*>(sA_lo + s * a_f4));
-    if (BMAJ == TC_K_MAJOR)
-      stage_k_major(bt.B, p.ldb, NT, bt.n_valid, k0, kend_b, sB_hi + s * b_f4, sB_lo + s * b_f4);
-    else
-      stage_transposed(bt.B, p.ldb, NT, bt.n_valid, k0, kend_b, p.ones_col, reinterpret_cast<float*>(sB_hi + s * b_f4),
-                       reinterpret_cast<float*>(sB_lo + s * b_f4));
-    fence_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      const uint32_t ah = smem_u32(sA_hi + s * a_f4), al = smem_u32(sA_lo + s * a_f4);
-      const uint32_t bh = smem_u32(sB_hi + s * b_f4), bl = smem_u32(sB_lo + s * b_f4);
+  const int c = blockIdx.x;
+  const int k0 = c * TC_KC;
+  if (k0 >= Ktot) return;
+  float4* img = dst + (long)blockIdx.y * batch_stride_f4 + (long)c * NT * 8;
+  for (int q = threadIdx.x; q < NT * 4; q += 256) {
+    const int c4 = q / NT, row = q - c4 * NT;
+    const int k = k0 + c4 * 4;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row < bt.n_valid) {
+      if (MAJ == TC_K_MAJOR) {
+        if (k < Kb) x = *reinterpret_cast<const float4*>(bt.B + (long)row * p.ldb + k);
+      } else {
+        float* xs = &x.x;
 #pragma unroll
-      for (int ks = 0; ks < TC_KC / 8; ++ks) {
-        const uint64_t dah = umma_desc(ah + ks * a_kstep, a_lbo, sbo);
-        const uint64_t dal = umma_desc(al + ks * a_kstep, a_lbo, sbo);
-        const uint64_t dbh = umma_desc(bh + ks * b_kstep, b_lbo, sbo);
-        const uint64_t dbl = umma_desc(bl + ks * b_kstep, b_lbo, sbo);
-        const uint32_t first = (c == 0 && ks == 0) ? 0u : 1u;
-        if (p.dbg & 2) {
-          umma_tf32(tmem, dah, dbh, idesc, first);
-        } else {
-          umma_tf32(tmem, dal, dbh, idesc, first);  // small terms first
-          umma_tf32(tmem, dah, dbl, idesc, 1u);
-          umma_tf32(tmem, dah, dbh, idesc, 1u);
-        }
-      }
-      umma_commit(&s_bar[s]);
-    }
-  }
-  if (nchunks > 0) {
-    const int last = nchunks - 1;
-    mbar_wait(&s_bar[last & 1], (uint32_t)((last >> 1) & 1));
-  }
-  tc_fence_after();
-
-  // ---- epilogue: thread t owns accumulator row t (TMEM lane t) ----
-  const int row = tid;
-  const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-  const long grow = (long)m0 + row;  // global row for K-major A
-  const bool row_ok = row < a_rows_valid;
-  for (int n0 = 0; n0 < NT; n0 += 16) {
-    float v[16];
-    if (nchunks > 0) {
-      tmem_ld16(lane_addr + (uint32_t)n0, v);
-    } else {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = 0.f;
-    }
-    if (!row_ok) continue;
-    if (AMAJ == TC_K_MAJOR) {
-      const bool full = (n0 + 16 <= bt.n_valid);
-      switch (p.epilogue) {
-        case TC_EPI_BIAS_ACT: {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int n = n0 + i;
-            if (n < bt.n_valid) {
-              float x = v[i] + (bt.bias ? bt.bias[n] : 0.f);
-              if (p.relu) x = fmaxf(x, 0.f);
-              v[i] = x;
-            }
-          }
-          if (full && (bt.ldc & 3) == 0) {
-            float4* dst = reinterpret_cast<float4*>(bt.C + grow * bt.ldc + n0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-          } else {
-            for (int i = 0; i < 16; ++i)
-              if (n0 + i < bt.n_valid) bt.C[grow * bt.ldc + n0 + i] = v[i];
-          }
-        } break;
-        case TC_EPI_MASK: {
-          if (full && (bt.ldc & 3) == 0 && (bt.ldaux & 3) == 0) {
-            const float4* msk = reinterpret_cast<const float4*>(bt.aux + grow * bt.ldaux + n0);
-            float4* dst = reinterpret_cast<float4*>(bt.C + grow * bt.ldc + n0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float4 m = msk[i];
-              dst[i] = make_float4(m.x > 0.f ? v[4 * i] : 0.f, m.y > 0.f ? v[4 * i + 1] : 0.f,
-                                   m.z > 0.f ? v[4 * i + 2] : 0.f, m.w > 0.f ? v[4 * i + 3] : 0.f);
-            }
-          } else {
-            for (int i = 0; i < 16; ++i) {
-              const int n = n0 + i;
-              if (n < bt.n_valid) bt.C[grow * bt.ldc + n] = (bt.aux[grow * bt.ldaux + n] > 0.f) ? v[i] : 0.f;
-            }
-          }
-        } break;
-        case TC_EPI_ACCUM: {
-          for (int i = 0; i < 16; ++i) {
-            const int n = n0 + i;
-            if (n < bt.n_valid) {
-              float* dst = bt.C + grow * bt.ldc + n;
-              *dst = (p.accumulate ? *dst : 0.f) + v[i];
-            }
-          }
-        } break;
-        case TC_EPI_HEAD: {
-          for (int i = 0; i < 16; ++i) {
-            const int n = n0 + i;
-            if (n < bt.n_valid)
-              bt.C[grow * bt.ldc + n] = bt.aux[grow * bt.ldaux + n] + (v[i] + bt.bias[n]) * bt.scale;
-          }
-        } break;
-        default: break;
-      }
-    } else {
-      // weight gradients: D row = feature m, contraction was over Gaussians
-      for (int i = 0; i < 16; ++i) {
-        const int n = n0 + i;
-        if (n < bt.n_valid) {
-          float* dst = (p.epilogue == TC_EPI_ATOMIC_T) ? (bt.C + (long)n * bt.ldc + row) : (bt.C + (long)row * bt.ldc + n);
-          atomicAdd(dst, v[i]);
-        } else if (n == p.ones_col && bt.bias_grad != nullptr) {
-          atomicAdd(bt.bias_grad + row, v[i]);
-        }
+        for (int i = 0; i < 4; ++i)
+          if (k + i < Kb) xs[i] = bt.B[(long)(k + i) * p.ldb + row];
       }
     }
+    split_store(x, img + q, img + NT * 4 + q);
   }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, ncols);
 }
 
-inline size_t tc_gemm_smem_bytes(int NT) { return (size_t)2 * 2 * (TC_M + NT) * (TC_KC / 4) * sizeof(float4); }
+inline size_t tc_raw_stages(int NT) { return NT <= 128 ? 3 : 2; }
+// Shared memory of one CTA. bprep: B arrives as prepared images (ring of 3), A through a raw ring of 2.
+inline size_t tc_gemm_smem_bytes(int NT, bool bprep) {
+  if (bprep) {
+    return (size_t)2 * TC_M * TC_KC * sizeof(float)                 // raw A ring
+           + (size_t)2 * 2 * TC_M * (TC_KC / 4) * sizeof(float4)     // UMMA A stages (hi, lo)
+           + (size_t)3 * NT * 8 * sizeof(float4);                    // prepared-B ring
+  }
+  const size_t raw = tc_raw_stages(NT) * (size_t)(TC_M + NT) * TC_KC * sizeof(float);
+  const size_t umma = (size_t)2 * 2 * (TC_M + NT) * (TC_KC / 4) * sizeof(float4);
+  return raw + umma;
+}
 
 }  // namespace ed3dgs
+
+#include "tc_gemm_kernel.cuh"

@@ -1,0 +1,70 @@
+// Host-side launch of the tensor-core GEMM block: picks the instantiation (tile width, prepared
+// weights or not), splits weight operands into UMMA images first, orders blocks so that the batch
+// entries (heads) of one row tile are adjacent.
+#pragma once
+#include "tc_gemm.cuh"
+#include "profiler.h"
+
+namespace ed3dgs {
+
+// floats of scratch the prepared-weight images of one launch can need:
+// 5 heads x K=128 or one matrix with K=640, NT <= 128  ->  40 chunks x 128 x 8 float4
+inline size_t tc_prep_scratch_floats() { return (size_t)48 * 128 * 8 * 4; }
+
+template <int AMAJ, int BMAJ, int NT_T, bool BPREP>
+static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, const char* name, cudaStream_t stream) {
+  const size_t smem = tc_gemm_smem_bytes(a.NT, BPREP);
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<AMAJ, BMAJ, NT_T, BPREP>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  ProfScope ps(name, stream);
+  tc_gemm_kernel<AMAJ, BMAJ, NT_T, BPREP><<<grid, TC_THREADS, smem, stream>>>(a);
+  return cudaGetLastError();
+}
+
+inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch, float* prep_scratch,
+                             cudaStream_t stream) {
+  if (nbatch <= 0) return cudaSuccess;
+  TcArgs a = a_in;
+  a.nbatch = nbatch;
+  unsigned tiles;
+  if (amaj == TC_K_MAJOR) tiles = (a.M + TC_M - 1) / TC_M;
+  else tiles = (a.K + a.k_per_cta - 1) / a.k_per_cta;
+  if (tiles == 0) return cudaSuccess;
+  const dim3 grid(tiles * (unsigned)nbatch, 1, 1);  // batch entries of one tile are adjacent blocks
+  if (amaj == TC_K_MAJOR) {
+    // weights: split once into per-chunk hi/lo images
+    int kmax = 0;
+    for (int i = 0; i < nbatch; ++i) kmax = max(kmax, a.b[i].K > 0 ? a.b[i].K : a.K);
+    const int chunks = (kmax + TC_KC - 1) / TC_KC;
+    const long stride_f4 = (long)chunks * a.NT * 8;
+    if ((size_t)stride_f4 * nbatch * 4 > tc_prep_scratch_floats() || prep_scratch == nullptr) return cudaErrorInvalidValue;
+    for (int i = 0; i < nbatch; ++i) a.b[i].Bprep = reinterpret_cast<const float4*>(prep_scratch) + i * stride_f4;
+    {
+      ProfScope ps("tc_prepare_b", stream);
+      const dim3 pg(chunks, nbatch, 1);
+      if (bmaj == TC_K_MAJOR) tc_prepare_b<TC_K_MAJOR><<<pg, 256, 0, stream>>>(a, reinterpret_cast<float4*>(prep_scratch), stride_f4);
+      else tc_prepare_b<TC_MN_MAJOR><<<pg, 256, 0, stream>>>(a, reinterpret_cast<float4*>(prep_scratch), stride_f4);
+    }
+    const char* name = (bmaj == TC_MN_MAJOR) ? "tc_gemm_kernel<dgrad>" : "tc_gemm_kernel<fwd>";
+    switch (a.NT) {
+      case 128: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 128, true>(a, grid, name, stream);
+      case 48: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 48, true>(a, grid, name, stream);
+      case 32: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 32, true>(a, grid, name, stream);
+      default: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 0, true>(a, grid, name, stream);
+    }
+  }
+  if (bmaj != TC_MN_MAJOR) return cudaErrorInvalidValue;
+  const char* name = "tc_gemm_kernel<wgrad>";
+  switch (a.NT) {
+    case 144: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 144, false>(a, grid, name, stream);
+    case 48: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 48, false>(a, grid, name, stream);
+    default: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 0, false>(a, grid, name, stream);
+  }
+}
+
+}  // namespace ed3dgs
