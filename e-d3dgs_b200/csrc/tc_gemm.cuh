@@ -37,7 +37,16 @@ enum TcEpilogue : int {
 
 constexpr int TC_MAX_BATCH = 5;
 constexpr int TC_M = 128;        // rows per CTA = TMEM lanes
-constexpr int TC_KC = 16;        // K elements per pipeline chunk (two UMMA k-steps)
+#ifndef ED3DGS_TC_KC
+#define ED3DGS_TC_KC 16
+#endif
+constexpr int TC_KC = ED3DGS_TC_KC;   // K elements per pipeline chunk (8 or 16: one or two UMMA k-steps)
+constexpr int TC_PC = TC_KC / 4;      // 16-byte pieces per row of a chunk
+// K-major raw tile: 16-byte pieces XOR-swizzled inside a row so the conversion pass (8 consecutive
+// rows per quarter-warp) reads conflict-free.
+__device__ __forceinline__ int tc_raw_kmajor(int row, int c4) {
+  return row * TC_KC + ((c4 ^ ((row >> (TC_PC == 4 ? 1 : 2)) & (TC_PC - 1))) << 2);
+}
 constexpr int TC_THREADS = 256;
 
 struct TcBatch {
@@ -55,6 +64,12 @@ struct TcBatch {
   const float4* Bprep;   // set by tc_launch: per-chunk UMMA images of B (weights), see tc_prepare_b
 };
 
+// Per-tile programme of the persistent rows kernel (tc_rows.cuh), built on the host by tc_launch:
+// a list of 16-wide K slabs; each one is an activation slab to stage (hi/lo), a prepared weight
+// slab to copy and 3 or 6 UMMAs.
+constexpr int TC_MAX_STEPS = 48;
+enum TcStepFlags : int { TC_STEP_FIRST = 1, TC_STEP_LAST = 2 };
+
 struct TcArgs {
   TcBatch b[TC_MAX_BATCH];
   long lda, ldb;
@@ -68,6 +83,9 @@ struct TcArgs {
   int accumulate; // ACCUM
   int ones_col;   // MN-major B: column of D that sums A over the contraction (-1: none)
   int dbg;        // test hook: 2 = single pass (hi*hi only)
+  // rows kernel programme (K-major A only)
+  int nsteps, ntiles;
+  uint32_t steps[TC_MAX_STEPS];   // batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
 };
 
 // ---- raw PTX wrappers ------------------------------------------------------------------------
@@ -132,6 +150,40 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// One lane of a converged warp (the issuing lane of tcgen05.mma / bulk copies).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// Bulk copy global -> shared through the TMA unit (no tensor map), completion on an mbarrier.
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 __device__ __forceinline__ float tf32_rna(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -188,14 +240,14 @@ __device__ __forceinline__ void raw_issue(float* raw, const float* __restrict__ 
                                           int rows_valid, int k0, int kend) {
   const int rows = ROWS_T ? ROWS_T : rows_rt;
   if (MAJ == TC_K_MAJOR) {
-    const int total = rows * 4;
+    const int total = rows * TC_PC;
 #pragma unroll
     for (int q = threadIdx.x; q < total; q += TC_THREADS) {
-      const int row = q >> 2, c4 = q & 3;
+      const int row = q / TC_PC, c4 = q % TC_PC;
       const int k = k0 + c4 * 4;
       const bool ok = row < rows_valid && k < kend;
       const float* s = ok ? (src + (long)row * ld + k) : src;
-      cp_async16_zfill(raw + row * 16 + ((c4 ^ ((row >> 1) & 3)) << 2), s, ok ? 16 : 0);
+      cp_async16_zfill(raw + tc_raw_kmajor(row, c4), s, ok ? 16 : 0);
     }
   } else {
     const int groups = rows >> 2;
@@ -217,13 +269,13 @@ template <int MAJ, int ROWS_T>
 __device__ __forceinline__ void raw_convert(const float* raw, int rows_rt, int k0, int kend, int ones_row, float4* hi,
                                             float4* lo) {
   const int rows = ROWS_T ? ROWS_T : rows_rt;
-  const int total = rows * 4;
+  const int total = rows * TC_PC;
 #pragma unroll
   for (int q = threadIdx.x; q < total; q += TC_THREADS) {
     const int c4 = q / rows, row = q - c4 * rows;
     float4 x;
     if (MAJ == TC_K_MAJOR) {
-      x = *reinterpret_cast<const float4*>(raw + row * 16 + ((c4 ^ ((row >> 1) & 3)) << 2));
+      x = *reinterpret_cast<const float4*>(raw + tc_raw_kmajor(row, c4));
     } else {
       const float* r0 = raw + (c4 * 4) * rows + row;
       x = make_float4(r0[0], r0[rows], r0[2 * rows], r0[3 * rows]);
@@ -248,8 +300,8 @@ __global__ void __launch_bounds__(256) tc_prepare_b(const TcArgs p, float4* __re
   const int c = blockIdx.x;
   const int k0 = c * TC_KC;
   if (k0 >= Ktot) return;
-  float4* img = dst + (long)blockIdx.y * batch_stride_f4 + (long)c * NT * 8;
-  for (int q = threadIdx.x; q < NT * 4; q += 256) {
+  float4* img = dst + (long)blockIdx.y * batch_stride_f4 + (long)c * NT * (2 * TC_PC);
+  for (int q = threadIdx.x; q < NT * TC_PC; q += 256) {
     const int c4 = q / NT, row = q - c4 * NT;
     const int k = k0 + c4 * 4;
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -263,7 +315,7 @@ __global__ void __launch_bounds__(256) tc_prepare_b(const TcArgs p, float4* __re
           if (k + i < Kb) xs[i] = bt.B[(long)(k + i) * p.ldb + row];
       }
     }
-    split_store(x, img + q, img + NT * 4 + q);
+    split_store(x, img + q, img + NT * TC_PC + q);
   }
 }
 
@@ -273,7 +325,7 @@ inline size_t tc_gemm_smem_bytes(int NT, bool bprep) {
   if (bprep) {
     return (size_t)2 * TC_M * TC_KC * sizeof(float)                 // raw A ring
            + (size_t)2 * 2 * TC_M * (TC_KC / 4) * sizeof(float4)     // UMMA A stages (hi, lo)
-           + (size_t)3 * NT * 8 * sizeof(float4);                    // prepared-B ring
+           + (size_t)3 * NT * (2 * TC_PC) * sizeof(float4);          // prepared-B ring
   }
   const size_t raw = tc_raw_stages(NT) * (size_t)(TC_M + NT) * TC_KC * sizeof(float);
   const size_t umma = (size_t)2 * 2 * (TC_M + NT) * (TC_KC / 4) * sizeof(float4);

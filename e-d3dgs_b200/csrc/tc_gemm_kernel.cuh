@@ -95,7 +95,7 @@ __device__ __forceinline__ void tc_epilogue_row(const TcArgs& p, const TcBatch& 
 }
 
 template <int AMAJ, int BMAJ, int NT_T, bool BPREP>
-__global__ void __launch_bounds__(TC_THREADS, 2) tc_gemm_kernel(const TcArgs p) {
+__global__ void __launch_bounds__(TC_THREADS, (TC_KC == 8 && BPREP) ? 4 : 2) tc_gemm_kernel(const TcArgs p) {
   extern __shared__ __align__(128) unsigned char tc_smem[];
   __shared__ __align__(8) uint64_t s_bar[2];
   __shared__ uint32_t s_tmem;

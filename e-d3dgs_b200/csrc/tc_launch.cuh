@@ -3,6 +3,7 @@
 // entries (heads) of one row tile are adjacent.
 #pragma once
 #include "tc_gemm.cuh"
+#include "tc_rows.cuh"
 #include "profiler.h"
 
 namespace ed3dgs {
@@ -26,6 +27,53 @@ static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, const char* name, cud
   return cudaGetLastError();
 }
 
+// Programme of one tile of 256 Gaussians for tc_rows_kernel: the 16-wide K slabs of every batch
+// entry in order, with the flags that open and close an accumulation.
+inline bool tc_rows_build(TcArgs& a) {
+  int ns = 0;
+  for (int i = 0; i < a.nbatch; ++i) {
+    const int Ki = a.b[i].K > 0 ? a.b[i].K : a.K;
+    if (Ki <= 0 || (Ki & 3)) return false;
+    for (int k0 = 0; k0 < Ki; k0 += 16) {
+      if (ns >= TC_MAX_STEPS) return false;
+      const int left = Ki - k0;
+      const uint32_t npieces = left >= 16 ? 4 : (left + 3) / 4;
+      const uint32_t nk = left > 8 ? 2 : 1;
+      const uint32_t flags = (k0 == 0 ? TC_STEP_FIRST : 0) | (k0 + 16 >= Ki ? TC_STEP_LAST : 0);
+      a.steps[ns++] = (uint32_t)i | ((uint32_t)(k0 / 16) << 8) | (npieces << 16) | (nk << 20) | (flags << 24);
+    }
+  }
+  a.nsteps = ns;
+  a.ntiles = (a.M + ROWS_TG - 1) / ROWS_TG;
+  return ns > 0;
+}
+
+inline int tc_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
+  return sms;
+}
+
+inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stream) {
+  if ((a.lda & 3) || !tc_rows_build(a)) return cudaErrorInvalidValue;
+  for (int i = 0; i < a.nbatch; ++i)
+    if (a.b[i].n_valid > 128) return cudaErrorInvalidValue;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const int grid = a.ntiles < tc_sm_count() ? a.ntiles : tc_sm_count();
+  ProfScope ps(name, stream);
+  tc_rows_kernel<<<grid, ROWS_THREADS, ROWS_SMEM_BYTES, stream>>>(a);
+  return cudaGetLastError();
+}
+
 inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch, float* prep_scratch,
                              cudaStream_t stream) {
   if (nbatch <= 0) return cudaSuccess;
@@ -37,11 +85,12 @@ inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch,
   if (tiles == 0) return cudaSuccess;
   const dim3 grid(tiles * (unsigned)nbatch, 1, 1);  // batch entries of one tile are adjacent blocks
   if (amaj == TC_K_MAJOR) {
-    // weights: split once into per-chunk hi/lo images
+    // weights: split once into per-slab hi/lo images of 128 rows (rows >= n_valid are zero)
+    a.NT = 128;
     int kmax = 0;
     for (int i = 0; i < nbatch; ++i) kmax = max(kmax, a.b[i].K > 0 ? a.b[i].K : a.K);
     const int chunks = (kmax + TC_KC - 1) / TC_KC;
-    const long stride_f4 = (long)chunks * a.NT * 8;
+    const long stride_f4 = (long)chunks * a.NT * (2 * TC_PC);
     if ((size_t)stride_f4 * nbatch * 4 > tc_prep_scratch_floats() || prep_scratch == nullptr) return cudaErrorInvalidValue;
     for (int i = 0; i < nbatch; ++i) a.b[i].Bprep = reinterpret_cast<const float4*>(prep_scratch) + i * stride_f4;
     {
@@ -51,12 +100,7 @@ inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch,
       else tc_prepare_b<TC_MN_MAJOR><<<pg, 256, 0, stream>>>(a, reinterpret_cast<float4*>(prep_scratch), stride_f4);
     }
     const char* name = (bmaj == TC_MN_MAJOR) ? "tc_gemm_kernel<dgrad>" : "tc_gemm_kernel<fwd>";
-    switch (a.NT) {
-      case 128: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 128, true>(a, grid, name, stream);
-      case 48: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 48, true>(a, grid, name, stream);
-      case 32: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 32, true>(a, grid, name, stream);
-      default: return tc_launch_t<TC_K_MAJOR, TC_K_MAJOR, 0, true>(a, grid, name, stream);
-    }
+    return tc_rows_launch(a, name, stream);
   }
   if (bmaj != TC_MN_MAJOR) return cudaErrorInvalidValue;
   const char* name = "tc_gemm_kernel<wgrad>";

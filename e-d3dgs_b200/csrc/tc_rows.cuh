@@ -1,0 +1,311 @@
+// Persistent, warp-specialised 3xTF32 GEMM over tiles of 256 Gaussians (sm_100a, tcgen05 + TMEM).
+//
+//   for every tile of 256 Gaussians g, for every batch entry (head):
+//       D^T[f][g] = sum_k W[f][k] * X[g][k]          f < 128 output features, then a fused epilogue
+//
+// The Gaussians sit on the N side of the UMMA (N = 256) and the <= 128 output features on the M
+// side: on B200 a 128 x N x 8 tf32 UMMA costs 128 clocks for every N <= 256 (tests/probes/mma_rate.cu),
+// so only N = 256 runs the tensor pipe at full rate. It also makes the epilogue naturally
+// coalesced: a TMEM lane is a feature, so the 32 lanes of a warp write 128 contiguous bytes of one
+// Gaussian's row.
+//
+// One CTA per SM walks the tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the work of a tile is a
+// list of 16-wide K slabs built on the host (TcArgs::steps, tc_launch.cuh). Four roles run that
+// list concurrently and meet only through mbarriers:
+//
+//   warps 10-17 X stagers   global --ld.global.v4, 4 slabs ahead in registers--> split hi/lo -->
+//                           UMMA K-major operand stages (ring of 4 x [256 Gaussians x 16 k])
+//   warp 9      W loader    prepared hi/lo weight slabs (tc_prepare_b) --cp.async.bulk--> ring of 4
+//   warp 8      MMA issuer  per slab: 2 k-steps x (W_lo*X_hi + W_hi*X_lo + W_hi*X_hi) tcgen05.mma;
+//                           tcgen05.commit releases the X stage / the W slot / the accumulator
+//   warps 0-7   epilogue    TMEM (2 accumulators of 256 columns, ping-pong) -> registers -> fused
+//                           bias/ReLU | ReLU-mask | accumulate | x + delta*coef -> global
+//
+// The SM is instruction-issue bound long before it is tensor bound (ncu: 18 warps, ~4400
+// warp-instructions per slab in the first version), so every role keeps its per-slab instruction
+// count small: descriptors are affine in the ring index, the step table is one 32-bit word per
+// slab, stagers keep running offsets, the epilogue is specialised on the row stride.
+#pragma once
+
+namespace ed3dgs {
+
+constexpr int ROWS_TG = 256;                             // Gaussians per tile = UMMA N
+constexpr int ROWS_EPI_WARPS = 8;                        // warps 0..7 (TMEM lane quarter = warp % 4)
+constexpr int ROWS_MMA_WARP = 8;
+constexpr int ROWS_LOAD_WARP = 9;
+constexpr int ROWS_CONV_WARP0 = 10;                      // 8 warps
+constexpr int ROWS_CONV_THREADS = 256;
+constexpr int ROWS_THREADS = (ROWS_CONV_WARP0 + 8) * 32;
+constexpr int ROWS_X_STAGES = 4;
+constexpr int ROWS_X_STAGE_BYTES = ROWS_TG * 16 * 4 * 2;  // hi + lo of [256 x 16]
+constexpr int ROWS_W_SLOTS = 4;
+constexpr int ROWS_W_SLOT_BYTES = 128 * 16 * 4 * 2;       // hi + lo of [128 x 16]
+constexpr int ROWS_PREFETCH = 4;
+constexpr size_t ROWS_SMEM_BYTES = (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES;
+
+struct RowsBars {
+  uint64_t x_full[ROWS_X_STAGES], x_free[ROWS_X_STAGES];
+  uint64_t w_full[ROWS_W_SLOTS], w_free[ROWS_W_SLOTS];
+  uint64_t acc_full[2], acc_free[2];
+};
+
+// hi = rna_tf32(x), lo = x - hi (exact). The tensor core ignores the low 13 bits of lo, which
+// perturbs a product by < 2^-21 relative: below the fp32 rounding of the accumulation.
+__device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* lo) {
+  float4 h;
+  h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
+  *hi = h;
+  *lo = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+}
+
+// Epilogue of one block of 32 Gaussians for this lane's feature: v[j] = D^T[f][g0 + j].
+// LD > 0: compile-time row stride of C (and of aux), so every access is base + immediate.
+// FULL: all 32 Gaussians of the block exist (no per-row predicate).
+template <int LD, bool FULL>
+__device__ __forceinline__ void rows_epilogue_block(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
+                                                    int jmax) {
+  const long ldc = LD ? LD : bt.ldc;
+  const long ldx = LD ? LD : bt.ldaux;
+  float* dst = bt.C + g0 * ldc + f;
+  if (p.epilogue == TC_EPI_BIAS_ACT) {
+    const float b = bt.bias != nullptr ? __ldg(bt.bias + f) : 0.f;
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (FULL || j < jmax) dst[j * ldc] = fmaxf(v[j] + b, 0.f);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (FULL || j < jmax) dst[j * ldc] = v[j] + b;
+    }
+  } else {
+    // the three other epilogues read one value per output first; a clamped row index keeps the
+    // loads unconditional, so they stay batched ahead of the stores
+    const float* src = (p.epilogue == TC_EPI_ACCUM) ? dst : (bt.aux + g0 * ldx + f);
+    const long lds = (p.epilogue == TC_EPI_ACCUM) ? ldc : ldx;
+    float o[32];
+    if (p.epilogue == TC_EPI_ACCUM && !p.accumulate) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) o[j] = 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) o[j] = src[(FULL ? j : min(j, jmax - 1)) * lds];
+    }
+    if (p.epilogue == TC_EPI_MASK) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (FULL || j < jmax) dst[j * ldc] = o[j] > 0.f ? v[j] : 0.f;
+    } else if (p.epilogue == TC_EPI_ACCUM) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (FULL || j < jmax) dst[j * ldc] = o[j] + v[j];
+    } else {  // TC_EPI_HEAD
+      const float b = __ldg(bt.bias + f);
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (FULL || j < jmax) dst[j * ldc] = o[j] + (v[j] + b) * bt.scale;
+    }
+  }
+}
+
+template <int LD>
+__device__ __forceinline__ void rows_epilogue_dispatch(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
+                                                       int jmax) {
+  if (jmax == 32) rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32);
+  else rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax);
+}
+
+// Step word (TcArgs::steps): batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
+__device__ __forceinline__ int step_batch(uint32_t w) { return (int)(w & 0xff); }
+__device__ __forceinline__ int step_slab(uint32_t w) { return (int)((w >> 8) & 0xff); }
+__device__ __forceinline__ int step_npieces(uint32_t w) { return (int)((w >> 16) & 0xf); }
+__device__ __forceinline__ int step_nk(uint32_t w) { return (int)((w >> 20) & 0xf); }
+__device__ __forceinline__ int step_flags(uint32_t w) { return (int)(w >> 24); }
+
+__device__ __forceinline__ uint64_t desc64(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
+
+__global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcArgs p) {
+  extern __shared__ __align__(128) unsigned char rows_smem[];
+  __shared__ RowsBars bars;
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  unsigned char* sX = rows_smem;
+  unsigned char* sW = sX + (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES;
+
+  if (warp == 0) tmem_alloc(&s_tmem, 512);
+  if (tid == 32) {
+    for (int i = 0; i < ROWS_X_STAGES; ++i) { mbar_init(&bars.x_full[i], ROWS_CONV_THREADS); mbar_init(&bars.x_free[i], 1); }
+    for (int i = 0; i < ROWS_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars.acc_full[i], 1); mbar_init(&bars.acc_free[i], ROWS_EPI_WARPS * 32); }
+    fence_mbar_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  const int my_tiles = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int nsteps = p.nsteps;
+  const int total = my_tiles * nsteps;   // slabs this CTA walks; the same counter drives every ring
+
+  if (warp >= ROWS_CONV_WARP0) {
+    // ------------------------------------------------------------------ X stagers (256 threads)
+    // One slab = 256 Gaussians x 16 k = 1024 pieces of 16 bytes, 4 per thread: 8 consecutive lanes
+    // take 8 consecutive Gaussians of one piece (conflict-free 128-byte shared-memory stores), the 4
+    // lane groups of a warp take the 4 pieces of a row (64 contiguous bytes of global memory).
+    const int cw = warp - ROWS_CONV_WARP0;
+    const int piece = lane >> 3;
+    const int row0 = cw * 32 + (lane & 7);            // rows row0 + 8 i, i = 0..3
+    const long roff = (long)row0 * p.lda + piece * 4;  // float offset of (row0, piece) inside a tile slab
+    const long lda8 = 8 * p.lda;
+    const long tile_stride = (long)gridDim.x * ROWS_TG * p.lda;
+    float4 buf[ROWS_PREFETCH][4];
+    // running position of the next slab to fetch
+    int fs = 0;
+    long ftile_off = (long)blockIdx.x * ROWS_TG * p.lda;
+    int frows = p.M - (int)blockIdx.x * ROWS_TG;      // rows of the tile that exist (may exceed 256)
+    auto fetch = [&](float4* r) {
+      const uint32_t st = p.steps[fs];
+      const float* base = p.b[step_batch(st)].A + ftile_off + step_slab(st) * 16 + roff;
+      const bool piece_ok = piece < step_npieces(st);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        r[i] = (piece_ok && row0 + 8 * i < frows) ? __ldg(reinterpret_cast<const float4*>(base + i * lda8))
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (++fs == nsteps) { fs = 0; ftile_off += tile_stride; frows -= (int)gridDim.x * ROWS_TG; }
+    };
+    float4* const hi0 = reinterpret_cast<float4*>(sX) + piece * ROWS_TG + row0;
+    auto stage_out = [&](int g, const float4* r) {
+      const int stage = g & (ROWS_X_STAGES - 1);
+      if (g >= ROWS_X_STAGES) {
+        mbar_wait(&bars.x_free[stage], (uint32_t)(((g >> 2) - 1) & 1));
+        tc_fence_after();
+      }
+      float4* hi = hi0 + stage * (ROWS_X_STAGE_BYTES / 16);
+      float4* lo = hi + 4 * ROWS_TG;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) split_store_fast(r[i], hi + 8 * i, lo + 8 * i);
+      fence_async_smem();
+      mbar_arrive(&bars.x_full[stage]);
+    };
+#pragma unroll
+    for (int u = 0; u < ROWS_PREFETCH; ++u)
+      if (u < total) fetch(buf[u]);
+    for (int g0 = 0; g0 < total; g0 += ROWS_PREFETCH) {
+#pragma unroll
+      for (int u = 0; u < ROWS_PREFETCH; ++u) {
+        const int g = g0 + u;
+        if (g < total) {
+          stage_out(g, buf[u]);
+          if (g + ROWS_PREFETCH < total) fetch(buf[u]);
+        }
+      }
+    }
+  } else if (warp == ROWS_LOAD_WARP) {
+    // ------------------------------------------------------------------ W loader (converged warp, elected lane issues)
+    int s = 0;
+    for (int g = 0; g < total; ++g) {
+      const uint32_t st = p.steps[s];
+      if (++s == nsteps) s = 0;
+      const int slot = g & (ROWS_W_SLOTS - 1);
+      if (g >= ROWS_W_SLOTS) mbar_wait(&bars.w_free[slot], (uint32_t)(((g >> 2) - 1) & 1));
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&bars.w_full[slot], ROWS_W_SLOT_BYTES);
+        bulk_copy_g2s(sW + (size_t)slot * ROWS_W_SLOT_BYTES, p.b[step_batch(st)].Bprep + (size_t)step_slab(st) * (128 * 8),
+                      ROWS_W_SLOT_BYTES, &bars.w_full[slot]);
+      }
+      __syncwarp();
+    }
+  } else if (warp == ROWS_MMA_WARP) {
+    // ------------------------------------------------------------------ MMA issuer (converged warp, elected lane issues)
+    // Descriptors are affine in the ring index: low word = start address >> 4 | LBO >> 4 << 16,
+    // high word = SBO >> 4 | version.
+    const uint32_t idesc = umma_idesc_tf32(128, ROWS_TG);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+    const uint32_t w_lo0 = ((smem_u32(sW) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
+    const uint32_t x_lo0 = ((smem_u32(sX) & 0x3FFFFu) >> 4) | ((ROWS_TG * 16u >> 4) << 16);
+    constexpr uint32_t W_SLOT = ROWS_W_SLOT_BYTES >> 4, W_LO = W_SLOT / 2, W_KS = (2u * 128u * 16u) >> 4;
+    constexpr uint32_t X_STAGE = ROWS_X_STAGE_BYTES >> 4, X_LO = X_STAGE / 2, X_KS = (2u * ROWS_TG * 16u) >> 4;
+    const bool single = (p.dbg & 2) != 0;
+    int s = 0, go = 0;
+    uint32_t acc = tmem;
+    for (int g = 0; g < total; ++g) {
+      const uint32_t st = p.steps[s];
+      if (++s == nsteps) s = 0;
+      const int fl = step_flags(st);
+      if (fl & TC_STEP_FIRST) {
+        if (go >= 2) mbar_wait(&bars.acc_free[go & 1], (uint32_t)(((go >> 1) - 1) & 1));
+        acc = tmem + (uint32_t)(go & 1) * ROWS_TG;
+      }
+      const int ring = g & 3;
+      const uint32_t par = (uint32_t)((g >> 2) & 1);
+      mbar_wait(&bars.x_full[ring], par);
+      mbar_wait(&bars.w_full[ring], par);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t wh = w_lo0 + (uint32_t)ring * W_SLOT, xh = x_lo0 + (uint32_t)ring * X_STAGE;
+        const uint32_t first = (fl & TC_STEP_FIRST) ? 0u : 1u;
+        if (single) {
+          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh), idesc, first);
+          if (step_nk(st) == 2) umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS), idesc, 1u);
+        } else {
+          umma_tf32(acc, desc64(desc_hi, wh + W_LO), desc64(desc_hi, xh), idesc, first);  // small terms first
+          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh + X_LO), idesc, 1u);
+          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh), idesc, 1u);
+          if (step_nk(st) == 2) {
+            umma_tf32(acc, desc64(desc_hi, wh + W_KS + W_LO), desc64(desc_hi, xh + X_KS), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS + X_LO), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS), idesc, 1u);
+          }
+        }
+        umma_commit(&bars.w_free[ring]);
+        umma_commit(&bars.x_free[ring]);
+        if (fl & TC_STEP_LAST) umma_commit(&bars.acc_full[go & 1]);
+      }
+      __syncwarp();
+      if (fl & TC_STEP_LAST) ++go;
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 0..7)
+    // warp e: features 32*(e&3) .. +31 (its TMEM lane quarter); blocks of 32 Gaussians alternate
+    // between the two warps that share a quarter.
+    const int q = warp & 3, par = warp >> 2;
+    const int f = q * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    int go = 0;
+    for (int tl = 0; tl < my_tiles; ++tl) {
+      const long tile = (long)blockIdx.x + (long)tl * gridDim.x;
+      for (int o = 0; o < p.nbatch; ++o, ++go) {
+        const TcBatch& bt = p.b[o];
+        const int buf = go & 1;
+        mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
+        tc_fence_after();
+        if (q * 32 < bt.n_valid) {
+          const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
+          const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
+          for (int blk = par; blk < ROWS_TG / 32; blk += 2) {
+            const long g0 = tile * ROWS_TG + blk * 32;
+            const int jmax = (int)min(32L, (long)p.M - g0);
+            if (jmax <= 0) break;
+            float v[32];
+            tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
+            if (f < bt.n_valid) {
+              if (ld_case == 640) rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax);
+              else if (ld_case == 128) rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax);
+              else rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&bars.acc_free[buf]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace ed3dgs
