@@ -36,12 +36,14 @@ constexpr int ROWS_LOAD_WARP = 9;
 constexpr int ROWS_CONV_WARP0 = 10;                      // 8 warps
 constexpr int ROWS_CONV_THREADS = 256;
 constexpr int ROWS_THREADS = (ROWS_CONV_WARP0 + 8) * 32;
-constexpr int ROWS_X_STAGES = 4;
+constexpr int ROWS_X_STAGES = 3;
 constexpr int ROWS_X_STAGE_BYTES = ROWS_TG * 16 * 4 * 2;  // hi + lo of [256 x 16]
-constexpr int ROWS_W_SLOTS = 4;
+constexpr int ROWS_W_SLOTS = 3;
 constexpr int ROWS_W_SLOT_BYTES = 128 * 16 * 4 * 2;       // hi + lo of [128 x 16]
-constexpr int ROWS_PREFETCH = 4;
-constexpr size_t ROWS_SMEM_BYTES = (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES;
+constexpr int ROWS_RAW_SLOTS = 4;                        // cp.async raw slabs in flight per stager thread
+constexpr int ROWS_RAW_SLOT_BYTES = ROWS_TG * 16 * 4;
+constexpr size_t ROWS_SMEM_BYTES = (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES +
+                                   (size_t)ROWS_RAW_SLOTS * ROWS_RAW_SLOT_BYTES;
 
 struct RowsBars {
   uint64_t x_full[ROWS_X_STAGES], x_free[ROWS_X_STAGES];
@@ -124,6 +126,17 @@ __device__ __forceinline__ int step_flags(uint32_t w) { return (int)(w >> 24); }
 
 __device__ __forceinline__ uint64_t desc64(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
 
+// Position in a ring of N slots plus the mbarrier phase of the current round. Consumers wait on
+// full[idx] with `phase`; producers wait on free[idx] with `phase ^ 1` (passes at once in round 0).
+template <int N>
+struct RingPos {
+  int idx = 0;
+  uint32_t phase = 0;
+  __device__ __forceinline__ void advance() {
+    if (++idx == N) { idx = 0; phase ^= 1u; }
+  }
+};
+
 __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcArgs p) {
   extern __shared__ __align__(128) unsigned char rows_smem[];
   __shared__ RowsBars bars;
@@ -132,6 +145,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   unsigned char* sX = rows_smem;
   unsigned char* sW = sX + (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES;
+  unsigned char* sRaw = sW + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES;
 
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
@@ -147,75 +161,84 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
 
   const int my_tiles = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int nsteps = p.nsteps;
-  const int total = my_tiles * nsteps;   // slabs this CTA walks; the same counter drives every ring
+  const int total = my_tiles * nsteps;   // slabs this CTA walks; every role counts them the same way
 
   if (warp >= ROWS_CONV_WARP0) {
     // ------------------------------------------------------------------ X stagers (256 threads)
     // One slab = 256 Gaussians x 16 k = 1024 pieces of 16 bytes, 4 per thread: 8 consecutive lanes
-    // take 8 consecutive Gaussians of one piece (conflict-free 128-byte shared-memory stores), the 4
-    // lane groups of a warp take the 4 pieces of a row (64 contiguous bytes of global memory).
+    // take 8 consecutive Gaussians of one piece (conflict-free 128-byte stores into the UMMA stage),
+    // the 4 lane groups of a warp take the 4 pieces of a row (64 contiguous bytes of global memory).
+    // A thread converts exactly the pieces it copied itself, so the raw ring needs no barrier: the
+    // per-thread cp.async group counter is the only synchronisation (register-staged loads share
+    // scoreboards and serialise on memory latency; measured, tests/gemm_time.py).
     const int cw = warp - ROWS_CONV_WARP0;
     const int piece = lane >> 3;
-    const int row0 = cw * 32 + (lane & 7);            // rows row0 + 8 i, i = 0..3
+    const int row0 = cw * 32 + (lane & 7);             // rows row0 + 8 i, i = 0..3
     const long roff = (long)row0 * p.lda + piece * 4;  // float offset of (row0, piece) inside a tile slab
     const long lda8 = 8 * p.lda;
     const long tile_stride = (long)gridDim.x * ROWS_TG * p.lda;
-    float4 buf[ROWS_PREFETCH][4];
-    // running position of the next slab to fetch
-    int fs = 0;
+    float4* const raw0 = reinterpret_cast<float4*>(sRaw) + cw * 32 + lane;   // [slot][i][warp][lane]
+    // running position of the next slab to copy
+    int fs = 0, fslot = 0;
     long ftile_off = (long)blockIdx.x * ROWS_TG * p.lda;
-    int frows = p.M - (int)blockIdx.x * ROWS_TG;      // rows of the tile that exist (may exceed 256)
-    auto fetch = [&](float4* r) {
+    int frows = p.M - (int)blockIdx.x * ROWS_TG;       // rows of the tile that exist (may exceed 256)
+    auto issue = [&]() {
       const uint32_t st = p.steps[fs];
       const float* base = p.b[step_batch(st)].A + ftile_off + step_slab(st) * 16 + roff;
-      const bool piece_ok = piece < step_npieces(st);
+      const bool piece_ok = piece < step_npieces(st) && !(p.dbg & 8);
+      float4* dst = raw0 + fslot * (ROWS_RAW_SLOT_BYTES / 16);
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        r[i] = (piece_ok && row0 + 8 * i < frows) ? __ldg(reinterpret_cast<const float4*>(base + i * lda8))
-                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
-      if (++fs == nsteps) { fs = 0; ftile_off += tile_stride; frows -= (int)gridDim.x * ROWS_TG; }
-    };
-    float4* const hi0 = reinterpret_cast<float4*>(sX) + piece * ROWS_TG + row0;
-    auto stage_out = [&](int g, const float4* r) {
-      const int stage = g & (ROWS_X_STAGES - 1);
-      if (g >= ROWS_X_STAGES) {
-        mbar_wait(&bars.x_free[stage], (uint32_t)(((g >> 2) - 1) & 1));
-        tc_fence_after();
+      for (int i = 0; i < 4; ++i) {
+        const bool ok = piece_ok && row0 + 8 * i < frows;
+        cp_async16_zfill(dst + i * ROWS_CONV_THREADS, ok ? base + i * lda8 : base, ok ? 16 : 0);
       }
-      float4* hi = hi0 + stage * (ROWS_X_STAGE_BYTES / 16);
+      if (++fs == nsteps) { fs = 0; ftile_off += tile_stride; frows -= (int)gridDim.x * ROWS_TG; }
+      if (++fslot == ROWS_RAW_SLOTS) fslot = 0;
+    };
+    for (int u = 0; u < ROWS_RAW_SLOTS; ++u) {
+      if (u < total) issue();
+      cp_async_commit_group();
+    }
+    float4* const hi0 = reinterpret_cast<float4*>(sX) + piece * ROWS_TG + row0;
+    RingPos<ROWS_X_STAGES> xr;
+    int rslot = 0;
+    for (int g = 0; g < total; ++g) {
+      cp_async_wait_group<ROWS_RAW_SLOTS - 1>();        // this thread's pieces of slab g have landed
+      const float4* src = raw0 + rslot * (ROWS_RAW_SLOT_BYTES / 16);
+      float4 r[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) r[i] = src[i * ROWS_CONV_THREADS];
+      mbar_wait(&bars.x_free[xr.idx], xr.phase ^ 1u);
+      tc_fence_after();
+      float4* hi = hi0 + xr.idx * (ROWS_X_STAGE_BYTES / 16);
       float4* lo = hi + 4 * ROWS_TG;
 #pragma unroll
       for (int i = 0; i < 4; ++i) split_store_fast(r[i], hi + 8 * i, lo + 8 * i);
       fence_async_smem();
-      mbar_arrive(&bars.x_full[stage]);
-    };
-#pragma unroll
-    for (int u = 0; u < ROWS_PREFETCH; ++u)
-      if (u < total) fetch(buf[u]);
-    for (int g0 = 0; g0 < total; g0 += ROWS_PREFETCH) {
-#pragma unroll
-      for (int u = 0; u < ROWS_PREFETCH; ++u) {
-        const int g = g0 + u;
-        if (g < total) {
-          stage_out(g, buf[u]);
-          if (g + ROWS_PREFETCH < total) fetch(buf[u]);
-        }
-      }
+      mbar_arrive(&bars.x_full[xr.idx]);
+      xr.advance();
+      if (++rslot == ROWS_RAW_SLOTS) rslot = 0;
+      if (g + ROWS_RAW_SLOTS < total) issue();          // refills the raw slot just consumed
+      cp_async_commit_group();                          // always commit: keeps the group count uniform
     }
+    cp_async_wait_group<0>();
   } else if (warp == ROWS_LOAD_WARP) {
     // ------------------------------------------------------------------ W loader (converged warp, elected lane issues)
     int s = 0;
+    RingPos<ROWS_W_SLOTS> wr;
     for (int g = 0; g < total; ++g) {
       const uint32_t st = p.steps[s];
       if (++s == nsteps) s = 0;
-      const int slot = g & (ROWS_W_SLOTS - 1);
-      if (g >= ROWS_W_SLOTS) mbar_wait(&bars.w_free[slot], (uint32_t)(((g >> 2) - 1) & 1));
-      if (elect_one()) {
-        mbar_arrive_expect_tx(&bars.w_full[slot], ROWS_W_SLOT_BYTES);
-        bulk_copy_g2s(sW + (size_t)slot * ROWS_W_SLOT_BYTES, p.b[step_batch(st)].Bprep + (size_t)step_slab(st) * (128 * 8),
-                      ROWS_W_SLOT_BYTES, &bars.w_full[slot]);
+      mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
+      if ((p.dbg & 4) && g >= ROWS_W_SLOTS) {
+        if (elect_one()) mbar_arrive(&bars.w_full[wr.idx]);
+      } else if (elect_one()) {
+        mbar_arrive_expect_tx(&bars.w_full[wr.idx], ROWS_W_SLOT_BYTES);
+        bulk_copy_g2s(sW + (size_t)wr.idx * ROWS_W_SLOT_BYTES, p.b[step_batch(st)].Bprep + (size_t)step_slab(st) * (128 * 8),
+                      ROWS_W_SLOT_BYTES, &bars.w_full[wr.idx]);
       }
       __syncwarp();
+      wr.advance();
     }
   } else if (warp == ROWS_MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer (converged warp, elected lane issues)
@@ -230,21 +253,21 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
     const bool single = (p.dbg & 2) != 0;
     int s = 0, go = 0;
     uint32_t acc = tmem;
+    RingPos<ROWS_X_STAGES> xr;
+    RingPos<ROWS_W_SLOTS> wr;
     for (int g = 0; g < total; ++g) {
       const uint32_t st = p.steps[s];
       if (++s == nsteps) s = 0;
       const int fl = step_flags(st);
       if (fl & TC_STEP_FIRST) {
-        if (go >= 2) mbar_wait(&bars.acc_free[go & 1], (uint32_t)(((go >> 1) - 1) & 1));
+        mbar_wait(&bars.acc_free[go & 1], (uint32_t)(((go >> 1) & 1) ^ 1));
         acc = tmem + (uint32_t)(go & 1) * ROWS_TG;
       }
-      const int ring = g & 3;
-      const uint32_t par = (uint32_t)((g >> 2) & 1);
-      mbar_wait(&bars.x_full[ring], par);
-      mbar_wait(&bars.w_full[ring], par);
+      mbar_wait(&bars.x_full[xr.idx], xr.phase);
+      mbar_wait(&bars.w_full[wr.idx], wr.phase);
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t wh = w_lo0 + (uint32_t)ring * W_SLOT, xh = x_lo0 + (uint32_t)ring * X_STAGE;
+        const uint32_t wh = w_lo0 + (uint32_t)wr.idx * W_SLOT, xh = x_lo0 + (uint32_t)xr.idx * X_STAGE;
         const uint32_t first = (fl & TC_STEP_FIRST) ? 0u : 1u;
         if (single) {
           umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh), idesc, first);
@@ -259,11 +282,13 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS), idesc, 1u);
           }
         }
-        umma_commit(&bars.w_free[ring]);
-        umma_commit(&bars.x_free[ring]);
+        umma_commit(&bars.w_free[wr.idx]);
+        umma_commit(&bars.x_free[xr.idx]);
         if (fl & TC_STEP_LAST) umma_commit(&bars.acc_full[go & 1]);
       }
       __syncwarp();
+      xr.advance();
+      wr.advance();
       if (fl & TC_STEP_LAST) ++go;
     }
   } else {
@@ -290,7 +315,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             if (jmax <= 0) break;
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
-            if (f < bt.n_valid) {
+            if (f < bt.n_valid && !(p.dbg & 16)) {
               if (ld_case == 640) rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax);
               else if (ld_case == 128) rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax);
               else rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax);
