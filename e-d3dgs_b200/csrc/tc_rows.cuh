@@ -40,7 +40,7 @@ constexpr int ROWS_X_STAGES = 3;
 constexpr int ROWS_X_STAGE_BYTES = ROWS_TG * 16 * 4 * 2;  // hi + lo of [256 x 16]
 constexpr int ROWS_W_SLOTS = 3;
 constexpr int ROWS_W_SLOT_BYTES = 128 * 16 * 4 * 2;       // hi + lo of [128 x 16]
-constexpr int ROWS_RAW_SLOTS = 4;                        // cp.async raw slabs in flight per stager thread
+constexpr int ROWS_RAW_SLOTS = 5;                        // cp.async raw slabs in flight per stager thread
 constexpr int ROWS_RAW_SLOT_BYTES = ROWS_TG * 16 * 4;
 constexpr size_t ROWS_SMEM_BYTES = (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES +
                                    (size_t)ROWS_RAW_SLOTS * ROWS_RAW_SLOT_BYTES;
@@ -51,11 +51,16 @@ struct RowsBars {
   uint64_t acc_full[2], acc_free[2];
 };
 
-// hi = rna_tf32(x), lo = x - hi (exact). The tensor core ignores the low 13 bits of lo, which
-// perturbs a product by < 2^-21 relative: below the fp32 rounding of the accumulation.
+// hi = x rounded to tf32 (round half away from zero on the bit pattern: two integer instructions,
+// where cvt.rna.tf32 costs four because of its NaN/Inf path), lo = x - hi (exact). The tensor core
+// ignores the low 13 bits of lo, which perturbs a product by < 2^-21 relative: below the fp32
+// rounding of the accumulation.
+__device__ __forceinline__ float tf32_round_bits(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
 __device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* lo) {
   float4 h;
-  h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
+  h.x = tf32_round_bits(x.x); h.y = tf32_round_bits(x.y); h.z = tf32_round_bits(x.z); h.w = tf32_round_bits(x.w);
   *hi = h;
   *lo = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
 }
@@ -310,9 +315,10 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
           const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
           const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
           for (int blk = par; blk < ROWS_TG / 32; blk += 2) {
-            const long g0 = tile * ROWS_TG + blk * 32;
+            long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
             if (jmax <= 0) break;
+            if (p.dbg & 64) g0 &= 16383;   // timing knob: outputs stay in an L2-resident window
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
             if (f < bt.n_valid && !(p.dbg & 16)) {

@@ -105,6 +105,7 @@ class _DeformFunction(torch.autograd.Function):
                     tau_c.data_ptr(), tau_f.data_ptr(), ctypes.byref(in_arr), ctypes.byref(sub_arr),
                     ctypes.byref(out_arr), ctypes.byref(coef), work.data_ptr(), nbytes, _lib.stream_handle()))
         ctx.cfg = cfg
+        ctx.set_materialize_grads(False)   # unused outputs arrive as None instead of N-sized zero tensors
         ctx.save_for_backward(t_c, table_c, emb_c, tau_c, tau_f, work, *pc, *pf)
         subs[4] = subs[4].view(N, 16, 3)
         outs[4] = outs[4].view(N, 16, 3)
@@ -132,7 +133,9 @@ class _DeformFunction(torch.autograd.Function):
         d_out = [prep(gouts[5 + h], h) for h in range(5)]
         gc = [torch.zeros_like(p) for p in pc]
         gf = [torch.zeros_like(p) for p in pf]
-        d_emb = torch.zeros(N, gemb, dtype=torch.float32, device=dev)
+        # the first stage that runs overwrites d_emb (accumulate flag), so it needs no zero fill
+        d_emb = (torch.empty if (N > 0 and (cfg["coarse"] or cfg["fine"])) else torch.zeros)(
+            N, gemb, dtype=torch.float32, device=dev)
         d_tau_c = torch.zeros(temb, dtype=torch.float32, device=dev)
         d_tau_f = torch.zeros(temb, dtype=torch.float32, device=dev)
         d_table = torch.zeros_like(table_c)

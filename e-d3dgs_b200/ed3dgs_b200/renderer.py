@@ -97,7 +97,9 @@ def render(viewpoint_camera, pc, pipe, bg_color, kernel_size, scaling_modifier=1
         sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center, prefiltered=False,
         debug=getattr(pipe, "debug", False), kernel_size=kernel_size, require_coord=require_coord,
         require_depth=require_depth)
-    time = torch.tensor(viewpoint_camera.time).to(means3D.device).repeat(means3D.shape[0], 1)
+    # the reference repeats the scalar to [N, 1] (gaussian_renderer/__init__.py:84); the network only reads
+    # element [0, 0], so one device-side element avoids a pageable H2D copy (a sync) and 4 MB of traffic
+    time = torch.full((1, 1), float(viewpoint_camera.time), dtype=torch.float32, device=means3D.device)
     rasterizer = GaussianRasterizer(raster_settings=raster_settings)
     means2D = screenspace_points
     opacity = pc._opacity

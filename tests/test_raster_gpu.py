@@ -43,7 +43,10 @@ def test_c2_scale_bit_exact_keys():
     rs, inp = pu.make_case(P=300_000, W=802, H=550)
     a = pu.run_product(rs, inp, pu.upstream_grads)
     b = pu.run_reference(rs, inp, pu.upstream_grads)
-    pu.assert_report(pu.compare(rs, a, b), rs)
+    b2 = pu.run_reference(rs, inp, pu.upstream_grads)
+    noise = pu.compare(rs, b2, b)
+    print("reference run-to-run:", {k: v for k, v in noise.items() if k.startswith("grad_") and "scale" not in k})
+    pu.assert_report(pu.compare(rs, a, b), rs, noise=noise)
 
 
 def test_empty_and_all_culled():
