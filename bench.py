@@ -145,14 +145,19 @@ def algorithmic_work(cfg, hyper, R, visible_frac, sort_passes):
     W = hyper.net_width
     heads = [True, not hyper.no_ds, not hyper.no_dr, not hyper.no_do, not hyper.no_dc]
     k_on = sum(k for k, on in zip((3, 3, 4, 1, 48), heads) if on)
-    per_stage = 2 * (hyper.gaussian_embedding_dim * W + sum(heads) * W * W + W * k_on)
     stages = (0 if hyper.no_coarse_deform else 1) + (0 if hyper.no_fine_deform else 1)
-    mlp_fwd = per_stage * stages * P
+    nh, ge, D = sum(heads), hyper.gaussian_embedding_dim, hyper.defor_depth
+    # Deformation network: HBM bytes per Gaussian per stage that the algorithm cannot avoid with
+    # activations kept in fp32 for the backward pass: every activation matrix is written once
+    # by its producer and read once by each consumer GEMM; weights (<= 0.6 MB) are L2-resident.
+    fwd_b = 4 * ((ge + W) + (D - 1) * 2 * W + (W + nh * W) + (nh * W + 2 * k_on))
+    dgrad_b = 4 * ((80 + 2 * nh * W) + (nh * W + 2 * W) + (D - 1) * 3 * W + (W + ge))
+    wgrad_b = 4 * ((80 + nh * W) + (W + nh * W) + (D - 1) * 2 * W + (ge + W))
     V = visible_frac
     return {
-        "tc_gemm_kernel<fwd>": ("tensor", mlp_fwd),
-        "tc_gemm_kernel<dgrad>": ("tensor", mlp_fwd),
-        "tc_gemm_kernel<wgrad>": ("tensor", mlp_fwd),
+        "tc_rows_kernel<fwd>": ("hbm", fwd_b * stages * P),
+        "tc_rows_kernel<dgrad>": ("hbm", dgrad_b * stages * P + (4 * ge * P if stages == 2 else 0)),
+        "tc_wgrad_kernel": ("hbm", wgrad_b * stages * P),
         "preprocess_fwd": ("hbm", P * (240 + 143 * V)),
         "scan_tiles": ("hbm", 8 * P),
         "emit_keys": ("hbm", 20 * P + 12 * R),

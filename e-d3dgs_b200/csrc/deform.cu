@@ -350,7 +350,6 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
                           float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
   const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
-  const int kslice = 1024;  // shorter tensor-core accumulation chains are measurably more accurate
   int act[5];
   const int na = active_heads(w, act);
 
@@ -359,40 +358,51 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       const int h = act[i];
       if (g->head_b2[h]) add_vec<<<1, 64, 0, stream>>>(g->head_b2[h], colsum + hHeadOff[h], hHeadDim[h]);
     }
-    // dW2_h[j][f] += sum_n G_h[n][j] * Rz_h[n][f]
-    TcArgs a = tc_args(5L * W, GW, W, N, 48, TC_EPI_ATOMIC_T);
-    a.k_per_cta = kslice;
-    int nb = 0;
-    for (int i = 0; i < na; ++i) {
-      const int h = act[i];
-      if (!g->head_w2[h]) continue;
-      a.b[nb++] = TcBatch{wk.Rz[s] + (long)i * W, G + hHeadOff[h], g->head_w2[h], nullptr, nullptr, nullptr,
-                          W, 0, hHeadDim[h], 0, 0, 1.f};
+    // dW2_h[j][f] += sum_n G_h[n][j] * Rz_h[n][f]: all 80 columns of G on the M side, the hidden
+    // activations of two heads side by side on the N side; only the (head rows x head columns) blocks
+    // of the product are kept.
+    WgArgs a{};
+    a.N = N;
+    for (int i0 = 0; i0 < na; i0 += 2) {
+      WgGroup& gr = a.g[a.ngroups];
+      gr.P = G; gr.ldp = GW; gr.pcols = GW;
+      gr.Q = wk.Rz[s] + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = (i0 + 1 < na ? 2 : 1) * W;
+      for (int i = i0; i < i0 + 2 && i < na; ++i) {
+        const int h = act[i];
+        if (!g->head_w2[h]) continue;
+        gr.seg[gr.nseg++] = WgSegment{g->head_w2[h], 1, (long)W, (i - i0) * W, W, hHeadOff[h], hHeadDim[h]};
+      }
+      if (gr.nseg > 0) ++a.ngroups;
+      else gr = WgGroup{};
     }
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, nullptr, stream));
+    TC_TRY(tc_wgrad_launch(a, stream));
   }
   {  // dZ_h = (G_h * W2_h) masked by Rz_h > 0
     TcArgs a = tc_args(GW, W, N, 0, W, TC_EPI_MASK);
     for (int i = 0; i < na; ++i) {
       const int h = act[i];
-      a.b[i] = TcBatch{G + hHeadOff[h], w->head_w2[h], wk.dZ + (long)i * W, nullptr, wk.Rz[s] + (long)i * W, nullptr,
-                       5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
+      a.b[i] = TcBatch{G + hHeadOff[h], w->head_w2[h], wk.dZ + (long)i * W, nullptr, wk.Rz[s] + (long)i * W,
+                       g ? g->head_b1[h] : nullptr, 5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
     }
     a.K = 48;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, wk.Wprep, stream));
   }
-  if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i] ; db1_h[o] += sum_n dZ_h[n][o]
-    TcArgs a = tc_args(5L * W, W, W, N, W + 16, TC_EPI_ATOMIC);
-    a.k_per_cta = kslice;
-    a.ones_col = W;
-    int nb = 0;
-    for (int i = 0; i < na; ++i) {
-      const int h = act[i];
-      if (!g->head_w1[h]) continue;
-      a.b[nb++] = TcBatch{wk.dZ + (long)i * W, wk.R[s][D - 1], g->head_w1[h], nullptr, nullptr, g->head_b1[h],
-                          W, 0, W, 0, 0, 1.f};
+  if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i]: trunk activations on the M side, two heads' dZ on the N side
+    WgArgs a{};
+    a.N = N;
+    for (int i0 = 0; i0 < na; i0 += 2) {
+      WgGroup& gr = a.g[a.ngroups];
+      gr.P = wk.R[s][D - 1]; gr.ldp = W; gr.pcols = W;
+      gr.Q = wk.dZ + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = (i0 + 1 < na ? 2 : 1) * W;
+      for (int i = i0; i < i0 + 2 && i < na; ++i) {
+        const int h = act[i];
+        if (!g->head_w1[h]) continue;
+        gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], (long)W, 1, (i - i0) * W, W, 0, W};
+      }
+      if (gr.nseg > 0) ++a.ngroups;
+      else gr = WgGroup{};
     }
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, nb, nullptr, stream));
+    TC_TRY(tc_wgrad_launch(a, stream));
   }
   // dR = (dZ[N, na*W] * W1_all[na*W, W]) masked by R > 0
   for (int i = 0; i < na; ++i)
@@ -400,34 +410,39 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
                            cudaMemcpyDeviceToDevice, stream));
   float* dh = wk.dH[0];
   float* dh_other = wk.dH[1];
+  // the bias gradient of trunk layer l is the column sum of dh at that layer (MASK epilogue);
+  // for layer 0 it is dc1, which also carries the temporal half of the first Linear
+  TC_TRY(cudaMemsetAsync(wk.dc1, 0, W * sizeof(float), stream));
+  auto trunk_bias_grad = [&](int l) -> float* { return l == 0 ? wk.dc1 : (g ? g->feat_b[l] : nullptr); };
   {
     TcArgs a = tc_args(5L * W, W, N, na * W, W, TC_EPI_MASK);
-    a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], nullptr, W, W, W, 0, 0, 1.f};
+    a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], trunk_bias_grad(D - 1), W, W, W, 0, 0, 1.f};
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
   }
   for (int l = D - 1; l >= 1; --l) {
-    if (g && g->feat_w[l]) {
-      TcArgs a = tc_args(W, W, W, N, W + 16, TC_EPI_ATOMIC);
-      a.k_per_cta = kslice;
-      a.ones_col = W;
-      a.b[0] = TcBatch{dh, wk.R[s][l - 1], g->feat_w[l], nullptr, nullptr, g->feat_b[l], W, 0, W, 0, 0, 1.f};
-      TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, nullptr, stream));
+    if (g && g->feat_w[l]) {  // dW_l[o][i] += sum_n dh[n][o] * R_{l-1}[n][i]
+      WgArgs a{};
+      a.N = N; a.ngroups = 1;
+      a.g[0].P = wk.R[s][l - 1]; a.g[0].ldp = W; a.g[0].pcols = W;
+      a.g[0].Q = dh; a.g[0].ldq = W; a.g[0].qcols = W;
+      a.g[0].nseg = 1;
+      a.g[0].seg[0] = WgSegment{g->feat_w[l], (long)W, 1, 0, W, 0, W};
+      TC_TRY(tc_wgrad_launch(a, stream));
     }
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_MASK);
-    a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], nullptr, W, W, W, 0, 0, 1.f};
+    a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], trunk_bias_grad(l - 1), W, W, W, 0, 0, 1.f};
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
     float* t = dh; dh = dh_other; dh_other = t;
   }
-  // layer 0: weight gradient of the embedding columns + dc1 (ones column), then dE
-  TC_TRY(cudaMemsetAsync(wk.dc1, 0, W * sizeof(float), stream));
-  {
-    TcArgs a = tc_args(W, gemb, W, N, gemb + 16, TC_EPI_ATOMIC);
-    a.k_per_cta = kslice;
-    a.ones_col = gemb;
-    float* dW0e = (g && g->feat_w[0]) ? g->feat_w[0] + temb : nullptr;
-    // without a weight-gradient target only the ones column (dc1) is kept: n_valid = 0
-    a.b[0] = TcBatch{dh, emb, dW0e ? dW0e : wk.dc1, nullptr, nullptr, wk.dc1, ld0, 0, dW0e ? gemb : 0, 0, 0, 1.f};
-    TC_TRY(tc_launch(TC_MN_MAJOR, TC_MN_MAJOR, a, 1, nullptr, stream));
+  // layer 0: weight gradient of the embedding columns, then dE (dc1 came from the MASK epilogue above)
+  if (g && g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dh[n][o] * emb[n][i]
+    WgArgs a{};
+    a.N = N; a.ngroups = 1;
+    a.g[0].P = emb; a.g[0].ldp = gemb; a.g[0].pcols = gemb;
+    a.g[0].Q = dh; a.g[0].ldq = W; a.g[0].qcols = W;
+    a.g[0].nseg = 1;
+    a.g[0].seg[0] = WgSegment{g->feat_w[0] + temb, ld0, 1, 0, W, 0, gemb};
+    TC_TRY(tc_wgrad_launch(a, stream));
   }
   {
     TcArgs a = tc_args(W, ld0, N, W, gemb, TC_EPI_ACCUM);
@@ -578,6 +593,18 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
 int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, const float* A, long lda,
                         const float* B, long ldb, float* C, long ldc, int k_per_cta, int ones_col,
                         float* bias_grad, int epilogue, int dbg, void* stream) {
+  if (amaj == TC_MN_MAJOR) {
+    // weight-gradient form: A stored [K][lda] (P side, M columns), B stored [K][ldb] (Q side, n_valid columns)
+    WgArgs wa{};
+    wa.N = K; wa.ngroups = 1; wa.dbg = dbg;
+    wa.g[0].P = A; wa.g[0].ldp = lda; wa.g[0].pcols = (M + 3) / 4 * 4;
+    wa.g[0].Q = B; wa.g[0].ldq = ldb; wa.g[0].qcols = (n_valid + 3) / 4 * 4;
+    wa.g[0].nseg = 1;
+    wa.g[0].seg[0] = (epilogue == TC_EPI_ATOMIC_T) ? WgSegment{C, ldc, 1, 0, n_valid, 0, M} : WgSegment{C, 1, ldc, 0, n_valid, 0, M};
+    const cudaError_t e = tc_wgrad_launch(wa, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) { set_error("tc_wgrad launch failed: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
+    return ED3DGS_OK;
+  }
   TcArgs a{};
   a.b[0] = TcBatch{A, B, C, nullptr, nullptr, bias_grad, ldc, 0, n_valid, 0, 0, 1.f};
   a.lda = lda; a.ldb = ldb;

@@ -4,6 +4,7 @@
 #pragma once
 #include "tc_gemm.cuh"
 #include "tc_rows.cuh"
+#include "tc_wgrad.cuh"
 #include "profiler.h"
 
 namespace ed3dgs {
@@ -74,6 +75,29 @@ inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stre
   return cudaGetLastError();
 }
 
+// Weight gradients: D = P^T Q over all Gaussians, scattered into the gradient matrices (tc_wgrad.cuh).
+inline cudaError_t tc_wgrad_launch(const WgArgs& a, cudaStream_t stream) {
+  if (a.ngroups <= 0 || a.N <= 0) return cudaSuccess;
+  if (a.ngroups > WG_MAX_GROUPS) return cudaErrorInvalidValue;
+  for (int i = 0; i < a.ngroups; ++i) {
+    const WgGroup& g = a.g[i];
+    if (g.pcols <= 0 || g.pcols > 128 || (g.pcols & 3) || g.qcols <= 0 || g.qcols > 256 || (g.qcols & 3) ||
+        (g.ldp & 3) || (g.ldq & 3) || g.nseg < 0 || g.nseg > 2)
+      return cudaErrorInvalidValue;
+  }
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const int items = ((a.N + WG_SLICE - 1) / WG_SLICE) * a.ngroups;
+  const int grid = items < tc_sm_count() ? items : tc_sm_count();
+  ProfScope ps("tc_wgrad_kernel", stream);
+  tc_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(a);
+  return cudaGetLastError();
+}
+
 inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch, float* prep_scratch,
                              cudaStream_t stream) {
   if (nbatch <= 0) return cudaSuccess;
@@ -99,7 +123,7 @@ inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch,
       if (bmaj == TC_K_MAJOR) tc_prepare_b<TC_K_MAJOR><<<pg, 256, 0, stream>>>(a, reinterpret_cast<float4*>(prep_scratch), stride_f4);
       else tc_prepare_b<TC_MN_MAJOR><<<pg, 256, 0, stream>>>(a, reinterpret_cast<float4*>(prep_scratch), stride_f4);
     }
-    const char* name = (bmaj == TC_MN_MAJOR) ? "tc_gemm_kernel<dgrad>" : "tc_gemm_kernel<fwd>";
+    const char* name = (bmaj == TC_MN_MAJOR) ? "tc_rows_kernel<dgrad>" : "tc_rows_kernel<fwd>";
     return tc_rows_launch(a, name, stream);
   }
   if (bmaj != TC_MN_MAJOR) return cudaErrorInvalidValue;

@@ -68,12 +68,14 @@ __device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* l
 // Epilogue of one block of 32 Gaussians for this lane's feature: v[j] = D^T[f][g0 + j].
 // LD > 0: compile-time row stride of C (and of aux), so every access is base + immediate.
 // FULL: all 32 Gaussians of the block exist (no per-row predicate).
+// Returns the sum of the values it stored (MASK only: the bias gradient of the layer below).
 template <int LD, bool FULL>
-__device__ __forceinline__ void rows_epilogue_block(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
+__device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
                                                     int jmax) {
   const long ldc = LD ? LD : bt.ldc;
   const long ldx = LD ? LD : bt.ldaux;
   float* dst = bt.C + g0 * ldc + f;
+  float csum = 0.f;
   if (p.epilogue == TC_EPI_BIAS_ACT) {
     const float b = bt.bias != nullptr ? __ldg(bt.bias + f) : 0.f;
     if (p.relu) {
@@ -100,8 +102,10 @@ __device__ __forceinline__ void rows_epilogue_block(const TcArgs& p, const TcBat
     }
     if (p.epilogue == TC_EPI_MASK) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (FULL || j < jmax) dst[j * ldc] = o[j] > 0.f ? v[j] : 0.f;
+      for (int j = 0; j < 32; ++j) {
+        const float r = o[j] > 0.f ? v[j] : 0.f;
+        if (FULL || j < jmax) { dst[j * ldc] = r; csum += r; }
+      }
     } else if (p.epilogue == TC_EPI_ACCUM) {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
@@ -113,13 +117,14 @@ __device__ __forceinline__ void rows_epilogue_block(const TcArgs& p, const TcBat
         if (FULL || j < jmax) dst[j * ldc] = o[j] + (v[j] + b) * bt.scale;
     }
   }
+  return csum;
 }
 
 template <int LD>
-__device__ __forceinline__ void rows_epilogue_dispatch(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
-                                                       int jmax) {
-  if (jmax == 32) rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32);
-  else rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax);
+__device__ __forceinline__ float rows_epilogue_dispatch(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
+                                                        int jmax) {
+  if (jmax == 32) return rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32);
+  return rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax);
 }
 
 // Step word (TcArgs::steps): batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
@@ -314,6 +319,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
         if (q * 32 < bt.n_valid) {
           const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
           const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
+          float colsum = 0.f;
           for (int blk = par; blk < ROWS_TG / 32; blk += 2) {
             long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
@@ -322,11 +328,13 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
             if (f < bt.n_valid && !(p.dbg & 16)) {
-              if (ld_case == 640) rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax);
-              else if (ld_case == 128) rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax);
-              else rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax);
+              if (ld_case == 640) colsum += rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax);
+              else if (ld_case == 128) colsum += rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax);
+              else colsum += rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax);
             }
           }
+          // column sums of a masked gradient = bias gradient of the layer that produced the mask
+          if (p.epilogue == TC_EPI_MASK && bt.bias_grad != nullptr && f < bt.n_valid) atomicAdd(bt.bias_grad + f, colsum);
         }
         tc_fence_before();
         mbar_arrive(&bars.acc_free[buf]);

@@ -63,8 +63,8 @@ def main():
         ("KMN 256x128x48", dict(amaj=0, bmaj=1, M=256, n_valid=128, NT=128, K=48)),
         ("KMN 1000x32x128", dict(amaj=0, bmaj=1, M=1000, n_valid=32, NT=32, K=128)),
         ("KMN 512x128x640", dict(amaj=0, bmaj=1, M=512, n_valid=128, NT=128, K=640)),
-        ("MNMN 128x128 K=5000", dict(amaj=1, bmaj=1, M=128, n_valid=128, NT=144, K=5000, k_per_cta=2048, ones_col=128, epilogue=4)),
-        ("MNMN 128x32 K=3000 T", dict(amaj=1, bmaj=1, M=128, n_valid=32, NT=48, K=3000, k_per_cta=1024, ones_col=32, epilogue=5)),
+        ("MNMN 128x128 K=5000", dict(amaj=1, bmaj=1, M=128, n_valid=128, NT=144, K=5000, k_per_cta=2048, epilogue=4)),
+        ("MNMN 128x32 K=3000 T", dict(amaj=1, bmaj=1, M=128, n_valid=32, NT=48, K=3000, k_per_cta=1024, epilogue=5)),
         ("MNMN 128x8 K=777", dict(amaj=1, bmaj=1, M=128, n_valid=8, NT=16, K=777, k_per_cta=512, epilogue=5)),
     ]
     for dbg in (0, 1, 2):
