@@ -5,8 +5,8 @@
 //    (deformation.py:65 `.repeat`), so layer 0 is  E[N,32] * W0[:,256:]^T + (W0[:,:256] * tau + b0):
 //    per-Gaussian K drops from 288 to 32 and the [N,288] concat is never materialised.
 //  * All GEMMs (forward, input-gradient, weight-gradient) run through one tcgen05/TMEM building
-//    block (tc_gemm.cuh) with bias / ReLU / ReLU-mask / head-update epilogues fused in.
-//  * Bias gradients ride along as a ones-column of the weight-gradient GEMMs.
+//    kernel pair (tc_rows.cuh, tc_wgrad.cuh) with bias / ReLU / ReLU-mask / head-update epilogues fused in.
+//  * Bias gradients are the column sums of the ReLU-masked gradients, accumulated in that epilogue.
 #include <cstdio>
 #include "raster_api.h"
 #include "tc_gemm.cuh"

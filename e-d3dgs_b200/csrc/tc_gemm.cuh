@@ -1,19 +1,13 @@
-// 3xTF32 tensor-core GEMM building block for the deformation network (sm_100a, tcgen05 + TMEM).
+// Shared pieces of the 3xTF32 tensor-core kernels of the deformation network (sm_100a, tcgen05 + TMEM):
+// argument structs, PTX wrappers (mbarrier, tcgen05, cp.async, bulk copies), UMMA descriptors and the
+// weight preparation kernel. The kernels themselves:
+//   tc_rows.cuh   D^T[f][g] = sum_k W[f][k] X[g][k]   forward layers and input gradients (256 Gaussians / tile)
+//   tc_wgrad.cuh  D[m][n]   = sum_g P[g][m] Q[g][n]   weight gradients (contraction over Gaussians)
 //
-//   D[128 x NT] (+)= A[128 x K] * B[NT x K]^T        per CTA, fp32 accumulate in tensor memory
-//
-// Every product is evaluated as  A_lo*B_hi + A_hi*B_lo + A_hi*B_hi  with hi = rna_tf32(x) and
-// lo = rna_tf32(x - hi), so the result carries ~22 mantissa bits per factor: fp32-grade, which
-// is what the reference computes (nn.Linear on cuBLAS SGEMM, TF32 off).
-//
-// Pipeline of one CTA (256 threads, 2 CTAs per SM):
-//   global --cp.async 16 B, 2-3 chunks ahead--> raw fp32 ring in shared memory
-//   raw ring --all threads: split hi/lo (+ transpose when the contraction index is the slow one
-//             in global memory)--> two UMMA operand stages (canonical no-swizzle K-major layout)
-//   one elected thread: 6 x tcgen05.mma.kind::tf32 per 16-wide K chunk, tcgen05.commit -> mbarrier
-//   epilogue: 8 warps read the accumulator from TMEM (tcgen05.ld 32x32b.x16), fused
-//             bias/ReLU | ReLU-mask | x += delta*coef | atomic weight-gradient (+ ones column = bias)
-// No transposed or split copy of any operand is ever written to HBM.
+// Every product is evaluated as  A_lo*B_hi + A_hi*B_lo + A_hi*B_hi  with hi = x rounded to tf32 and
+// lo = x - hi, so a result carries ~21 mantissa bits per factor and fp32 accumulation: fp32-grade,
+// which is what the reference computes (nn.Linear on cuBLAS SGEMM, TF32 off).
+// No transposed or split copy of an activation matrix is ever written to HBM.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -31,23 +25,20 @@ enum TcEpilogue : int {
   TC_EPI_MASK = 1,       // C = aux > 0 ? acc : 0                     (activation backward)
   TC_EPI_ACCUM = 2,      // C = (accumulate ? C : 0) + acc            (input gradient)
   TC_EPI_HEAD = 3,       // C = aux + (acc + bias) * scale            (deformation heads)
-  TC_EPI_ATOMIC = 4,     // C[m][n] += acc      (weight gradient, split over Gaussians)
-  TC_EPI_ATOMIC_T = 5,   // C[n][m] += acc      (weight gradient, transposed)
+  TC_EPI_ATOMIC = 4,     // test hook only: weight-gradient form, C[m][n] += acc
+  TC_EPI_ATOMIC_T = 5,   // test hook only: weight-gradient form, C[n][m] += acc
 };
 
 constexpr int TC_MAX_BATCH = 5;
 constexpr int TC_M = 128;        // rows per CTA = TMEM lanes
-#ifndef ED3DGS_TC_KC
-#define ED3DGS_TC_KC 16
+constexpr int TC_KC = 16;       // K elements per weight slab: two UMMA k-steps
+constexpr int TC_PC = TC_KC / 4; // 16-byte pieces per row of a slab
+// Where the generic->async proxy fence for stager-written operand stages is executed: by the MMA
+// warp after it acquired the stage (true) or by every stager thread before it arrives (false).
+#ifndef ED3DGS_FENCE_AT_CONSUMER
+#define ED3DGS_FENCE_AT_CONSUMER 0
 #endif
-constexpr int TC_KC = ED3DGS_TC_KC;   // K elements per pipeline chunk (8 or 16: one or two UMMA k-steps)
-constexpr int TC_PC = TC_KC / 4;      // 16-byte pieces per row of a chunk
-// K-major raw tile: 16-byte pieces XOR-swizzled inside a row so the conversion pass (8 consecutive
-// rows per quarter-warp) reads conflict-free.
-__device__ __forceinline__ int tc_raw_kmajor(int row, int c4) {
-  return row * TC_KC + ((c4 ^ ((row >> (TC_PC == 4 ? 1 : 2)) & (TC_PC - 1))) << 2);
-}
-constexpr int TC_THREADS = 256;
+constexpr bool FENCE_AT_CONSUMER = ED3DGS_FENCE_AT_CONSUMER != 0;
 
 struct TcBatch {
   const float* A;
@@ -55,7 +46,7 @@ struct TcBatch {
   float* C;
   const float* bias;     // BIAS_ACT / HEAD: [n]
   const float* aux;      // MASK: mask matrix; HEAD: base matrix
-  float* bias_grad;      // ATOMIC*: receives the ones-column sums ([m]), may be null
+  float* bias_grad;      // MASK: += column sums of the stored values ([n], bias gradient of the layer below); may be null
   long ldc, ldaux;
   int n_valid;           // columns of D that exist (rows of B)
   int K;                 // contraction length of this batch entry (0: TcArgs::K)
@@ -75,13 +66,13 @@ struct TcArgs {
   long lda, ldb;
   int M;          // K-major A: number of valid rows (Gaussians). MN-major A: valid rows of D (features)
   int K;          // contraction length (MN-major A: number of Gaussians)
-  int NT;         // tile width, multiple of 16, <= 256
-  int k_per_cta;  // MN-major A only: contraction slice per CTA
-  int nbatch;     // batch entries; blockIdx.x = tile * nbatch + batch (entries of a tile run adjacently -> L2 reuse of A)
+  int NT;         // rows of the prepared weight images (set by tc_launch: 128)
+  int k_per_cta;  // unused (test hook compatibility)
+  int nbatch;     // batch entries (heads) processed per tile, in order
   int epilogue;
   int relu;       // BIAS_ACT
   int accumulate; // ACCUM
-  int ones_col;   // MN-major B: column of D that sums A over the contraction (-1: none)
+  int ones_col;   // unused (test hook compatibility)
   int dbg;        // test hook: 2 = single pass (hi*hi only)
   // rows kernel programme (K-major A only)
   int nsteps, ntiles;
@@ -234,64 +225,6 @@ __device__ __forceinline__ void split_store(float4 x, float4* hi, float4* lo) {
   *lo = l;
 }
 
-// ---- stage 1: global -> raw ring (cp.async) ----------------------------------------------------
-// K-major source, tile [rows x 16k]: raw float index = row*16 + ((c4 ^ ((row>>1)&3)) << 2)
-//   (16-byte pieces XOR-swizzled inside the 64-byte row so the conversion pass reads conflict-free)
-// MN-major source, tile [16k x rows]: raw float index = kl*rows + row  (straight lines)
-// ROWS_T > 0 makes the tile height a compile-time constant (no integer divisions, loops unrolled).
-template <int MAJ, int ROWS_T>
-__device__ __forceinline__ void raw_issue(float* raw, const float* __restrict__ src, long ld, int rows_rt,
-                                          int rows_valid, int k0, int kend) {
-  const int rows = ROWS_T ? ROWS_T : rows_rt;
-  if (MAJ == TC_K_MAJOR) {
-    const int total = rows * TC_PC;
-#pragma unroll
-    for (int q = threadIdx.x; q < total; q += TC_THREADS) {
-      const int row = q / TC_PC, c4 = q % TC_PC;
-      const int k = k0 + c4 * 4;
-      const bool ok = row < rows_valid && k < kend;
-      const float* s = ok ? (src + (long)row * ld + k) : src;
-      cp_async16_zfill(raw + tc_raw_kmajor(row, c4), s, ok ? 16 : 0);
-    }
-  } else {
-    const int groups = rows >> 2;
-    const int total = TC_KC * groups;
-#pragma unroll
-    for (int q = threadIdx.x; q < total; q += TC_THREADS) {
-      const int kl = q / groups, g = q - kl * groups;
-      const int k = k0 + kl;
-      const bool ok = k < kend && g * 4 < rows_valid;
-      const float* s = ok ? (src + (long)k * ld + g * 4) : src;
-      cp_async16_zfill(raw + kl * rows + g * 4, s, ok ? 16 : 0);
-    }
-  }
-}
-
-// ---- stage 2: raw ring -> UMMA operand stage (hi / lo), K-major tile ----------------------------
-// UMMA tile [rows x 16k]: float4 index = (k/4) * rows + row -> LBO (next K chunk) = rows*16 B, SBO = 128 B.
-template <int MAJ, int ROWS_T>
-__device__ __forceinline__ void raw_convert(const float* raw, int rows_rt, int k0, int kend, int ones_row, float4* hi,
-                                            float4* lo) {
-  const int rows = ROWS_T ? ROWS_T : rows_rt;
-  const int total = rows * TC_PC;
-#pragma unroll
-  for (int q = threadIdx.x; q < total; q += TC_THREADS) {
-    const int c4 = q / rows, row = q - c4 * rows;
-    float4 x;
-    if (MAJ == TC_K_MAJOR) {
-      x = *reinterpret_cast<const float4*>(raw + tc_raw_kmajor(row, c4));
-    } else {
-      const float* r0 = raw + (c4 * 4) * rows + row;
-      x = make_float4(r0[0], r0[rows], r0[2 * rows], r0[3 * rows]);
-      if (row == ones_row) {
-        const int k = k0 + c4 * 4;
-        x = make_float4(k < kend ? 1.f : 0.f, k + 1 < kend ? 1.f : 0.f, k + 2 < kend ? 1.f : 0.f, k + 3 < kend ? 1.f : 0.f);
-      }
-    }
-    split_store(x, hi + q, lo + q);
-  }
-}
-
 // ---- weights: split once per launch into per-chunk UMMA images ---------------------------------
 // image of chunk c (NT*8 float4 = NT*128 B): [hi: (k/4)*NT + row][lo: same], so the GEMM CTAs copy
 // it into shared memory with plain 16-byte cp.async and never touch it with the ALU.
@@ -323,19 +256,5 @@ __global__ void __launch_bounds__(256) tc_prepare_b(const TcArgs p, float4* __re
   }
 }
 
-inline size_t tc_raw_stages(int NT) { return NT <= 128 ? 3 : 2; }
-// Shared memory of one CTA. bprep: B arrives as prepared images (ring of 3), A through a raw ring of 2.
-inline size_t tc_gemm_smem_bytes(int NT, bool bprep) {
-  if (bprep) {
-    return (size_t)2 * TC_M * TC_KC * sizeof(float)                 // raw A ring
-           + (size_t)2 * 2 * TC_M * (TC_KC / 4) * sizeof(float4)     // UMMA A stages (hi, lo)
-           + (size_t)3 * NT * (2 * TC_PC) * sizeof(float4);          // prepared-B ring
-  }
-  const size_t raw = tc_raw_stages(NT) * (size_t)(TC_M + NT) * TC_KC * sizeof(float);
-  const size_t umma = (size_t)2 * 2 * (TC_M + NT) * (TC_KC / 4) * sizeof(float4);
-  return raw + umma;
-}
-
 }  // namespace ed3dgs
 
-#include "tc_gemm_kernel.cuh"

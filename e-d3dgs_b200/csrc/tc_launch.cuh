@@ -13,21 +13,6 @@ namespace ed3dgs {
 // 5 heads x K=128 or one matrix with K=640, NT <= 128  ->  40 chunks x 128 x 8 float4
 inline size_t tc_prep_scratch_floats() { return (size_t)48 * 128 * 8 * 4; }
 
-template <int AMAJ, int BMAJ, int NT_T, bool BPREP>
-static cudaError_t tc_launch_t(const TcArgs& a, dim3 grid, const char* name, cudaStream_t stream) {
-  const size_t smem = tc_gemm_smem_bytes(a.NT, BPREP);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<AMAJ, BMAJ, NT_T, BPREP>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
-  ProfScope ps(name, stream);
-  tc_gemm_kernel<AMAJ, BMAJ, NT_T, BPREP><<<grid, TC_THREADS, smem, stream>>>(a);
-  return cudaGetLastError();
-}
-
 // Programme of one tile of 256 Gaussians for tc_rows_kernel: the 16-wide K slabs of every batch
 // entry in order, with the flags that open and close an accumulation.
 inline bool tc_rows_build(TcArgs& a) {
@@ -103,11 +88,7 @@ inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch,
   if (nbatch <= 0) return cudaSuccess;
   TcArgs a = a_in;
   a.nbatch = nbatch;
-  unsigned tiles;
-  if (amaj == TC_K_MAJOR) tiles = (a.M + TC_M - 1) / TC_M;
-  else tiles = (a.K + a.k_per_cta - 1) / a.k_per_cta;
-  if (tiles == 0) return cudaSuccess;
-  const dim3 grid(tiles * (unsigned)nbatch, 1, 1);  // batch entries of one tile are adjacent blocks
+  if (a.M <= 0) return cudaSuccess;
   if (amaj == TC_K_MAJOR) {
     // weights: split once into per-slab hi/lo images of 128 rows (rows >= n_valid are zero)
     a.NT = 128;
@@ -126,13 +107,7 @@ inline cudaError_t tc_launch(int amaj, int bmaj, const TcArgs& a_in, int nbatch,
     const char* name = (bmaj == TC_MN_MAJOR) ? "tc_rows_kernel<dgrad>" : "tc_rows_kernel<fwd>";
     return tc_rows_launch(a, name, stream);
   }
-  if (bmaj != TC_MN_MAJOR) return cudaErrorInvalidValue;
-  const char* name = "tc_gemm_kernel<wgrad>";
-  switch (a.NT) {
-    case 144: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 144, false>(a, grid, name, stream);
-    case 48: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 48, false>(a, grid, name, stream);
-    default: return tc_launch_t<TC_MN_MAJOR, TC_MN_MAJOR, 0, false>(a, grid, name, stream);
-  }
+  return cudaErrorInvalidValue;   // weight gradients go through tc_wgrad_launch
 }
 
 }  // namespace ed3dgs

@@ -13,18 +13,21 @@
 // list of 16-wide K slabs built on the host (TcArgs::steps, tc_launch.cuh). Four roles run that
 // list concurrently and meet only through mbarriers:
 //
-//   warps 10-17 X stagers   global --ld.global.v4, 4 slabs ahead in registers--> split hi/lo -->
-//                           UMMA K-major operand stages (ring of 4 x [256 Gaussians x 16 k])
-//   warp 9      W loader    prepared hi/lo weight slabs (tc_prepare_b) --cp.async.bulk--> ring of 4
+//   warps 10-17 X stagers   global --cp.async 16 B, 4 slabs ahead--> raw ring (5 slabs, thread-private
+//                           pieces) --split hi/lo--> UMMA K-major operand stages (ring of 3 x [256 x 16 k])
+//   warp 9      W loader    prepared hi/lo weight slabs (tc_prepare_b) --cp.async.bulk--> ring of 3
 //   warp 8      MMA issuer  per slab: 2 k-steps x (W_lo*X_hi + W_hi*X_lo + W_hi*X_hi) tcgen05.mma;
 //                           tcgen05.commit releases the X stage / the W slot / the accumulator
 //   warps 0-7   epilogue    TMEM (2 accumulators of 256 columns, ping-pong) -> registers -> fused
-//                           bias/ReLU | ReLU-mask | accumulate | x + delta*coef -> global
+//                           bias/ReLU | ReLU-mask (+ column sums = bias gradient) | accumulate |
+//                           x + delta*coef -> global
 //
-// The SM is instruction-issue bound long before it is tensor bound (ncu: 18 warps, ~4400
-// warp-instructions per slab in the first version), so every role keeps its per-slab instruction
-// count small: descriptors are affine in the ring index, the step table is one 32-bit word per
-// slab, stagers keep running offsets, the epilogue is specialised on the row stride.
+// Measured limits (ncu, tests/gemm_time.py): with global traffic switched off a slab takes ~1260 clocks
+// against 768 clocks of UMMA time: the shared-memory pipe is saturated (UMMA operand reads 576
+// wavefronts + stager traffic ~650 per slab). The SM is also instruction-issue bound long before it is
+// tensor bound, so every role keeps its per-slab instruction count small: descriptors are affine in
+// the ring index, the step table is one 32-bit word per slab, stagers keep running offsets, the
+// epilogue is specialised on the row stride, waits and issues are warp-uniform with one elected lane.
 #pragma once
 
 namespace ed3dgs {
@@ -194,7 +197,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
     int frows = p.M - (int)blockIdx.x * ROWS_TG;       // rows of the tile that exist (may exceed 256)
     auto issue = [&]() {
       const uint32_t st = p.steps[fs];
-      const float* base = p.b[step_batch(st)].A + ftile_off + step_slab(st) * 16 + roff;
+      const float* base = p.b[step_batch(st)].A + ((p.dbg & 128) ? (ftile_off & 0xFFFFF) : ftile_off) + step_slab(st) * 16 + roff;   // knob 128: L2-resident window
       const bool piece_ok = piece < step_npieces(st) && !(p.dbg & 8);
       float4* dst = raw0 + fslot * (ROWS_RAW_SLOT_BYTES / 16);
 #pragma unroll
@@ -224,7 +227,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
       float4* lo = hi + 4 * ROWS_TG;
 #pragma unroll
       for (int i = 0; i < 4; ++i) split_store_fast(r[i], hi + 8 * i, lo + 8 * i);
-      fence_async_smem();
+      if (!FENCE_AT_CONSUMER) fence_async_smem();
       mbar_arrive(&bars.x_full[xr.idx]);
       xr.advance();
       if (++rslot == ROWS_RAW_SLOTS) rslot = 0;
@@ -276,6 +279,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
       mbar_wait(&bars.x_full[xr.idx], xr.phase);
       mbar_wait(&bars.w_full[wr.idx], wr.phase);
       tc_fence_after();
+        if (FENCE_AT_CONSUMER) fence_async_smem();   // generic-proxy stage writes (acquired above) -> async proxy
       if (elect_one()) {
         const uint32_t wh = w_lo0 + (uint32_t)wr.idx * W_SLOT, xh = x_lo0 + (uint32_t)xr.idx * X_STAGE;
         const uint32_t first = (fl & TC_STEP_FIRST) ? 0u : 1u;

@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
             else split_store_fast(x, qst + gq * 256 + (b - 1) * 128 + f, qst + 4 * 256 + gq * 256 + (b - 1) * 128 + f);
           }
         }
-        fence_async_smem();
+        if (!FENCE_AT_CONSUMER) fence_async_smem();
         mbar_arrive(&bars.x_full[xr.idx]);
         xr.advance();
         if (++rslot == WG_RAW_SLOTS) rslot = 0;
@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
       for (int s = 0; s < nslab; ++s) {
         mbar_wait(&bars.x_full[xr.idx], xr.phase);
         tc_fence_after();
+        if (FENCE_AT_CONSUMER) fence_async_smem();   // generic-proxy stage writes (acquired above) -> async proxy
         if (elect_one()) {
           const uint32_t ph = p_lo0 + (uint32_t)xr.idx * P_STAGE, qh = q_lo0 + (uint32_t)xr.idx * Q_STAGE;
           const uint32_t first = s == 0 ? 0u : 1u;
