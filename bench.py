@@ -381,6 +381,16 @@ def run_ours(args, rank, local, world):
         rooflines[name] = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
                            "traffic": None, "ms_per_step": ms, "launches_per_step": launches[name],
                            "algorithmic_per_step": amount}
+    # DRAM traffic measured once with ncu --set full (profiles/r01_traffic.json), per launch like `achieved`
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            measured = json.load(f)["per_step_bytes"]
+        if args.workload == "C3":
+            for name, b in measured.items():
+                if name in rooflines:
+                    rooflines[name]["traffic"] = b / max(rooflines[name]["launches_per_step"], 1)
+    except (OSError, KeyError, ValueError):
+        pass
     dominant = max(rooflines, key=lambda k: rooflines[k]["ms_per_step"]) if rooflines else None
     roof = dict(rooflines[dominant], kernel=dominant, peak_source=peaks["source"]) if dominant else None
     if roof and roof["bound"] == "tensor":
