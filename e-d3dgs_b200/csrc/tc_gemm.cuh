@@ -9,6 +9,7 @@
 // which is what the reference computes (nn.Linear on cuBLAS SGEMM, TF32 off).
 // No transposed or split copy of an activation matrix is ever written to HBM.
 #pragma once
+#include <cuda.h>           // CUtensorMap (type only; the encoder is fetched through the runtime)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -77,6 +78,8 @@ struct TcArgs {
   // rows kernel programme (K-major A only)
   int nsteps, ntiles;
   uint32_t steps[TC_MAX_STEPS];   // batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
+  // one 2-D tensor map per batch entry: dims {K_b floats, M rows}, box {16, 256}, SWIZZLE_64B (tc_rows_launch)
+  alignas(64) CUtensorMap xmap[TC_MAX_BATCH];
 };
 
 // ---- raw PTX wrappers ------------------------------------------------------------------------

@@ -44,10 +44,46 @@ inline int tc_sm_count() {
   return sms;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda).
+typedef CUresult (*tc_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                       const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                       CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline tc_encode_tiled_fn tc_encode_tiled() {
+  static tc_encode_tiled_fn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<tc_encode_tiled_fn>(ptr);
+  }
+  return fn;
+}
+
 inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stream) {
   if ((a.lda & 3) || !tc_rows_build(a)) return cudaErrorInvalidValue;
   for (int i = 0; i < a.nbatch; ++i)
     if (a.b[i].n_valid > 128) return cudaErrorInvalidValue;
+  // Activation tiles come in by TMA: 256 rows x 16 columns, 64-byte swizzle = the UMMA's K-major SW64
+  // layout. Columns >= K_b and rows >= M are zero-filled by the unit.
+  tc_encode_tiled_fn enc = tc_encode_tiled();
+  if (!enc) return cudaErrorNotSupported;
+  for (int i = 0; i < a.nbatch; ++i) {
+    const int Ki = a.b[i].K > 0 ? a.b[i].K : a.K;
+    if (i > 0 && a.b[i].A == a.b[i - 1].A && Ki == (a.b[i - 1].K > 0 ? a.b[i - 1].K : a.K)) {
+      a.xmap[i] = a.xmap[i - 1];
+      continue;
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)Ki, (cuuint64_t)a.M};
+    const cuuint64_t strides[1] = {(cuuint64_t)a.lda * sizeof(float)};
+    const cuuint32_t box[2] = {16, (cuuint32_t)ROWS_TG};
+    const cuuint32_t estr[2] = {1, 1};
+    if ((reinterpret_cast<uintptr_t>(a.b[i].A) & 15) != 0) return cudaErrorInvalidValue;
+    const CUresult r = enc(&a.xmap[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(a.b[i].A), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM_BYTES);

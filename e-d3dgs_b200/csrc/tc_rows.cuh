@@ -36,36 +36,35 @@ constexpr int ROWS_TG = 256;                             // Gaussians per tile =
 constexpr int ROWS_EPI_WARPS = 8;                        // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int ROWS_MMA_WARP = 8;
 constexpr int ROWS_LOAD_WARP = 9;
-constexpr int ROWS_CONV_WARP0 = 10;                      // 8 warps
-constexpr int ROWS_CONV_THREADS = 256;
-constexpr int ROWS_THREADS = (ROWS_CONV_WARP0 + 8) * 32;
-constexpr int ROWS_X_STAGES = 3;
-constexpr int ROWS_X_STAGE_BYTES = ROWS_TG * 16 * 4 * 2;  // hi + lo of [256 x 16]
+constexpr int ROWS_CONV_WARP0 = 10;                      // 6 warps: 16 warps in all = 4 per SM sub-partition = 128 registers
+constexpr int ROWS_CONV_THREADS = 192;
+constexpr int ROWS_THREADS = ROWS_CONV_WARP0 * 32 + ROWS_CONV_THREADS;
+constexpr int ROWS_XH_SLOTS = 7;                         // raw activation slabs written by TMA = the hi operand
+constexpr int ROWS_XL_SLOTS = 4;                         // lo parts written by the stagers
+constexpr int ROWS_X_SLAB_BYTES = ROWS_TG * 16 * 4;      // [256 Gaussians][16 k] fp32, 64-byte rows, SWIZZLE_64B
 constexpr int ROWS_W_SLOTS = 3;
-constexpr int ROWS_W_SLOT_BYTES = 128 * 16 * 4 * 2;       // hi + lo of [128 x 16]
-constexpr int ROWS_RAW_SLOTS = 5;                        // cp.async raw slabs in flight per stager thread
-constexpr int ROWS_RAW_SLOT_BYTES = ROWS_TG * 16 * 4;
-constexpr size_t ROWS_SMEM_BYTES = (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES +
-                                   (size_t)ROWS_RAW_SLOTS * ROWS_RAW_SLOT_BYTES;
+constexpr int ROWS_W_SLOT_BYTES = 128 * 16 * 4 * 2;      // hi + lo of [128 x 16], no-swizzle K-major
+constexpr size_t ROWS_SMEM_BYTES = (size_t)(ROWS_XH_SLOTS + ROWS_XL_SLOTS) * ROWS_X_SLAB_BYTES +
+                                   (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES + 1024;   // + slack to align to 1024
 
 struct RowsBars {
-  uint64_t x_full[ROWS_X_STAGES], x_free[ROWS_X_STAGES];
+  uint64_t xh_full[ROWS_XH_SLOTS], xh_free[ROWS_XH_SLOTS];
+  uint64_t x_full[ROWS_XL_SLOTS], xl_free[ROWS_XL_SLOTS];
   uint64_t w_full[ROWS_W_SLOTS], w_free[ROWS_W_SLOTS];
   uint64_t acc_full[2], acc_free[2];
 };
 
-// hi = x rounded to tf32 (round half away from zero on the bit pattern: two integer instructions,
-// where cvt.rna.tf32 costs four because of its NaN/Inf path), lo = x - hi (exact). The tensor core
-// ignores the low 13 bits of lo, which perturbs a product by < 2^-21 relative: below the fp32
-// rounding of the accumulation.
-__device__ __forceinline__ float tf32_round_bits(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
-}
-__device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* lo) {
-  float4 h;
-  h.x = tf32_round_bits(x.x); h.y = tf32_round_bits(x.y); h.z = tf32_round_bits(x.z); h.w = tf32_round_bits(x.w);
-  *hi = h;
-  *lo = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+// The tensor core reads a raw fp32 word as tf32 by ignoring its low 13 bits, so the raw slab IS the
+// hi part (hi = trunc(x)) and only lo = x - trunc(x) has to be written. lo keeps 11 of its <= 13
+// significant bits: a product is perturbed by < 2^-20 relative (dropped lo*lo term included),
+// inside the rounding noise of an fp32 GEMM of this length (tests/gemm_check.py: 1.4e-6 at K = 128).
+__device__ __forceinline__ float4 split_lo(float4 x) {
+  float4 l;
+  l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+  l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+  l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+  l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+  return l;
 }
 
 // Epilogue of one block of 32 Gaussians for this lane's feature: v[j] = D^T[f][g0 + j].
@@ -150,19 +149,29 @@ struct RingPos {
   }
 };
 
+// 2-D TMA tile load (tensor map in kernel parameter space), completion on an mbarrier.
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+
 __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcArgs p) {
-  extern __shared__ __align__(128) unsigned char rows_smem[];
+  extern __shared__ __align__(128) unsigned char rows_smem_raw[];
   __shared__ RowsBars bars;
   __shared__ uint32_t s_tmem;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  unsigned char* sX = rows_smem;
-  unsigned char* sW = sX + (size_t)ROWS_X_STAGES * ROWS_X_STAGE_BYTES;
-  unsigned char* sRaw = sW + (size_t)ROWS_W_SLOTS * ROWS_W_SLOT_BYTES;
+  // SWIZZLE_64B patterns repeat every 512 bytes: the slabs must sit on that grid
+  unsigned char* sXh = rows_smem_raw + ((1024u - (smem_u32(rows_smem_raw) & 1023u)) & 1023u);
+  unsigned char* sXl = sXh + (size_t)ROWS_XH_SLOTS * ROWS_X_SLAB_BYTES;
+  unsigned char* sW = sXl + (size_t)ROWS_XL_SLOTS * ROWS_X_SLAB_BYTES;
 
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
-    for (int i = 0; i < ROWS_X_STAGES; ++i) { mbar_init(&bars.x_full[i], ROWS_CONV_THREADS); mbar_init(&bars.x_free[i], 1); }
+    for (int i = 0; i < ROWS_XH_SLOTS; ++i) { mbar_init(&bars.xh_full[i], 1); mbar_init(&bars.xh_free[i], 1); }
+    for (int i = 0; i < ROWS_XL_SLOTS; ++i) { mbar_init(&bars.x_full[i], ROWS_CONV_THREADS); mbar_init(&bars.xl_free[i], 1); }
     for (int i = 0; i < ROWS_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&bars.acc_full[i], 1); mbar_init(&bars.acc_free[i], ROWS_EPI_WARPS * 32); }
     fence_mbar_init();
@@ -178,95 +187,82 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
 
   if (warp >= ROWS_CONV_WARP0) {
     // ------------------------------------------------------------------ X stagers (256 threads)
-    // One slab = 256 Gaussians x 16 k = 1024 pieces of 16 bytes, 4 per thread: 8 consecutive lanes
-    // take 8 consecutive Gaussians of one piece (conflict-free 128-byte stores into the UMMA stage),
-    // the 4 lane groups of a warp take the 4 pieces of a row (64 contiguous bytes of global memory).
-    // A thread converts exactly the pieces it copied itself, so the raw ring needs no barrier: the
-    // per-thread cp.async group counter is the only synchronisation (register-staged loads share
-    // scoreboards and serialise on memory latency; measured, tests/gemm_time.py).
-    const int cw = warp - ROWS_CONV_WARP0;
-    const int piece = lane >> 3;
-    const int row0 = cw * 32 + (lane & 7);             // rows row0 + 8 i, i = 0..3
-    const long roff = (long)row0 * p.lda + piece * 4;  // float offset of (row0, piece) inside a tile slab
-    const long lda8 = 8 * p.lda;
-    const long tile_stride = (long)gridDim.x * ROWS_TG * p.lda;
-    float4* const raw0 = reinterpret_cast<float4*>(sRaw) + cw * 32 + lane;   // [slot][i][warp][lane]
-    // running position of the next slab to copy
-    int fs = 0, fslot = 0;
-    long ftile_off = (long)blockIdx.x * ROWS_TG * p.lda;
-    int frows = p.M - (int)blockIdx.x * ROWS_TG;       // rows of the tile that exist (may exceed 256)
-    auto issue = [&]() {
-      const uint32_t st = p.steps[fs];
-      const float* base = p.b[step_batch(st)].A + ((p.dbg & 128) ? (ftile_off & 0xFFFFF) : ftile_off) + step_slab(st) * 16 + roff;   // knob 128: L2-resident window
-      const bool piece_ok = piece < step_npieces(st) && !(p.dbg & 8);
-      float4* dst = raw0 + fslot * (ROWS_RAW_SLOT_BYTES / 16);
+    // TMA has dropped slab g (256 Gaussians x 16 k, 64-byte rows, 64B swizzle) into the hi ring; the
+    // stagers only add the lo part in the same layout. 16-byte chunk c of row r sits at
+    // r*64 + ((c ^ ((r >> 1) & 3)) << 4); 8 consecutive lanes take 8 consecutive rows of one chunk, which
+    // the swizzle spreads over all 32 banks.
+    const int ct = tid - ROWS_CONV_WARP0 * 32;
+    constexpr int NIT = (ROWS_TG * 4 + ROWS_CONV_THREADS - 1) / ROWS_CONV_THREADS;   // 16-byte chunks per thread
+    int off[NIT];                                      // float4 index inside a slab (-1: none)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const bool ok = piece_ok && row0 + 8 * i < frows;
-        cp_async16_zfill(dst + i * ROWS_CONV_THREADS, ok ? base + i * lda8 : base, ok ? 16 : 0);
-      }
-      if (++fs == nsteps) { fs = 0; ftile_off += tile_stride; frows -= (int)gridDim.x * ROWS_TG; }
-      if (++fslot == ROWS_RAW_SLOTS) fslot = 0;
-    };
-    for (int u = 0; u < ROWS_RAW_SLOTS; ++u) {
-      if (u < total) issue();
-      cp_async_commit_group();
+    for (int i = 0; i < NIT; ++i) {
+      const int q = ct + i * ROWS_CONV_THREADS;        // chunk q >> 8 of row q & 255: consecutive lanes, consecutive rows
+      const int r = q & (ROWS_TG - 1), c = q >> 8;
+      off[i] = (q < ROWS_TG * 4) ? r * 4 + (c ^ ((r >> 1) & 3)) : -1;
     }
-    float4* const hi0 = reinterpret_cast<float4*>(sX) + piece * ROWS_TG + row0;
-    RingPos<ROWS_X_STAGES> xr;
-    int rslot = 0;
+    const float4* const hi0 = reinterpret_cast<const float4*>(sXh);
+    float4* const lo0 = reinterpret_cast<float4*>(sXl);
+    RingPos<ROWS_XH_SLOTS> hr;
+    RingPos<ROWS_XL_SLOTS> lr;
     for (int g = 0; g < total; ++g) {
-      cp_async_wait_group<ROWS_RAW_SLOTS - 1>();        // this thread's pieces of slab g have landed
-      const float4* src = raw0 + rslot * (ROWS_RAW_SLOT_BYTES / 16);
-      float4 r[4];
+      mbar_wait(&bars.xh_full[hr.idx], hr.phase);       // TMA bytes of slab g have landed
+      const float4* src = hi0 + hr.idx * (ROWS_X_SLAB_BYTES / 16);
+      float4 r[NIT];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) r[i] = src[i * ROWS_CONV_THREADS];
-      mbar_wait(&bars.x_free[xr.idx], xr.phase ^ 1u);
-      tc_fence_after();
-      float4* hi = hi0 + xr.idx * (ROWS_X_STAGE_BYTES / 16);
-      float4* lo = hi + 4 * ROWS_TG;
+      for (int i = 0; i < NIT; ++i)
+        if (off[i] >= 0) r[i] = src[off[i]];
+      mbar_wait(&bars.xl_free[lr.idx], lr.phase ^ 1u);  // the UMMAs that read this lo slot are done
+      float4* lo = lo0 + lr.idx * (ROWS_X_SLAB_BYTES / 16);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) split_store_fast(r[i], hi + 8 * i, lo + 8 * i);
-      if (!FENCE_AT_CONSUMER) fence_async_smem();
-      mbar_arrive(&bars.x_full[xr.idx]);
-      xr.advance();
-      if (++rslot == ROWS_RAW_SLOTS) rslot = 0;
-      if (g + ROWS_RAW_SLOTS < total) issue();          // refills the raw slot just consumed
-      cp_async_commit_group();                          // always commit: keeps the group count uniform
+      for (int i = 0; i < NIT; ++i)
+        if (off[i] >= 0) lo[off[i]] = split_lo(r[i]);
+      fence_async_smem();
+      mbar_arrive(&bars.x_full[lr.idx]);
+      hr.advance();
+      lr.advance();
     }
-    cp_async_wait_group<0>();
   } else if (warp == ROWS_LOAD_WARP) {
-    // ------------------------------------------------------------------ W loader (converged warp, elected lane issues)
+    // ------------------------------------------------------------------ loader (converged warp, elected lane issues)
+    // per slab: one bulk copy of the prepared weight slab, one TMA tile of the activations
     int s = 0;
+    long tile_row = (long)blockIdx.x * ROWS_TG;
     RingPos<ROWS_W_SLOTS> wr;
+    RingPos<ROWS_XH_SLOTS> hr;
     for (int g = 0; g < total; ++g) {
       const uint32_t st = p.steps[s];
-      if (++s == nsteps) s = 0;
       mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
-      if ((p.dbg & 4) && g >= ROWS_W_SLOTS) {
-        if (elect_one()) mbar_arrive(&bars.w_full[wr.idx]);
-      } else if (elect_one()) {
+      mbar_wait(&bars.xh_free[hr.idx], hr.phase ^ 1u);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&bars.xh_full[hr.idx], ROWS_X_SLAB_BYTES);
+        tma_load_2d(sXh + (size_t)hr.idx * ROWS_X_SLAB_BYTES, &p.xmap[step_batch(st)], step_slab(st) * 16, (int)tile_row,
+                    &bars.xh_full[hr.idx]);
         mbar_arrive_expect_tx(&bars.w_full[wr.idx], ROWS_W_SLOT_BYTES);
         bulk_copy_g2s(sW + (size_t)wr.idx * ROWS_W_SLOT_BYTES, p.b[step_batch(st)].Bprep + (size_t)step_slab(st) * (128 * 8),
                       ROWS_W_SLOT_BYTES, &bars.w_full[wr.idx]);
       }
       __syncwarp();
       wr.advance();
+      hr.advance();
+      if (++s == nsteps) { s = 0; tile_row += (long)gridDim.x * ROWS_TG; }
     }
   } else if (warp == ROWS_MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer (converged warp, elected lane issues)
-    // Descriptors are affine in the ring index: low word = start address >> 4 | LBO >> 4 << 16,
-    // high word = SBO >> 4 | version.
+    // Descriptor low word = start address >> 4 | LBO >> 4 << 16, high word = SBO >> 4 | version | layout.
+    // W: no-swizzle K-major (LBO = 128 rows x 16 B between k-pieces, SBO = 128 B between 8-row groups).
+    // X: SWIZZLE_64B K-major (8-row atoms of 512 B -> SBO = 512 B; a k-step advances the start by 32 B).
     const uint32_t idesc = umma_idesc_tf32(128, ROWS_TG);
-    const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+    const uint32_t w_desc_hi = (128u >> 4) | (1u << 14);
+    const uint32_t x_desc_hi = (512u >> 4) | (1u << 14) | (4u << 29);
     const uint32_t w_lo0 = ((smem_u32(sW) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
-    const uint32_t x_lo0 = ((smem_u32(sX) & 0x3FFFFu) >> 4) | ((ROWS_TG * 16u >> 4) << 16);
+    const uint32_t xh_lo0 = ((smem_u32(sXh) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t xl_lo0 = ((smem_u32(sXl) & 0x3FFFFu) >> 4) | (1u << 16);
     constexpr uint32_t W_SLOT = ROWS_W_SLOT_BYTES >> 4, W_LO = W_SLOT / 2, W_KS = (2u * 128u * 16u) >> 4;
-    constexpr uint32_t X_STAGE = ROWS_X_STAGE_BYTES >> 4, X_LO = X_STAGE / 2, X_KS = (2u * ROWS_TG * 16u) >> 4;
+    constexpr uint32_t X_SLAB = ROWS_X_SLAB_BYTES >> 4, X_KS = 32u >> 4;
     const bool single = (p.dbg & 2) != 0;
     int s = 0, go = 0;
     uint32_t acc = tmem;
-    RingPos<ROWS_X_STAGES> xr;
+    RingPos<ROWS_XH_SLOTS> hr;
+    RingPos<ROWS_XL_SLOTS> xr;
     RingPos<ROWS_W_SLOTS> wr;
     for (int g = 0; g < total; ++g) {
       const uint32_t st = p.steps[s];
@@ -276,31 +272,33 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
         mbar_wait(&bars.acc_free[go & 1], (uint32_t)(((go >> 1) & 1) ^ 1));
         acc = tmem + (uint32_t)(go & 1) * ROWS_TG;
       }
-      mbar_wait(&bars.x_full[xr.idx], xr.phase);
+      mbar_wait(&bars.x_full[xr.idx], xr.phase);        // lo written (and the stagers saw the hi slab land)
       mbar_wait(&bars.w_full[wr.idx], wr.phase);
       tc_fence_after();
-        if (FENCE_AT_CONSUMER) fence_async_smem();   // generic-proxy stage writes (acquired above) -> async proxy
       if (elect_one()) {
-        const uint32_t wh = w_lo0 + (uint32_t)wr.idx * W_SLOT, xh = x_lo0 + (uint32_t)xr.idx * X_STAGE;
+        const uint32_t wh = w_lo0 + (uint32_t)wr.idx * W_SLOT;
+        const uint32_t xh = xh_lo0 + (uint32_t)hr.idx * X_SLAB, xl = xl_lo0 + (uint32_t)xr.idx * X_SLAB;
         const uint32_t first = (fl & TC_STEP_FIRST) ? 0u : 1u;
         if (single) {
-          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh), idesc, first);
-          if (step_nk(st) == 2) umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS), idesc, 1u);
+          umma_tf32(acc, desc64(w_desc_hi, wh), desc64(x_desc_hi, xh), idesc, first);
+          if (step_nk(st) == 2) umma_tf32(acc, desc64(w_desc_hi, wh + W_KS), desc64(x_desc_hi, xh + X_KS), idesc, 1u);
         } else {
-          umma_tf32(acc, desc64(desc_hi, wh + W_LO), desc64(desc_hi, xh), idesc, first);  // small terms first
-          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh + X_LO), idesc, 1u);
-          umma_tf32(acc, desc64(desc_hi, wh), desc64(desc_hi, xh), idesc, 1u);
+          umma_tf32(acc, desc64(w_desc_hi, wh + W_LO), desc64(x_desc_hi, xh), idesc, first);  // small terms first
+          umma_tf32(acc, desc64(w_desc_hi, wh), desc64(x_desc_hi, xl), idesc, 1u);
+          umma_tf32(acc, desc64(w_desc_hi, wh), desc64(x_desc_hi, xh), idesc, 1u);
           if (step_nk(st) == 2) {
-            umma_tf32(acc, desc64(desc_hi, wh + W_KS + W_LO), desc64(desc_hi, xh + X_KS), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS + X_LO), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, wh + W_KS), desc64(desc_hi, xh + X_KS), idesc, 1u);
+            umma_tf32(acc, desc64(w_desc_hi, wh + W_KS + W_LO), desc64(x_desc_hi, xh + X_KS), idesc, 1u);
+            umma_tf32(acc, desc64(w_desc_hi, wh + W_KS), desc64(x_desc_hi, xl + X_KS), idesc, 1u);
+            umma_tf32(acc, desc64(w_desc_hi, wh + W_KS), desc64(x_desc_hi, xh + X_KS), idesc, 1u);
           }
         }
         umma_commit(&bars.w_free[wr.idx]);
-        umma_commit(&bars.x_free[xr.idx]);
+        umma_commit(&bars.xl_free[xr.idx]);
+        umma_commit(&bars.xh_free[hr.idx]);
         if (fl & TC_STEP_LAST) umma_commit(&bars.acc_full[go & 1]);
       }
       __syncwarp();
+      hr.advance();
       xr.advance();
       wr.advance();
       if (fl & TC_STEP_LAST) ++go;

@@ -24,6 +24,19 @@
 
 namespace ed3dgs {
 
+// hi = x rounded to tf32 (round half away from zero on the bit pattern: two integer instructions,
+// where cvt.rna.tf32 costs four because of its NaN/Inf path), lo = x - hi (exact). The tensor core
+// ignores the low 13 bits of lo, which perturbs a product by < 2^-21 relative.
+__device__ __forceinline__ float tf32_round_bits(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+__device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* lo) {
+  float4 h;
+  h.x = tf32_round_bits(x.x); h.y = tf32_round_bits(x.y); h.z = tf32_round_bits(x.z); h.w = tf32_round_bits(x.w);
+  *hi = h;
+  *lo = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+}
+
 constexpr int WG_SLICE = 2048;                    // Gaussians per work item (tensor-core accumulation chain)
 constexpr int WG_MAX_GROUPS = 3;
 constexpr int WG_EPI_WARPS = 8;
