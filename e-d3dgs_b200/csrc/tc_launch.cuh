@@ -97,14 +97,31 @@ inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stre
 }
 
 // Weight gradients: D = P^T Q over all Gaussians, scattered into the gradient matrices (tc_wgrad.cuh).
-inline cudaError_t tc_wgrad_launch(const WgArgs& a, cudaStream_t stream) {
-  if (a.ngroups <= 0 || a.N <= 0) return cudaSuccess;
-  if (a.ngroups > WG_MAX_GROUPS) return cudaErrorInvalidValue;
+inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
+  if (a_in.ngroups <= 0 || a_in.N <= 0) return cudaSuccess;
+  if (a_in.ngroups > WG_MAX_GROUPS) return cudaErrorInvalidValue;
+  WgArgs a = a_in;
+  tc_encode_tiled_fn enc = tc_encode_tiled();
+  if (!enc) return cudaErrorNotSupported;
   for (int i = 0; i < a.ngroups; ++i) {
     const WgGroup& g = a.g[i];
     if (g.pcols <= 0 || g.pcols > 128 || (g.pcols & 3) || g.qcols <= 0 || g.qcols > 256 || (g.qcols & 3) ||
-        (g.ldp & 3) || (g.ldq & 3) || g.nseg < 0 || g.nseg > 2)
+        (g.ldp & 3) || (g.ldq & 3) || g.nseg < 0 || g.nseg > 2 || (reinterpret_cast<uintptr_t>(g.P) & 15) ||
+        (reinterpret_cast<uintptr_t>(g.Q) & 15))
       return cudaErrorInvalidValue;
+    // tiles of 32 features x 16 Gaussians, 32-byte chunks swizzled inside 128-byte rows = the UMMA's MN-major
+    // layout for 32-bit elements (SWIZZLE_128B_BASE32B);
+    // columns >= cols and rows >= N are zero-filled by the unit
+    const cuuint32_t box[2] = {32, 16};
+    const cuuint32_t estr[2] = {1, 1};
+    for (int side = 0; side < 2; ++side) {
+      const cuuint64_t dims[2] = {(cuuint64_t)(side ? g.qcols : g.pcols), (cuuint64_t)a.N};
+      const cuuint64_t strides[1] = {(cuuint64_t)(side ? g.ldq : g.ldp) * sizeof(float)};
+      const CUresult r = enc(side ? &a.qmap[i] : &a.pmap[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                             const_cast<float*>(side ? g.Q : g.P), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    }
   }
   static bool configured = false;
   if (!configured) {

@@ -3,55 +3,42 @@
 //
 //   D[m][n] = sum_g P[g][m] * Q[g][n]        m < 128 features of P (TMEM lanes), n < 256 features of Q
 //
-// P and Q are activation matrices stored [Gaussian][feature], i.e. the contraction index is the slow
-// one, and the UMMA wants it contiguous (K-major; MN-major tf32 descriptors without swizzle return
-// zeros on B200). The stagers therefore transpose on the way:
+// P and Q are activation matrices stored [Gaussian][feature]: the contraction index is the slow one,
+// i.e. both operands are MN-major for the UMMA. With the 128-byte / 32-byte-atom swizzle that layout is exactly
+// what a TMA tile of 32 features x 16 Gaussians produces (rows of 128 B, one per Gaussian, atoms of 4 rows),
+// so nothing is transposed and no thread touches the raw data except to derive the lo part:
 //
-//   global --cp.async 16 B, whole feature rows (512 B - 1 KB contiguous per Gaussian)--> raw ring [16 g][384]
-//   raw ring --4 x ld.shared.b32 down a column = one float4 of 4 Gaussians--> split hi/lo -->
-//            UMMA K-major stages P [128 x 16 g], Q [256 x 16 g]          (all accesses conflict-free)
+//   loader    global --TMA 2-D tiles {32 features, 16 Gaussians}, SWIZZLE_128B_ATOM_32B--> hi ring (raw fp32; the
+//             tensor core reads it as tf32 by ignoring the low 13 bits)
+//   stagers   hi slab --lo = x - trunc_tf32(x), same offsets--> lo ring
+//   MMA       per 16-Gaussian slab: 2 k-steps x (P_lo*Q_hi + P_hi*Q_lo + P_hi*Q_hi), N = 256 (two heads
+//             side by side keep the tensor pipe at full rate, see tc_rows.cuh)
+//   epilogue  TMEM (2 accumulators, ping-pong) -> red.global.add.f32 into the weight gradients, one
+//             flush per work item
 //
-// Work item = (slice of WG_SLICE Gaussians, group); a group is one (P, Q) pair, e.g. the trunk
-// activations against the pre-activation gradients of two heads side by side (N = 256 keeps the
-// tensor pipe at full rate, see tc_rows.cuh). One CTA per SM walks items blockIdx.x,
-// blockIdx.x + gridDim.x, ...; groups of a slice are adjacent so they share P through L2.
-//
-//   warps 9-16  stagers     as above, raw ring of 3 slabs, per-thread cp.async groups
-//   warp 8      MMA issuer  per 16-Gaussian slab: 2 k-steps x (P_lo*Q_hi + P_hi*Q_lo + P_hi*Q_hi)
-//   warps 0-7   epilogue    TMEM (2 accumulators, ping-pong) -> red.global.add.f32 into the weight
-//                           gradients; one flush per item, so atomics are ~1/128 of the old per-slice scheme
+// Work item = (slice of WG_SLICE Gaussians, group); a group is one (P, Q) pair. One CTA per SM walks
+// items blockIdx.x, blockIdx.x + gridDim.x, ...; groups of a slice are adjacent so they share P through L2.
+// (The first version transposed in the stagers -- cp.async rows, ld.shared.b32 columns -- because
+// MN-major tf32 descriptors of every other layout type return zeros; it was shared-memory and barrier bound.)
 #pragma once
 
 namespace ed3dgs {
 
-// hi = x rounded to tf32 (round half away from zero on the bit pattern: two integer instructions,
-// where cvt.rna.tf32 costs four because of its NaN/Inf path), lo = x - hi (exact). The tensor core
-// ignores the low 13 bits of lo, which perturbs a product by < 2^-21 relative.
-__device__ __forceinline__ float tf32_round_bits(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
-}
-__device__ __forceinline__ void split_store_fast(float4 x, float4* hi, float4* lo) {
-  float4 h;
-  h.x = tf32_round_bits(x.x); h.y = tf32_round_bits(x.y); h.z = tf32_round_bits(x.z); h.w = tf32_round_bits(x.w);
-  *hi = h;
-  *lo = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
-}
-
 constexpr int WG_SLICE = 2048;                    // Gaussians per work item (tensor-core accumulation chain)
 constexpr int WG_MAX_GROUPS = 3;
-constexpr int WG_EPI_WARPS = 8;
+constexpr int WG_EPI_WARPS = 8;                   // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int WG_MMA_WARP = 8;
-constexpr int WG_CONV_WARP0 = 9;
-constexpr int WG_CONV_THREADS = 256;
-constexpr int WG_THREADS = (WG_CONV_WARP0 + 8) * 32;
-constexpr int WG_STAGES = 3;
-constexpr int WG_P_STAGE_BYTES = 128 * 16 * 4 * 2;  // hi + lo of [128 features x 16 g]
-constexpr int WG_Q_STAGE_BYTES = 256 * 16 * 4 * 2;  // hi + lo of [256 features x 16 g]
-constexpr int WG_RAW_SLOTS = 3;
-constexpr int WG_RAW_LD = 384;                      // floats per Gaussian row of a raw slab: P 128 | Q 256
-constexpr int WG_RAW_SLOT_BYTES = 16 * WG_RAW_LD * 4;
-constexpr size_t WG_SMEM_BYTES =
-    (size_t)WG_STAGES * (WG_P_STAGE_BYTES + WG_Q_STAGE_BYTES) + (size_t)WG_RAW_SLOTS * WG_RAW_SLOT_BYTES;
+constexpr int WG_LOAD_WARP = 9;
+constexpr int WG_CONV_WARP0 = 10;                 // 6 warps: 16 warps in all = 128 registers
+constexpr int WG_CONV_THREADS = 192;
+constexpr int WG_THREADS = WG_CONV_WARP0 * 32 + WG_CONV_THREADS;
+constexpr int WG_BLOCK_BYTES = 16 * 128;          // one TMA tile: 16 Gaussians x 32 features
+constexpr int WG_P_BYTES = 4 * WG_BLOCK_BYTES;    // 128 features
+constexpr int WG_Q_BYTES = 8 * WG_BLOCK_BYTES;    // 256 features
+constexpr int WG_SLAB_BYTES = WG_P_BYTES + WG_Q_BYTES;
+constexpr int WG_HI_SLOTS = 5;
+constexpr int WG_LO_SLOTS = 4;
+constexpr size_t WG_SMEM_BYTES = (size_t)(WG_HI_SLOTS + WG_LO_SLOTS) * WG_SLAB_BYTES + 1024;   // + slack to align to 1024
 
 // Where a block of D goes: C[(n - n0) * ldn + (m - m0) * ldm] += D[m][n] for n0 <= n < n0 + ncnt,
 // m0 <= m < m0 + mcnt.
@@ -73,26 +60,36 @@ struct WgArgs {
   int ngroups;
   int N;            // Gaussians
   int dbg;          // 2 = single pass (hi*hi only)
+  // tensor maps of P and Q of every group: dims {cols, N}, box {32, 16}, SWIZZLE_128B_ATOM_32B (tc_wgrad_launch)
+  alignas(64) CUtensorMap pmap[WG_MAX_GROUPS];
+  alignas(64) CUtensorMap qmap[WG_MAX_GROUPS];
 };
 
 struct WgBars {
-  uint64_t x_full[WG_STAGES], x_free[WG_STAGES];
+  uint64_t hi_full[WG_HI_SLOTS], hi_free[WG_HI_SLOTS];
+  uint64_t x_full[WG_LO_SLOTS], lo_free[WG_LO_SLOTS];
   uint64_t acc_full[2], acc_free[2];
 };
 
+// UMMA instruction descriptor, kind::tf32, fp32 accumulate, both operands MN-major (bits 15 / 16).
+__device__ __forceinline__ uint32_t umma_idesc_tf32_mn(int M, int N) {
+  return umma_idesc_tf32(M, N) | (1u << 15) | (1u << 16);
+}
+
 __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_constant__ WgArgs p) {
-  extern __shared__ __align__(128) unsigned char wg_smem[];
+  extern __shared__ __align__(128) unsigned char wg_smem_raw[];
   __shared__ WgBars bars;
   __shared__ uint32_t s_tmem;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  unsigned char* sP = wg_smem;
-  unsigned char* sQ = sP + (size_t)WG_STAGES * WG_P_STAGE_BYTES;
-  unsigned char* sRaw = sQ + (size_t)WG_STAGES * WG_Q_STAGE_BYTES;
+  // 128-byte-swizzle atoms are 1024 bytes: the tiles must sit on that grid
+  unsigned char* sHi = wg_smem_raw + ((1024u - (smem_u32(wg_smem_raw) & 1023u)) & 1023u);
+  unsigned char* sLo = sHi + (size_t)WG_HI_SLOTS * WG_SLAB_BYTES;
 
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
-    for (int i = 0; i < WG_STAGES; ++i) { mbar_init(&bars.x_full[i], WG_CONV_THREADS); mbar_init(&bars.x_free[i], 1); }
+    for (int i = 0; i < WG_HI_SLOTS; ++i) { mbar_init(&bars.hi_full[i], 1); mbar_init(&bars.hi_free[i], 1); }
+    for (int i = 0; i < WG_LO_SLOTS; ++i) { mbar_init(&bars.x_full[i], WG_CONV_THREADS); mbar_init(&bars.lo_free[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&bars.acc_full[i], 1); mbar_init(&bars.acc_free[i], WG_EPI_WARPS * 32); }
     fence_mbar_init();
   }
@@ -116,120 +113,111 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
   };
 
   if (warp >= WG_CONV_WARP0) {
-    // ------------------------------------------------------------------ stagers (256 threads)
+    // ------------------------------------------------------------------ stagers (192 threads)
+    // lo = x - trunc_tf32(x), elementwise: same offsets in the lo slot, so the swizzle never shows
     const int ct = tid - WG_CONV_WARP0 * 32;
-    // copy mapping: Gaussian row ct / 16 of the slab, 16-byte chunks (ct % 16) + 16 i, i < 6:
-    //   chunks 0..31 = P columns, 32..95 = Q columns -> 256 contiguous bytes per half-warp
-    const int cg = ct >> 4, cw = ct & 15;
-    // convert mapping: feature ct % 128 of a 128-feature block, Gaussian quads ct / 128 and ct / 128 + 2
-    const int f = ct & 127, gq0 = ct >> 7;
-    float* const raw = reinterpret_cast<float*>(sRaw);
-
-    int ik = 0, is_ = 0, igroup = 0, inslab = 0, islot = 0;
-    long irow0 = 0;
-    if (my_items > 0) item_setup(0, igroup, irow0, inslab);
-    auto issue = [&]() {
-      const WgGroup& G = p.g[igroup];
-      const long grow = irow0 + is_ * 16 + cg;
-      const bool rok = grow < (long)p.N;
-      float* dst = raw + islot * (WG_RAW_SLOT_BYTES / 4) + cg * WG_RAW_LD;
-      const float* prow = G.P + grow * G.ldp;
-      const float* qrow = G.Q + grow * G.ldq;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        const int w = cw + 16 * i;
-        const int col = (i < 2) ? 4 * w : 4 * (w - 32);
-        const bool ok = rok && col < ((i < 2) ? G.pcols : G.qcols);
-        const float* src = (i < 2) ? prow + col : qrow + col;
-        cp_async16_zfill(dst + 4 * w, ok ? src : G.P, ok ? 16 : 0);
-      }
-      if (++islot == WG_RAW_SLOTS) islot = 0;
-      if (++is_ == inslab) {
-        is_ = 0;
-        if (++ik < my_items) item_setup(ik, igroup, irow0, inslab);
-      }
-    };
-    for (int u = 0; u < WG_RAW_SLOTS - 1; ++u) {
-      if (ik < my_items) issue();
-      cp_async_commit_group();
-    }
-    RingPos<WG_STAGES> xr;
-    int rslot = 0;
+    constexpr int NIT = (WG_SLAB_BYTES / 16 + WG_CONV_THREADS - 1) / WG_CONV_THREADS;
+    RingPos<WG_HI_SLOTS> hr;
+    RingPos<WG_LO_SLOTS> lr;
     for (int k = 0; k < my_items; ++k) {
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
-      const int nblk = 1 + ((p.g[group].qcols + 127) >> 7);
+      const int nchunks = (WG_P_BYTES + (p.g[group].qcols > 128 ? 8 : 4) * WG_BLOCK_BYTES) / 16;
       for (int s = 0; s < nslab; ++s) {
-        cp_async_wait_group<WG_RAW_SLOTS - 2>();        // this thread's pieces of the current slab landed
-        // The raw slab is read across threads (a column holds pieces copied by 4 different threads), so
-        // all stagers meet here: everybody's copies of this slab are visible, and everybody is done
-        // reading the previous slab, whose slot the next copy refills.
-        asm volatile("bar.sync 1, %0;" ::"n"(WG_CONV_THREADS) : "memory");
-        if (ik < my_items) issue();
-        cp_async_commit_group();                        // always commit: keeps the group count uniform
-        const float* src = raw + rslot * (WG_RAW_SLOT_BYTES / 4) + f;
-        mbar_wait(&bars.x_free[xr.idx], xr.phase ^ 1u);
-        tc_fence_after();
-        float4* pst = reinterpret_cast<float4*>(sP + (size_t)xr.idx * WG_P_STAGE_BYTES);
-        float4* qst = reinterpret_cast<float4*>(sQ + (size_t)xr.idx * WG_Q_STAGE_BYTES);
-        for (int b = 0; b < nblk; ++b) {
+        mbar_wait(&bars.hi_full[hr.idx], hr.phase);       // TMA bytes of this slab have landed
+        const float4* src = reinterpret_cast<const float4*>(sHi + (size_t)hr.idx * WG_SLAB_BYTES);
+        float4 r[NIT];
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            const int gq = gq0 + 2 * j;
-            const float* c0 = src + (4 * gq) * WG_RAW_LD + b * 128;
-            const float4 x = make_float4(c0[0], c0[WG_RAW_LD], c0[2 * WG_RAW_LD], c0[3 * WG_RAW_LD]);
-            if (b == 0) split_store_fast(x, pst + gq * 128 + f, pst + 4 * 128 + gq * 128 + f);
-            else split_store_fast(x, qst + gq * 256 + (b - 1) * 128 + f, qst + 4 * 256 + gq * 256 + (b - 1) * 128 + f);
-          }
+        for (int i = 0; i < NIT; ++i) {
+          const int q = ct + i * WG_CONV_THREADS;
+          if (q < nchunks) r[i] = src[q];
         }
-        if (!FENCE_AT_CONSUMER) fence_async_smem();
-        mbar_arrive(&bars.x_full[xr.idx]);
-        xr.advance();
-        if (++rslot == WG_RAW_SLOTS) rslot = 0;
+        mbar_wait(&bars.lo_free[lr.idx], lr.phase ^ 1u);  // the UMMAs that read this lo slot are done
+        float4* lo = reinterpret_cast<float4*>(sLo + (size_t)lr.idx * WG_SLAB_BYTES);
+#pragma unroll
+        for (int i = 0; i < NIT; ++i) {
+          const int q = ct + i * WG_CONV_THREADS;
+          if (q < nchunks) lo[q] = split_lo(r[i]);
+        }
+        fence_async_smem();
+        mbar_arrive(&bars.x_full[lr.idx]);
+        hr.advance();
+        lr.advance();
       }
     }
-    cp_async_wait_group<0>();
+  } else if (warp == WG_LOAD_WARP) {
+    // ------------------------------------------------------------------ loader (converged warp, elected lane issues)
+    RingPos<WG_HI_SLOTS> hr;
+    for (int k = 0; k < my_items; ++k) {
+      int group, nslab;
+      long row0;
+      item_setup(k, group, row0, nslab);
+      const int nqb = p.g[group].qcols > 128 ? 8 : 4;
+      const uint32_t bytes = (uint32_t)(WG_P_BYTES + nqb * WG_BLOCK_BYTES);
+      for (int s = 0; s < nslab; ++s) {
+        mbar_wait(&bars.hi_free[hr.idx], hr.phase ^ 1u);
+        if (elect_one()) {
+          uint64_t* bar = &bars.hi_full[hr.idx];
+          mbar_arrive_expect_tx(bar, bytes);
+          unsigned char* dst = sHi + (size_t)hr.idx * WG_SLAB_BYTES;
+          const int row = (int)row0 + s * 16;
+#pragma unroll
+          for (int b = 0; b < 4; ++b) tma_load_2d(dst + b * WG_BLOCK_BYTES, &p.pmap[group], 32 * b, row, bar);
+          for (int b = 0; b < nqb; ++b) tma_load_2d(dst + WG_P_BYTES + b * WG_BLOCK_BYTES, &p.qmap[group], 32 * b, row, bar);
+        }
+        __syncwarp();
+        hr.advance();
+      }
+    }
   } else if (warp == WG_MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer
-    const uint32_t desc_hi = (128u >> 4) | (1u << 14);
-    const uint32_t p_lo0 = ((smem_u32(sP) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
-    const uint32_t q_lo0 = ((smem_u32(sQ) & 0x3FFFFu) >> 4) | ((256u * 16u >> 4) << 16);
-    constexpr uint32_t P_STAGE = WG_P_STAGE_BYTES >> 4, P_LO = P_STAGE / 2, P_KS = (2u * 128u * 16u) >> 4;
-    constexpr uint32_t Q_STAGE = WG_Q_STAGE_BYTES >> 4, Q_LO = Q_STAGE / 2, Q_KS = (2u * 256u * 16u) >> 4;
+    // MN-major operands of 32-bit elements: only layout type 1 (SWIZZLE_128B_BASE32B: 32-byte chunks of a
+    // 128-byte row XORed with the row index & 3) produces non-zero products on B200; every other layout
+    // type returns zeros with the MN-major bits set (tests/probes/mn_probe.cu). A tile of 32 features is
+    // 16 rows of 128 B: SBO = 512 B to the next 4 Gaussians, LBO = 2048 B to the next 32 features,
+    // k-step (8 Gaussians) = +1024 B.
+    const uint32_t desc_hi = (512u >> 4) | (1u << 14) | (1u << 29);
+    const uint32_t lbo = (2048u >> 4) << 16;
+    const uint32_t hi0 = ((smem_u32(sHi) & 0x3FFFFu) >> 4) | lbo;
+    const uint32_t lo0 = ((smem_u32(sLo) & 0x3FFFFu) >> 4) | lbo;
+    constexpr uint32_t SLAB = WG_SLAB_BYTES >> 4, QOFF = WG_P_BYTES >> 4, KS = 1024u >> 4;
     const bool single = (p.dbg & 2) != 0;
-    RingPos<WG_STAGES> xr;
+    RingPos<WG_HI_SLOTS> hr;
+    RingPos<WG_LO_SLOTS> lr;
     for (int k = 0; k < my_items; ++k) {
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
-      const uint32_t idesc = umma_idesc_tf32(128, p.g[group].qcols > 128 ? 256 : 128);
+      const uint32_t idesc = umma_idesc_tf32_mn(128, p.g[group].qcols > 128 ? 256 : 128);
       const int buf = k & 1;
       mbar_wait(&bars.acc_free[buf], (uint32_t)(((k >> 1) & 1) ^ 1));
       const uint32_t acc = tmem + (uint32_t)buf * 256u;
       for (int s = 0; s < nslab; ++s) {
-        mbar_wait(&bars.x_full[xr.idx], xr.phase);
+        mbar_wait(&bars.x_full[lr.idx], lr.phase);        // lo written (and the stagers saw the hi slab land)
         tc_fence_after();
-        if (FENCE_AT_CONSUMER) fence_async_smem();   // generic-proxy stage writes (acquired above) -> async proxy
         if (elect_one()) {
-          const uint32_t ph = p_lo0 + (uint32_t)xr.idx * P_STAGE, qh = q_lo0 + (uint32_t)xr.idx * Q_STAGE;
+          const uint32_t ph = hi0 + (uint32_t)hr.idx * SLAB, pl = lo0 + (uint32_t)lr.idx * SLAB;
+          const uint32_t qh = ph + QOFF, ql = pl + QOFF;
           const uint32_t first = s == 0 ? 0u : 1u;
           if (single) {
             umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, qh), idesc, first);
-            umma_tf32(acc, desc64(desc_hi, ph + P_KS), desc64(desc_hi, qh + Q_KS), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, qh + KS), idesc, 1u);
           } else {
-            umma_tf32(acc, desc64(desc_hi, ph + P_LO), desc64(desc_hi, qh), idesc, first);  // small terms first
-            umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, qh + Q_LO), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, pl), desc64(desc_hi, qh), idesc, first);  // small terms first
+            umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, ql), idesc, 1u);
             umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, qh), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph + P_KS + P_LO), desc64(desc_hi, qh + Q_KS), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph + P_KS), desc64(desc_hi, qh + Q_KS + Q_LO), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph + P_KS), desc64(desc_hi, qh + Q_KS), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, pl + KS), desc64(desc_hi, qh + KS), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, ql + KS), idesc, 1u);
+            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, qh + KS), idesc, 1u);
           }
-          umma_commit(&bars.x_free[xr.idx]);
+          umma_commit(&bars.lo_free[lr.idx]);
+          umma_commit(&bars.hi_free[hr.idx]);
           if (s == nslab - 1) umma_commit(&bars.acc_full[buf]);
         }
         __syncwarp();
-        xr.advance();
+        hr.advance();
+        lr.advance();
       }
     }
   } else {
