@@ -78,16 +78,39 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
   const long ldx = LD ? LD : bt.ldaux;
   float* dst = bt.C + g0 * ldc + f;
   float csum = 0.f;
+  const int lane = threadIdx.x & 31;
   if (p.epilogue == TC_EPI_BIAS_ACT) {
     const float b = bt.bias != nullptr ? __ldg(bt.bias + f) : 0.f;
     if (p.relu) {
+      if (bt.mask_out != nullptr) {
+        // sign bits of the 32 features of this warp, one word per Gaussian: the ReLU mask the backward
+        // pass reads instead of the fp32 activations (n_valid is a multiple of 32 here: full warps)
+        uint32_t word = 0;
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (FULL || j < jmax) dst[j * ldc] = fmaxf(v[j] + b, 0.f);
+        for (int j = 0; j < 32; ++j) {
+          const float x = fmaxf(v[j] + b, 0.f);
+          const uint32_t bits = __ballot_sync(0xffffffffu, x > 0.f);
+          if (lane == j) word = bits;
+          if (FULL || j < jmax) dst[j * ldc] = x;
+        }
+        if (FULL || lane < jmax) bt.mask_out[(long)(bt.mask_row + (f >> 5)) * bt.mask_ld + g0 + lane] = word;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (FULL || j < jmax) dst[j * ldc] = fmaxf(v[j] + b, 0.f);
+      }
     } else {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (FULL || j < jmax) dst[j * ldc] = v[j] + b;
+    }
+  } else if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr) {
+    const uint32_t word = bt.mask_in[(long)(bt.mask_row + (f >> 5)) * bt.mask_ld + g0 + (FULL ? lane : min(lane, jmax - 1))];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const uint32_t bits = __shfl_sync(0xffffffffu, word, j);
+      const float r = ((bits >> lane) & 1u) ? v[j] : 0.f;
+      if (FULL || j < jmax) { dst[j * ldc] = r; csum += r; }
     }
   } else {
     // the three other epilogues read one value per output first; a clamped row index keeps the
