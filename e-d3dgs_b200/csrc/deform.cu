@@ -236,10 +236,9 @@ struct DeformWork {
   float* c1[2];                          // [W]
   float* dc1;                            // [W]
   float* colsum[2];                      // [80]
-  // ReLU masks as bits (net width a multiple of 32): word (row * mask_ld + Gaussian), 32 features per word
-  uint32_t* Mr[2][ED3DGS_DEFORM_MAX_DEPTH];  // trunk layers: 4 rows each
-  uint32_t* Mz[2];                           // head hidden layers: 4 rows per head slot
-  long mask_ld;                              // 0: masks are read from the fp32 activations instead
+  // ReLU masks as bits: one word per (block of 32 Gaussians, feature)
+  uint32_t* Mr[2][ED3DGS_DEFORM_MAX_DEPTH];  // trunk layers: [ceil(N/32)][W]
+  uint32_t* Mz[2];                           // head hidden layers: [ceil(N/32)][5W]
 };
 
 static inline void carve_f(char*& p, float*& out, size_t count) {
@@ -257,14 +256,12 @@ static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
     carve_f(p, w.c1[s], W);
     carve_f(p, w.colsum[s], GW);
   }
-  w.mask_ld = (W % 32 == 0) ? (long)((N + 31) / 32 * 32) : 0;
-  if (w.mask_ld) {
-    for (int s = 0; s < 2; ++s) {
-      float* t;
-      for (int l = 0; l < depth; ++l) { carve_f(p, t, 4 * (size_t)w.mask_ld); w.Mr[s][l] = reinterpret_cast<uint32_t*>(t); }
-      carve_f(p, t, 20 * (size_t)w.mask_ld);
-      w.Mz[s] = reinterpret_cast<uint32_t*>(t);
-    }
+  const size_t nblk32 = (N + 31) / 32;
+  for (int s = 0; s < 2; ++s) {
+    float* t;
+    for (int l = 0; l < depth; ++l) { carve_f(p, t, nblk32 * W); w.Mr[s][l] = reinterpret_cast<uint32_t*>(t); }
+    carve_f(p, t, nblk32 * 5 * W);
+    w.Mz[s] = reinterpret_cast<uint32_t*>(t);
   }
   carve_f(p, w.dZ, N * 5 * W);
   carve_f(p, w.dH[0], N * W);
@@ -323,14 +320,14 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
     TcArgs a = tc_args(gemb, ld0, N, gemb, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
     a.b[0] = TcBatch{emb, w->feat_w[0] + temb, wk.R[s][0], wk.c1[s], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    if (wk.mask_ld) { a.b[0].mask_out = wk.Mr[s][0]; a.b[0].mask_ld = wk.mask_ld; a.b[0].mask_row = 0; }
+    a.b[0].mask_out = wk.Mr[s][0]; a.b[0].mask_ld = W;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
   }
   for (int l = 1; l < D; ++l) {
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
     a.b[0] = TcBatch{wk.R[s][l - 1], w->feat_w[l], wk.R[s][l], w->feat_b[l], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    if (wk.mask_ld) { a.b[0].mask_out = wk.Mr[s][l]; a.b[0].mask_ld = wk.mask_ld; a.b[0].mask_row = 0; }
+    a.b[0].mask_out = wk.Mr[s][l]; a.b[0].mask_ld = W;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
   }
   int act[5];
@@ -342,7 +339,7 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
       const int h = act[i];
       a.b[i] = TcBatch{wk.R[s][D - 1], w->head_w1[h], wk.Rz[s] + (long)i * W, w->head_b1[h], nullptr, nullptr,
                        5L * W, 0, W, 0, 0, 1.f};
-      if (wk.mask_ld) { a.b[i].mask_out = wk.Mz[s]; a.b[i].mask_ld = wk.mask_ld; a.b[i].mask_row = 4 * i; }
+      a.b[i].mask_out = wk.Mz[s]; a.b[i].mask_ld = 5L * W; a.b[i].mask_col = i * W;
     }
     TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
   }
@@ -399,7 +396,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       const int h = act[i];
       a.b[i] = TcBatch{G + hHeadOff[h], w->head_w2[h], wk.dZ + (long)i * W, nullptr, wk.Rz[s] + (long)i * W,
                        g ? g->head_b1[h] : nullptr, 5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
-      if (wk.mask_ld) { a.b[i].mask_in = wk.Mz[s]; a.b[i].mask_ld = wk.mask_ld; a.b[i].mask_row = 4 * i; }
+      a.b[i].mask_in = wk.Mz[s]; a.b[i].mask_ld = 5L * W; a.b[i].mask_col = i * W;
     }
     a.K = 48;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, wk.Wprep, stream));
@@ -434,7 +431,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   {
     TcArgs a = tc_args(5L * W, W, N, na * W, W, TC_EPI_MASK);
     a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], trunk_bias_grad(D - 1), W, W, W, 0, 0, 1.f};
-    if (wk.mask_ld) { a.b[0].mask_in = wk.Mr[s][D - 1]; a.b[0].mask_ld = wk.mask_ld; a.b[0].mask_row = 0; }
+    a.b[0].mask_in = wk.Mr[s][D - 1]; a.b[0].mask_ld = W;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
   }
   for (int l = D - 1; l >= 1; --l) {
@@ -449,7 +446,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     }
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_MASK);
     a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], trunk_bias_grad(l - 1), W, W, W, 0, 0, 1.f};
-    if (wk.mask_ld) { a.b[0].mask_in = wk.Mr[s][l - 1]; a.b[0].mask_ld = wk.mask_ld; a.b[0].mask_row = 0; }
+    a.b[0].mask_in = wk.Mr[s][l - 1]; a.b[0].mask_ld = W;
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
     float* t = dh; dh = dh_other; dh_other = t;
   }

@@ -54,11 +54,11 @@ struct TcBatch {
   int kb_valid;          // MN-major B: rows of B along k that exist (0: same as K)
   float scale;           // HEAD
   const float4* Bprep;   // set by tc_launch: per-chunk UMMA images of B (weights), see tc_prepare_b
-  // ReLU masks as bits, word (mask_row + feature / 32) * mask_ld + Gaussian, bit = feature % 32:
-  uint32_t* mask_out;        // BIAS_ACT + relu: written (n_valid must be a multiple of 32); may be null
+  // ReLU masks as bits: word [Gaussian / 32][mask_ld] at column mask_col + feature, bit = Gaussian % 32
+  uint32_t* mask_out;        // BIAS_ACT + relu: written; may be null
   const uint32_t* mask_in;   // MASK: read instead of aux when not null
   long mask_ld;
-  int mask_row;
+  int mask_col;
 };
 
 // Per-tile programme of the persistent rows kernel (tc_rows.cuh), built on the host by tc_launch:

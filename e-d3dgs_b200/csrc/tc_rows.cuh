@@ -78,22 +78,20 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
   const long ldx = LD ? LD : bt.ldaux;
   float* dst = bt.C + g0 * ldc + f;
   float csum = 0.f;
-  const int lane = threadIdx.x & 31;
   if (p.epilogue == TC_EPI_BIAS_ACT) {
     const float b = bt.bias != nullptr ? __ldg(bt.bias + f) : 0.f;
     if (p.relu) {
       if (bt.mask_out != nullptr) {
-        // sign bits of the 32 features of this warp, one word per Gaussian: the ReLU mask the backward
-        // pass reads instead of the fp32 activations (n_valid is a multiple of 32 here: full warps)
+        // sign bits of this feature for the 32 Gaussians of the block, one word per (block, feature): the
+        // ReLU mask the backward pass reads instead of the fp32 activations
         uint32_t word = 0;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const float x = fmaxf(v[j] + b, 0.f);
-          const uint32_t bits = __ballot_sync(0xffffffffu, x > 0.f);
-          if (lane == j) word = bits;
+          word |= (x > 0.f ? 1u : 0u) << j;
           if (FULL || j < jmax) dst[j * ldc] = x;
         }
-        if (FULL || lane < jmax) bt.mask_out[(long)(bt.mask_row + (f >> 5)) * bt.mask_ld + g0 + lane] = word;
+        bt.mask_out[(g0 >> 5) * bt.mask_ld + bt.mask_col + f] = word;
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
@@ -105,11 +103,10 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
         if (FULL || j < jmax) dst[j * ldc] = v[j] + b;
     }
   } else if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr) {
-    const uint32_t word = bt.mask_in[(long)(bt.mask_row + (f >> 5)) * bt.mask_ld + g0 + (FULL ? lane : min(lane, jmax - 1))];
+    const uint32_t word = bt.mask_in[(g0 >> 5) * bt.mask_ld + bt.mask_col + f];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-      const uint32_t bits = __shfl_sync(0xffffffffu, word, j);
-      const float r = ((bits >> lane) & 1u) ? v[j] : 0.f;
+      const float r = ((word >> j) & 1u) ? v[j] : 0.f;
       if (FULL || j < jmax) { dst[j * ldc] = r; csum += r; }
     }
   } else {
@@ -246,27 +243,40 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
     }
   } else if (warp == ROWS_LOAD_WARP) {
     // ------------------------------------------------------------------ loader (converged warp, elected lane issues)
-    // per slab: one bulk copy of the prepared weight slab, one TMA tile of the activations
-    int s = 0;
-    long tile_row = (long)blockIdx.x * ROWS_TG;
+    // per slab: one bulk copy of the prepared weight slab, one TMA tile of the activations. The
+    // activation ring is deeper than the weight ring (weights come from L2, activations from HBM), so
+    // the activation loads run XA slabs ahead of the weight loads: slot (g + XA) % 7 and weight slot
+    // g % 3 are both released by the UMMAs of slab g - 3.
+    constexpr int XA = ROWS_XH_SLOTS - ROWS_W_SLOTS;
+    int sx = 0, sw = 0;
+    long xtile_row = (long)blockIdx.x * ROWS_TG;
     RingPos<ROWS_W_SLOTS> wr;
     RingPos<ROWS_XH_SLOTS> hr;
-    for (int g = 0; g < total; ++g) {
-      const uint32_t st = p.steps[s];
-      mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
+    auto load_x = [&]() {
+      const uint32_t st = p.steps[sx];
       mbar_wait(&bars.xh_free[hr.idx], hr.phase ^ 1u);
       if (elect_one()) {
         mbar_arrive_expect_tx(&bars.xh_full[hr.idx], ROWS_X_SLAB_BYTES);
-        tma_load_2d(sXh + (size_t)hr.idx * ROWS_X_SLAB_BYTES, &p.xmap[step_batch(st)], step_slab(st) * 16, (int)tile_row,
+        tma_load_2d(sXh + (size_t)hr.idx * ROWS_X_SLAB_BYTES, &p.xmap[step_batch(st)], step_slab(st) * 16, (int)xtile_row,
                     &bars.xh_full[hr.idx]);
+      }
+      __syncwarp();
+      hr.advance();
+      if (++sx == nsteps) { sx = 0; xtile_row += (long)gridDim.x * ROWS_TG; }
+    };
+    for (int g = 0; g < XA && g < total; ++g) load_x();
+    for (int g = 0; g < total; ++g) {
+      const uint32_t st = p.steps[sw];
+      if (++sw == nsteps) sw = 0;
+      mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&bars.w_full[wr.idx], ROWS_W_SLOT_BYTES);
         bulk_copy_g2s(sW + (size_t)wr.idx * ROWS_W_SLOT_BYTES, p.b[step_batch(st)].Bprep + (size_t)step_slab(st) * (128 * 8),
                       ROWS_W_SLOT_BYTES, &bars.w_full[wr.idx]);
       }
       __syncwarp();
       wr.advance();
-      hr.advance();
-      if (++s == nsteps) { s = 0; tile_row += (long)gridDim.x * ROWS_TG; }
+      if (g + XA < total) load_x();
     }
   } else if (warp == ROWS_MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer (converged warp, elected lane issues)
