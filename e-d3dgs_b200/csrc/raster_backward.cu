@@ -8,6 +8,7 @@
 //   gaussian_bwd    <- backward.cu:145-488 (computeCov2DCUDA) + :560-628 (preprocessCUDA) +
 //                      :21-140 (SH) + :492-555 (cov3D), fused into one per-Gaussian kernel.
 // Reference quirks that are reproduced on purpose are marked QUIRK.
+#include "raster_cull.cuh"
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
@@ -71,20 +72,6 @@ struct BwdCfg {
   static constexpr size_t mask_bytes = (size_t)BWD_WARPS * (B / 32) * sizeof(uint32_t);
   static constexpr size_t smem = rec_bytes + acc_bytes + id_bytes + mask_bytes + 64;
 };
-
-// Can a Gaussian (centre g, conic (a, b, c), opacity op) reach alpha >= 1/255 anywhere in the 8x4 pixel
-// patch whose first pixel is (x0, y0)? Conservative: alpha = op * exp(-q/2) >= 1/255 needs
-// q = a dx^2 + 2 b dx dy + c dy^2 <= 2 ln(255 op); the bounding box of that ellipse has half-widths
-// sqrt(t c / det), sqrt(t a / det). Margins (1e-3 in t, 1 % + 0.05 px in the box) dwarf fp32 rounding.
-__device__ __forceinline__ bool patch_may_touch(float gx, float gy, float a, float b, float c, float op, float x0, float y0) {
-  if (op < 1.0f / 255.0f) return false;            // G <= 1, so alpha <= op < 1/255 at every pixel
-  const float det = a * c - b * b;
-  if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return true;   // not an ellipse: leave it to the exact test
-  const float t = 2.f * __logf(255.f * op) * 1.001f + 1e-3f;
-  const float inv = t / det;
-  const float hx = sqrtf(inv * c) * 1.01f + 0.05f, hy = sqrtf(inv * a) * 1.01f + 0.05f;
-  return !(gx + hx < x0 || gx - hx > x0 + 7.f || gy + hy < y0 || gy - hy > y0 + 3.f);
-}
 
 template <bool COORD, bool DEPTH>
 __global__ void __launch_bounds__(BWD_THREADS, 2)

@@ -4,6 +4,7 @@
 // kernels forward.cu:427-545 (preprocessCUDATongue), rasterizer_impl.cu:70-111
 // (duplicateWithKeys), :151-173 (identifyTileRanges), forward.cu:550-822 (renderCUDA).
 #include <cstdio>
+#include "raster_cull.cuh"
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
@@ -353,6 +354,7 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
   const float2 pixf = make_float2((float)px, (float)py);
   const float2 pixnf = make_float2((pixf.x - W / 2.f) / fx, (pixf.y - H / 2.f) / fy);
   const float ln = sqrtf(pixnf.x * pixnf.x + pixnf.y * pixnf.y + 1);
+  const float patch_x0 = (float)(blockIdx.x * TILE + (warp & 1) * 8), patch_y0 = (float)(blockIdx.y * TILE + (warp >> 1) * 4);
 
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const int total = (int)(range.y - range.x);
@@ -398,11 +400,31 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
     id_next = load_id(i + 2);
 
     const int n = min(RENDER_BATCH, todo);
-    for (int j = 0; j < n; ++j) {
-      if (__all_sync(0xffffffffu, done)) break;
+    bool warp_done = false;
+#pragma unroll 1
+    for (int m = 0; m * 32 < n && !warp_done; ++m) {
+    // Conservative cull, 32 Gaussians at a time (one per lane): a Gaussian whose alpha >= 1/255 ellipse
+    // misses this warp's 8x4 pixel patch fails the exact per-pixel test below for every lane, so the warp
+    // skips it. The contributor index is the list position, so skipped entries still count.
+    uint32_t cand;
+    {
+      const int jl = m * 32 + lane;
+      bool touch = false;
+      if (jl < n) {
+        const float4 c0 = SQ(buf, 0, jl);
+        const float4 c1 = SQ(buf, 1, jl);
+        touch = patch_may_touch(c0.x, c0.y, c1.x, c1.y, c1.z, c1.w, patch_x0, patch_y0);
+      }
+      cand = __ballot_sync(0xffffffffu, touch);
+    }
+#pragma unroll 1
+    while (cand) {
+      if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+      const int j = m * 32 + __ffs(cand) - 1;
+      cand &= cand - 1;
       const float4 q0 = SQ(buf, 0, j);
       const float4 q1 = SQ(buf, 1, j);
-      if (!done) contributor++;
+      contributor = (uint32_t)(i * RENDER_BATCH + j + 1);
       const float2 d = make_float2(q0.x - pixf.x, q0.y - pixf.y);
       const float power = -0.5f * (q1.x * d.x * d.x + q1.z * d.y * d.y) - q1.y * d.x * d.y;
       bool use = !done && !(power > 0.0f);
@@ -456,6 +478,7 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
       weight += aT;
       T = test_T;
       last_contributor = contributor;
+    }
     }
   }
   cp_async_wait_all();
