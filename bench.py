@@ -49,52 +49,56 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clocks / throttle reasons sampled every 100 ms through NVML (pynvml) from a thread of this process.
+    NVML is initialised before the warm-up so no driver attach happens inside the timed region (an
+    `nvidia-smi -lms` child started there stalled launches for hundreds of ms on some boxes); only samples
+    taken between mark_begin() and mark_end() are reported."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index):
-        self.gpu = gpu_index
-        self.lines = []
-        self.proc = None
-
-    def start(self):
+        self.samples = []
+        self.t0 = self.t1 = None
+        self.stop_flag = threading.Event()
+        self.h = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[0].isdigit() else gpu_index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
             self.thread.start()
         except Exception:  # noqa: BLE001
-            self.proc = None
+            self.h = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+    def _poll(self):
+        while not self.stop_flag.wait(0.1):
+            try:
+                mhz = float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((time.perf_counter(), mhz, mask))
+            except Exception:  # noqa: BLE001
+                pass
+
+    def mark_begin(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
-        if self.proc is None:
-            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
-        time.sleep(0.25)
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return dict(sm_mhz=(sm[len(sm) // 2] if sm else None), sm_max_mhz=(max(mx) if mx else None),
-                    reasons=sorted(reasons), samples=len(sm))
+        if self.h is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvml unavailable"])
+        self.stop_flag.set()
+        inside = [s for s in self.samples if self.t0 is not None and self.t0 <= s[0] <= (self.t1 or 1e30)]
+        if not inside:  # region shorter than one polling interval: nearest sample
+            inside = sorted(self.samples, key=lambda s: abs(s[0] - (self.t0 or 0)))[:1]
+        sm = sorted(s[1] for s in inside)
+        reasons = sorted({name for s in inside for bit, name in self.REASONS if s[2] & bit})
+        return dict(sm_mhz=(sm[len(sm) // 2] if sm else None), sm_max_mhz=self.max_mhz, reasons=reasons,
+                    samples=len(sm))
 
 
 def build_scene(cfg, splat_scale, device, n_cams=16):
@@ -321,6 +325,7 @@ def run_ours(args, rank, local, world):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local) if rank == 0 else None
     for i in range(max(args.warmup, 3)):
         v = view_of(i)
         step(i, cams_dev[v], gts_dev[v % 4])
@@ -330,11 +335,10 @@ def run_ours(args, rank, local, world):
     R = int(state["pkg"]["render"].grad_fn.num_rendered) if hasattr(state["pkg"]["render"].grad_fn, "num_rendered") else 0
 
     # ---- timed region 1: inputs resident in HBM ----
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    if sampler:
+        sampler.mark_begin()
     ev0.record()
     for i in range(args.steps):
         v = view_of(i)
@@ -342,7 +346,10 @@ def run_ours(args, rank, local, world):
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = None
+    if sampler:
+        sampler.mark_end()
+        clocks = sampler.stop()
 
     # ---- timed region 2 (e2e): host buffers, H2D of the step's inputs and D2H of the loss inside ----
     h2d = 3 * H * W * 4 + (16 + 16 + 3) * 4
