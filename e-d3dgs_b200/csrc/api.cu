@@ -153,6 +153,46 @@ int ed3dgs_rasterize_forward(
   return raster_forward(a, static_cast<cudaStream_t>(stream));
 }
 
+size_t ed3dgs_integrate_workspace_bytes(int P, int PN, int width, int height) {
+  return integrate_workspace_bytes(P, PN, width, height);
+}
+
+int ed3dgs_integrate(
+    ed3dgs_alloc_fn geom_alloc, void* geom_user, ed3dgs_alloc_fn binning_alloc, void* binning_user,
+    ed3dgs_alloc_fn image_alloc, void* image_user, int PN, int P, int D, int M, const float* background,
+    int width, int height, const float* points3D, const float* means3D, const float* shs,
+    const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+    const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+    const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size, int prefiltered,
+    float* out_color, int* radii, float* out_alpha_integrated, float* out_color_integrated,
+    float* out_coordinate2d, float* out_sdf, void* workspace, size_t workspace_bytes, int debug,
+    void* stream, int* num_rendered) {
+  g_error[0] = 0;
+  if (P < 0 || PN < 0 || width <= 0 || height <= 0 || !num_rendered || !geom_alloc || !binning_alloc || !image_alloc) {
+    set_error("ed3dgs_integrate: bad argument");
+    return ED3DGS_ERR_ARG;
+  }
+  if (P > 0 && cov3D_precomp == nullptr && (scales == nullptr || rotations == nullptr)) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return ED3DGS_ERR_ARG;
+  }
+  IntegrateArgs ia{};
+  ia.fwd = RasterFwdArgs{geom_alloc, geom_user, binning_alloc, binning_user, image_alloc, image_user, P, D, M,
+                         background, width, height, means3D, shs, colors_precomp, opacities, nullptr, scales,
+                         scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx,
+                         tan_fovy, kernel_size, prefiltered, out_color, nullptr, nullptr, nullptr, nullptr, nullptr,
+                         nullptr, nullptr, radii, 0, 0, debug, num_rendered};
+  ia.PN = PN;
+  ia.points3D = points3D;
+  ia.out_alpha_integrated = out_alpha_integrated;
+  ia.out_color_integrated = out_color_integrated;
+  ia.out_coordinate2d = out_coordinate2d;
+  ia.out_sdf = out_sdf;
+  ia.workspace = workspace;
+  ia.workspace_bytes = workspace_bytes;
+  return raster_integrate(ia, static_cast<cudaStream_t>(stream));
+}
+
 // Test hook (not in the public header): the NEXT ed3dgs_rasterize_backward call of this thread
 // treats grad_scratch as input ([P][16|32] packed rows, raster_state.cuh) and runs only the
 // per-Gaussian stage. Lets the tests check that stage on the reference's own intermediates.

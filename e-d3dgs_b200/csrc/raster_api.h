@@ -45,7 +45,20 @@ struct RasterBwdArgs {
   int packed_is_input;  // test hook: grad_scratch already holds the packed per-Gaussian gradients
 };
 
+// Point integration: the forward argument pack (out_color is [9,H,W] here; tongue_class, the depth /
+// coordinate planes and require_* are unused) plus the query points and their outputs.
+struct IntegrateArgs {
+  RasterFwdArgs fwd;
+  int PN;
+  const float* points3D;
+  float *out_alpha_integrated, *out_color_integrated, *out_coordinate2d, *out_sdf;
+  void* workspace;
+  size_t workspace_bytes;
+};
+
 int raster_forward(const RasterFwdArgs& a, cudaStream_t stream);
+int raster_integrate(const IntegrateArgs& a, cudaStream_t stream);
+size_t integrate_workspace_bytes(int P, int PN, int width, int height);
 int raster_backward(const RasterBwdArgs& a, cudaStream_t stream);
 int mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                  uint8_t* present, cudaStream_t stream);

@@ -17,4 +17,16 @@ __device__ __forceinline__ bool patch_may_touch(float gx, float gy, float a, flo
   return !(gx + hx < x0 || gx - hx > x0 + 7.f || gy + hy < y0 || gy - hy > y0 + 3.f);
 }
 
+// Same test against an arbitrary axis-aligned box of sample positions [xmin, xmax] x [ymin, ymax].
+__device__ __forceinline__ bool box_may_touch(float gx, float gy, float a, float b, float c, float op, float xmin,
+                                              float xmax, float ymin, float ymax) {
+  if (op < 1.0f / 255.0f) return false;
+  const float det = a * c - b * b;
+  if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return true;
+  const float t = 2.f * __logf(255.f * op) * 1.001f + 1e-3f;
+  const float inv = t / det;
+  const float hx = sqrtf(inv * c) * 1.01f + 0.05f, hy = sqrtf(inv * a) * 1.01f + 0.05f;
+  return !(gx + hx < xmin || gx - hx > xmax || gy + hy < ymin || gy - hy > ymax);
+}
+
 }  // namespace ed3dgs

@@ -8,6 +8,7 @@
 #include "gs_math.cuh"
 #include "raster_state.cuh"
 #include "raster_api.h"
+#include "raster_front.h"
 #include "profiler.h"
 
 namespace ed3dgs {
@@ -50,9 +51,14 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const flo
 }
 
 // RaDe-GS geometry of one Gaussian (forward.cu:135-262): ray-space plane, camera-space plane,
-// view-space normal. Returns false for the degenerate case (all outputs zero).
+// view-space normal (all zero in the degenerate case). Returns the reference's `well_conditioned`
+// flag. INTE (computeCov2D<true>, forward.cu:187-236) additionally writes the inverse ray-space
+// covariance the point integration evaluates (upper triangle, 6 floats; zeros when degenerate).
+// For an ill-conditioned covariance the reference assigns that matrix to a shadowed local
+// (forward.cu:222) and stores an uninitialised one; the value it meant to store is written here.
+template <bool INTE>
 __device__ __forceinline__ bool splat_planes(const Cov2DCtx& c, float fx, float fy, float* cam_plane6,
-                                             float2& ray_plane, float3& normal) {
+                                             float2& ray_plane, float3& normal, float* inv6) {
   Mat3 evec;
   float eval[3];
   const int D = eig_sym3(c.Vrk, eval, evec);
@@ -75,7 +81,11 @@ __device__ __forceinline__ bool splat_planes(const Cov2DCtx& c, float fx, float 
     for (int i = 0; i < 6; ++i) cam_plane6[i] = 0;
     ray_plane = make_float2(0, 0);
     normal = make_float3(0, 0, 0);
-    return false;
+    if constexpr (INTE) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) inv6[i] = 0;
+    }
+    return well;
   }
   const float3 t = c.t;
   const float u2 = c.txtz * c.txtz, v2 = c.tytz * c.tytz, uv = c.txtz * c.tytz;
@@ -83,6 +93,37 @@ __device__ __forceinline__ bool splat_planes(const Cov2DCtx& c, float fx, float 
   const Mat3 nJ = mat3_cols(1 / t.z, 0.0f, -(t.x) / (t.z * t.z), 0.0f, 1 / t.z,
                             -(t.y) / (t.z * t.z), t.x / l, t.y / l, t.z / l);
   const Mat3 nJ_inv = mat3_cols(v2 + 1, -uv, 0, -uv, u2 + 1, 0, -c.txtz, -c.tytz, 0);
+  if constexpr (INTE) {
+    Mat3 inv_ray;
+    if (well) {
+      const float ltz = u2 + v2 + 1;
+      const Mat3 full = mat3_scale(mat3_cols(v2 + 1, -uv, c.txtz / l * ltz, -uv, u2 + 1, c.tytz / l * ltz,
+                                             -c.txtz, -c.tytz, 1 / l * ltz),
+                                   t.z / (u2 + v2 + 1));
+      const Mat3 T2 = mat3_mul(c.W, mat3_t(full));
+      inv_ray = mat3_mul(mat3_mul(mat3_t(T2), Vinv), T2);
+    } else {
+      const Mat3 T2 = mat3_mul(c.W, nJ);
+      const Mat3 cov_ray = mat3_mul(mat3_mul(mat3_t(T2), Vinv), T2);
+      Mat3 rvec;
+      float rval[3];
+      eig_sym3(cov_ray, rval, rvec);
+      const int mn = argmin3(rval);
+      const int i1 = (mn + 1) % 3, i2 = (mn + 2) % 3;
+      const float l1 = rval[i1], l2 = rval[i2];
+      Mat3 nv;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) { nv.m[0][r] = rvec.m[i1][r]; nv.m[1][r] = rvec.m[i2][r]; nv.m[2][r] = rvec.m[mn][r]; }
+      const float3 r3 = make_float3(nv.m[0][2], nv.m[1][2], nv.m[2][2]);
+      const Mat3 c2 = mat3_cols(1 / l1, 0, -r3.x / r3.z / l1, 0, 1 / l2, -r3.y / r3.z / l2, -r3.x / r3.z / l1,
+                                -r3.y / r3.z / l2, 0);
+      inv_ray = mat3_mul(mat3_mul(nv, c2), mat3_t(nv));
+    }
+    const Mat3 sc = mat3_cols(1 / fx, 0, 0, 0, 1 / fy, 0, 0, 0, 1);
+    inv_ray = mat3_mul(mat3_mul(sc, inv_ray), sc);
+    inv6[0] = inv_ray.m[0][0]; inv6[1] = inv_ray.m[0][1]; inv6[2] = inv_ray.m[0][2];
+    inv6[3] = inv_ray.m[1][1]; inv6[4] = inv_ray.m[1][2]; inv6[5] = inv_ray.m[2][2];
+  }
   const float vbn = dot3(uvh_mn, uvh);
   const float factor_normal = l / (u2 + v2 + 1);
   const float vb = fmaxf(vbn, 0.0000001f);
@@ -97,9 +138,12 @@ __device__ __forceinline__ bool splat_planes(const Cov2DCtx& c, float fx, float 
   ray_plane = make_float2(plane.x * l / nl / fx, plane.y * l / nl / fy);
   const float3 ray_n = make_float3(-plane.x * factor_normal, -plane.y * factor_normal, -1);
   normal = f3_normalize(mat3_vec(nJ, ray_n));
-  return true;
+  return well;
 }
 
+// INTE = the point-integration flavour (preprocessCUDA<C, true>, forward.cu:307-424): no tongue class,
+// and two more quads per Gaussian in inte_rec: {inv[0..3]} {inv[4], inv[5], well_conditioned, 0}.
+template <bool INTE>
 __global__ void __launch_bounds__(256)
 preprocess_fwd(int P, int D, int M, const float* __restrict__ means, const float* __restrict__ scales,
                float scale_mod, const float* __restrict__ rots, const float* __restrict__ opac,
@@ -108,7 +152,7 @@ preprocess_fwd(int P, int D, int M, const float* __restrict__ means, const float
                const float* __restrict__ view, const float* __restrict__ proj,
                const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy,
                float fx, float fy, float kernel_size, int* __restrict__ radii, GeomState g,
-               uint32_t gx, uint32_t gy, int write_coord) {
+               uint32_t gx, uint32_t gy, int write_coord, float4* __restrict__ inte_rec) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   radii[idx] = 0;
@@ -148,8 +192,17 @@ preprocess_fwd(int P, int D, int M, const float* __restrict__ means, const float
   float cam_plane[6];
   float2 ray_plane;
   float3 normal;
-  splat_planes(c, fx, fy, cam_plane, ray_plane, normal);
-  const float ts = sqrtf(pv.x * pv.x + pv.y * pv.y + pv.z * pv.z);
+  float inv6[6];
+  const bool well = splat_planes<INTE>(c, fx, fy, cam_plane, ray_plane, normal, inv6);
+  if constexpr (INTE) {
+    inte_rec[2 * (size_t)idx] = make_float4(inv6[0], inv6[1], inv6[2], inv6[3]);
+    inte_rec[2 * (size_t)idx + 1] = make_float4(inv6[4], inv6[5], well ? 1.f : 0.f, 0.f);
+  }
+  // x^2 + y^2 + z^2 as nvcc contracts it in the reference (fma(z, z, fma(x, x, y * y))): the point
+  // integration subtracts depths of nearly equal size, so |p_view| has to match to the last bit there
+  float ts;
+  if constexpr (INTE) ts = sqrtf(__fmaf_rn(pv.z, pv.z, __fmaf_rn(pv.x, pv.x, __fmul_rn(pv.y, pv.y))));
+  else ts = sqrtf(pv.x * pv.x + pv.y * pv.y + pv.z * pv.z);
 
   const float det = (cov_x * cov_z - cov_y * cov_y);
   if (det == 0.0f) return;
@@ -177,7 +230,7 @@ preprocess_fwd(int P, int D, int M, const float* __restrict__ means, const float
   g.depths[idx] = pv.z;
   radii[idx] = (int)my_radius;
   float4* rec = g.rec + (size_t)idx * REC_QUADS;
-  rec[0] = make_float4(pix.x, pix.y, ts, tongue[idx]);
+  rec[0] = make_float4(pix.x, pix.y, ts, INTE ? 0.f : tongue[idx]);
   rec[1] = make_float4(conic.x, conic.y, conic.z, opac[idx] * coef);
   rec[2] = make_float4(rgb.x, rgb.y, rgb.z, ray_plane.x);
   rec[3] = make_float4(ray_plane.y, normal.x, normal.y, normal.z);
@@ -552,53 +605,35 @@ static uint32_t tile_id_bits(uint32_t n) {
   return msb;
 }
 
-#define ED_CHECK(stmt)                                                                        \
-  do {                                                                                        \
-    cudaError_t err__ = (stmt);                                                               \
-    if (err__ != cudaSuccess) {                                                               \
-      set_error("%s failed: %s (%s:%d)", #stmt, cudaGetErrorString(err__), __FILE__, __LINE__); \
-      return ED3DGS_ERR_CUDA;                                                                 \
-    }                                                                                         \
-  } while (0)
-
-#define ED_DEBUG_SYNC(what)                                                                   \
-  do {                                                                                        \
-    if (a.debug) {                                                                            \
-      cudaError_t err__ = cudaStreamSynchronize(stream);                                      \
-      if (err__ == cudaSuccess) err__ = cudaGetLastError();                                   \
-      if (err__ != cudaSuccess) {                                                             \
-        set_error("[CUDA ERROR] after %s: %s", what, cudaGetErrorString(err__));              \
-        return ED3DGS_ERR_CUDA;                                                               \
-      }                                                                                       \
-    }                                                                                         \
-  } while (0)
-
-int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
+int raster_front(const RasterFwdArgs& a, float4* inte_rec, FrontEnd& fe, cudaStream_t stream) {
   const int P = a.P, W = a.width, H = a.height;
-  *a.num_rendered = 0;
-  if (P == 0) return ED3DGS_OK;
-  if (a.colors_precomp == nullptr && a.shs == nullptr) {
-    set_error("For non-RGB, provide precomputed Gaussian colors!");
-    return ED3DGS_ERR_ARG;
-  }
   const float focal_y = H / (2.0f * a.tan_fovy);
   const float focal_x = W / (2.0f * a.tan_fovx);
-  const bool coord = a.require_coord != 0, depth = a.require_depth != 0;
+  const bool coord = a.require_coord != 0;
   const uint32_t gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
   const size_t npix = (size_t)W * H, ntiles = (size_t)gx * gy;
+  fe.gx = gx; fe.gy = gy; fe.focal_x = focal_x; fe.focal_y = focal_y;
 
   char* gp = a.geom_alloc(a.geom_user, geom_bytes(P, coord));
   char* ip = a.image_alloc(a.image_user, image_bytes(npix, ntiles, coord));
   if (!gp || !ip) { set_error("state buffer allocation failed"); return ED3DGS_ERR_ALLOC; }
-  GeomState geom = carve_geom(gp, P, coord);
-  ImageState img = carve_image(ip, npix, ntiles, coord);
+  GeomState& geom = fe.geom;
+  ImageState& img = fe.img;
+  geom = carve_geom(gp, P, coord);
+  img = carve_image(ip, npix, ntiles, coord);
 
   {
   ProfScope ps("preprocess_fwd", stream);
-  preprocess_fwd<<<(P + 255) / 256, 256, 0, stream>>>(
-      P, a.D, a.M, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.tongue_class, a.shs,
-      a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.cam_pos, W, H, a.tan_fovx, a.tan_fovy,
-      focal_x, focal_y, a.kernel_size, a.radii, geom, gx, gy, coord ? 1 : 0);
+  if (inte_rec)
+    preprocess_fwd<true><<<(P + 255) / 256, 256, 0, stream>>>(
+        P, a.D, a.M, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, nullptr, a.shs,
+        a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.cam_pos, W, H, a.tan_fovx, a.tan_fovy,
+        focal_x, focal_y, a.kernel_size, a.radii, geom, gx, gy, coord ? 1 : 0, inte_rec);
+  else
+    preprocess_fwd<false><<<(P + 255) / 256, 256, 0, stream>>>(
+        P, a.D, a.M, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.tongue_class, a.shs,
+        a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.cam_pos, W, H, a.tan_fovx, a.tan_fovy,
+        focal_x, focal_y, a.kernel_size, a.radii, geom, gx, gy, coord ? 1 : 0, nullptr);
   }
   ED_DEBUG_SYNC("preprocess");
 
@@ -615,11 +650,12 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
   uint32_t R = 0;
   ED_CHECK(cudaMemcpyAsync(&R, geom.block_sums + nsb, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
   ED_CHECK(cudaStreamSynchronize(stream));
-  *a.num_rendered = (int)R;
+  fe.R = R;
 
   char* bp = a.binning_alloc(a.binning_user, binning_bytes(R));
   if (!bp) { set_error("binning buffer allocation failed"); return ED3DGS_ERR_ALLOC; }
-  BinningState bin = carve_binning(bp, R);
+  BinningState& bin = fe.bin;
+  bin = carve_binning(bp, R);
 
   int sel = 0;
   if (R > 0) {
@@ -636,9 +672,32 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
     }
     ED_DEBUG_SYNC("radix_sort");
   }
+  fe.sel = sel;
   ED_CHECK(cudaMemsetAsync(img.ranges, 0, ntiles * sizeof(uint2), stream));
   if (R > 0) { ProfScope ps("tile_ranges", stream); tile_ranges<<<(R + 255) / 256, 256, 0, stream>>>(R, bin.keys[sel], img.ranges); }
   ED_DEBUG_SYNC("tile_ranges");
+  return ED3DGS_OK;
+}
+
+int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
+  const int P = a.P, W = a.width, H = a.height;
+  *a.num_rendered = 0;
+  if (P == 0) return ED3DGS_OK;
+  if (a.colors_precomp == nullptr && a.shs == nullptr) {
+    set_error("For non-RGB, provide precomputed Gaussian colors!");
+    return ED3DGS_ERR_ARG;
+  }
+  const bool coord = a.require_coord != 0, depth = a.require_depth != 0;
+  FrontEnd fe;
+  const int rc = raster_front(a, nullptr, fe, stream);
+  if (rc != ED3DGS_OK) return rc;
+  *a.num_rendered = (int)fe.R;
+  const GeomState& geom = fe.geom;
+  const ImageState& img = fe.img;
+  const BinningState& bin = fe.bin;
+  const uint32_t gx = fe.gx, gy = fe.gy;
+  const float focal_x = fe.focal_x, focal_y = fe.focal_y;
+  const int sel = fe.sel;
 
   const dim3 grid(gx, gy, 1);
   const uint32_t* plist = bin.vals[sel];

@@ -38,6 +38,13 @@ def _declare(lib):
         + [c_int, c_int, c_int, c_void_p])
     lib.ed3dgs_rasterize_get_state.restype = c_int
     lib.ed3dgs_rasterize_get_state.argtypes = [c_int] * 5 + [P] * 3 + [P] * 17 + [c_void_p]
+    lib.ed3dgs_integrate_workspace_bytes.restype = c_size_t
+    lib.ed3dgs_integrate_workspace_bytes.argtypes = [c_int] * 4
+    lib.ed3dgs_integrate.restype = c_int
+    lib.ed3dgs_integrate.argtypes = (
+        [ALLOC_FN, c_void_p, ALLOC_FN, c_void_p, ALLOC_FN, c_void_p, c_int, c_int, c_int, c_int, P, c_int, c_int]
+        + [P] * 6 + [c_float] + [P] * 5 + [c_float, c_float, c_float, c_int] + [P] * 6
+        + [P, c_size_t, c_int, c_void_p, POINTER(c_int)])
     lib.ed3dgs_mark_visible.restype = c_int
     lib.ed3dgs_mark_visible.argtypes = [c_int, P, P, P, P, c_void_p]
     lib.ed3dgs_dist_cuda2_workspace_bytes.restype = c_size_t

@@ -168,6 +168,63 @@ def mark_visible_raw(means3D, viewmatrix, projmatrix):
     return present
 
 
+def integrate_gaussians_to_points_raw(bg, points3D, means3D, colors_precomp, opacities, scales, rotations,
+                                     scale_modifier, cov3Ds_precomp, view2gaussian_precomp, viewmatrix, projmatrix,
+                                     tanfovx, tanfovy, kernel_size, subpixel_offset, image_height, image_width, sh,
+                                     degree, campos, prefiltered, debug):
+    """Same argument list and 10-tuple result as the reference's pybind ``_C.integrate_gaussians_to_points``
+    (rasterize_points.h:84-108, rasterize_points.cu:273-392). ``view2gaussian_precomp`` and
+    ``subpixel_offset`` are dead arguments in the reference (forward.cu:1162) and are ignored."""
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if points3D.dim() != 2 or points3D.shape[1] != 3:
+        raise RuntimeError("points3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise _lib.Ed3dgsError("ed3dgs_b200 runs on CUDA tensors only (there is no CPU fallback)")
+    dev = means3D.device
+    P, PN = means3D.shape[0], points3D.shape[0]
+    H, W = int(image_height), int(image_width)
+    points3D, means3D = _f32c(points3D, dev), _f32c(means3D, dev)
+    sh, colors_precomp, opacities = _f32c(sh, dev), _f32c(colors_precomp, dev), _f32c(opacities, dev)
+    scales, rotations, cov3Ds_precomp = _f32c(scales, dev), _f32c(rotations, dev), _f32c(cov3Ds_precomp, dev)
+    bg, viewmatrix, projmatrix, campos = (_f32c(bg, dev), _f32c(viewmatrix, dev), _f32c(projmatrix, dev),
+                                          _f32c(campos, dev))
+    f32 = dict(dtype=torch.float32, device=dev)
+    geom, binning, img = _Buffer(dev), _Buffer(dev), _Buffer(dev)
+    rendered = ctypes.c_int(0)
+    if P != 0 and PN != 0:
+        # every output is fully written by the library
+        out_color = torch.empty((9, H, W), **f32)
+        radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+        alpha_integrated = torch.empty((PN,), **f32)
+        color_integrated = torch.empty((PN, 3), **f32)
+        coordinate2d = torch.empty((PN, 2), **f32)
+        sdf = torch.empty((PN,), **f32)
+        lib = _lib.lib()
+        work = torch.empty(lib.ed3dgs_integrate_workspace_bytes(P, PN, W, H), dtype=torch.uint8, device=dev)
+        M = sh.shape[1] if sh.numel() != 0 else 0
+        with torch.cuda.device(dev):
+            status = lib.ed3dgs_integrate(
+                geom.callback, None, binning.callback, None, img.callback, None, PN, P, int(degree), int(M),
+                _lib.ptr(bg), W, H, _lib.ptr(points3D), _lib.ptr(means3D), _lib.ptr(sh), _lib.ptr(colors_precomp),
+                _lib.ptr(opacities), _lib.ptr(scales), float(scale_modifier), _lib.ptr(rotations),
+                _lib.ptr(cov3Ds_precomp), _lib.ptr(viewmatrix), _lib.ptr(projmatrix), _lib.ptr(campos),
+                float(tanfovx), float(tanfovy), float(kernel_size), int(bool(prefiltered)), _lib.ptr(out_color),
+                _lib.ptr(radii), _lib.ptr(alpha_integrated), _lib.ptr(color_integrated), _lib.ptr(coordinate2d),
+                _lib.ptr(sdf), _lib.ptr(work), work.numel(), int(bool(debug)), _lib.stream_handle(),
+                ctypes.byref(rendered))
+        _lib.check(status)
+    else:  # the reference launches nothing and returns its pre-filled tensors (rasterize_points.cu:312-344)
+        out_color = torch.zeros((9, H, W), **f32)
+        radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+        alpha_integrated = torch.ones((PN,), **f32)
+        color_integrated = torch.zeros((PN, 3), **f32)
+        coordinate2d = torch.zeros((PN, 2), **f32)
+        sdf = torch.full((PN,), -1000.0, **f32)
+    return (rendered.value, out_color, alpha_integrated, color_integrated, coordinate2d, sdf, radii, geom.tensor,
+            binning.tensor, img.tensor)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, tongue_class, scales, rotations,
                         cov3Ds_precomp, raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, tongue_class, scales,
@@ -279,7 +336,40 @@ class GaussianRasterizer(nn.Module):
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, tongue_class, scales,
                                    rotations, cov3D_precomp, rs)
 
-    def integrate(self, *args, **kwargs):
-        raise NotImplementedError(
-            "GaussianRasterizer.integrate (GOF point integration for meshing, forward.cu:1109-1543) is a "
-            "'next' row of the hot-path scope (SURVEY.md 8f) and is not built yet")
+    def integrate(self, points3D, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
+                  rotations=None, cov3D_precomp=None, view2gaussian_precomp=None):
+        """GOF point integration for meshing (__init__.py:245-312): returns (color[9,H,W], alpha_integrated[PN],
+        color_integrated[PN,3], point_coordinate[PN,2], point_sdf[PN], radii[P]). Like the reference it is not
+        differentiable and passes kernel_size 0.0 regardless of the settings (:287)."""
+        rs = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        empty = torch.Tensor([])
+        shs = empty if shs is None else shs
+        colors_precomp = empty if colors_precomp is None else colors_precomp
+        scales = empty if scales is None else scales
+        rotations = empty if rotations is None else rotations
+        cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        view2gaussian_precomp = empty if view2gaussian_precomp is None else view2gaussian_precomp
+        args = (rs.bg, points3D, means3D, colors_precomp, opacities, scales, rotations,
+                _scalar(rs.scale_modifier, float), cov3D_precomp, view2gaussian_precomp, rs.viewmatrix,
+                rs.projmatrix, _scalar(rs.tanfovx, float), _scalar(rs.tanfovy, float), 0.0, None,
+                _scalar(rs.image_height, int), _scalar(rs.image_width, int), shs, _scalar(rs.sh_degree, int),
+                rs.campos, bool(rs.prefiltered), bool(rs.debug))
+        with torch.no_grad():
+            if rs.debug:
+                cpu_args = cpu_deep_copy_tuple(args)
+                try:
+                    out = integrate_gaussians_to_points_raw(*args)
+                except Exception as ex:
+                    torch.save(cpu_args, "snapshot_fw.dump")
+                    print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                    raise ex
+            else:
+                out = integrate_gaussians_to_points_raw(*args)
+        (_num_rendered, color, alpha_integrated, color_integrated, point_coordinate, point_sdf, radii, _g, _b,
+         _i) = out
+        return color, alpha_integrated, color_integrated, point_coordinate, point_sdf, radii

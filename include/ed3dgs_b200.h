@@ -110,6 +110,36 @@ int ed3dgs_rasterize_get_state(
     float* camera_planes, float* view_points, void* stream);
 
 /*
+ * Point integration for mesh extraction. Replaces CudaRasterizer::Rasterizer::integrate
+ * (cuda_rasterizer/rasterizer.h:114-149, rasterizer_impl.cu:580-851) as called from
+ * IntegrateGaussiansToPointsCUDA (rasterize_points.cu:273-392; pybind name
+ * `integrate_gaussians_to_points`, Python GaussianRasterizer.integrate, __init__.py:245-312).
+ *   points3D[PN,3]  (other inputs as ed3dgs_rasterize_forward, without tongue_class)
+ *   out_color[9,H,W]  planes: rgb, sum(depth alpha T), median depth, 0, max depth, sum(alpha T),
+ *                     number of points in the pixel (forward.cu:1311-1319,1541)
+ *   out_alpha_integrated[PN] out_color_integrated[PN,3] out_coordinate2d[PN,2] out_sdf[PN]
+ *   radii[P] (int32)
+ * All outputs are fully written when P > 0 and PN > 0 (points outside the image receive the values the
+ * reference pre-fills: alpha 1, colour 0, coordinate 0, sdf -1000; rasterize_points.cu:316-319); with
+ * P == 0 or PN == 0 nothing is written, as in the reference (:344), and the caller supplies the fill.
+ * The reference's invraycov / condition / accum_alpha tensors and its point and point-binning buffers
+ * (:320-336) live in `workspace` (ed3dgs_integrate_workspace_bytes bytes of device scratch, contents
+ * irrelevant). subpixel_offset and view2gaussian_precomp of the reference are dead arguments
+ * (forward.cu:1162 reads the former into an unused local) and are not part of this interface.
+ */
+size_t ed3dgs_integrate_workspace_bytes(int P, int PN, int width, int height);
+int ed3dgs_integrate(
+    ed3dgs_alloc_fn geom_alloc, void* geom_user, ed3dgs_alloc_fn binning_alloc, void* binning_user,
+    ed3dgs_alloc_fn image_alloc, void* image_user, int PN, int P, int D, int M, const float* background,
+    int width, int height, const float* points3D, const float* means3D, const float* shs,
+    const float* colors_precomp, const float* opacities, const float* scales, float scale_modifier,
+    const float* rotations, const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+    const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size, int prefiltered,
+    float* out_color, int* radii, float* out_alpha_integrated, float* out_color_integrated,
+    float* out_coordinate2d, float* out_sdf, void* workspace, size_t workspace_bytes, int debug,
+    void* stream, int* num_rendered);
+
+/*
  * Near-plane visibility mask. Replaces CudaRasterizer::Rasterizer::markVisible
  * (cuda_rasterizer/rasterizer.h:24-29, rasterizer_impl.cu:54-66,176-188; pybind `mark_visible`).
  * present[P] is one byte per Gaussian (torch.bool storage).

@@ -186,6 +186,41 @@ int ref_backward_preprocess(void* c, int P, int D, int M, int W, int H, const fl
   return cudaDeviceSynchronize() == cudaSuccess ? 0 : -1;
 }
 
+// Mirrors IntegrateGaussiansToPointsCUDA (rasterize_points.cu:273-392) minus tensor allocation. The caller
+// passes the outputs pre-filled the way that function fills them: out_color[9,H,W] = 0, accum_alpha[H,W] = 0,
+// radii = 0, out_alpha_integrated[PN] = 1, out_color_integrated[PN,3] = 0, out_coordinate2d[PN,2] = 0,
+// out_sdf[PN] = -1000, invraycov[P,6] = 0, condition[max(P,PN)] = 0 (the reference sizes it PN but indexes it
+// per Gaussian, rasterize_points.cu:322 vs forward.cu:379). Returns num_rendered or -1.
+int ref_integrate(void* c, int PN, int P, int D, int M, const float* background, int W, int H,
+                  const float* points3D, const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                  const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size,
+                  const float* subpixel_offset, float* out_color, float* accum_alpha, float* invraycov,
+                  int* radii, float* out_alpha_integrated, float* out_color_integrated, float* out_coordinate2d,
+                  float* out_sdf, bool* condition) {
+  Ctx* ctx = static_cast<Ctx*>(c);
+  try {
+    Buf pointbuf, pointbin;
+    std::function<char*(size_t)> g = [ctx](size_t n) { return ctx->geom.resize(n); };
+    std::function<char*(size_t)> b = [ctx](size_t n) { return ctx->binning.resize(n); };
+    std::function<char*(size_t)> i = [ctx](size_t n) { return ctx->img.resize(n); };
+    std::function<char*(size_t)> pb = [&pointbuf](size_t n) { return pointbuf.resize(n); };
+    std::function<char*(size_t)> pbin = [&pointbin](size_t n) { return pointbin.resize(n); };
+    int R = CudaRasterizer::Rasterizer::integrate(
+        g, b, i, pb, pbin, PN, P, D, M, background, W, H, points3D, means3D, shs, colors_precomp, opacities,
+        scales, scale_modifier, rotations, cov3D_precomp, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx,
+        tan_fovy, kernel_size, subpixel_offset, false, out_color, accum_alpha, invraycov, radii,
+        out_alpha_integrated, out_color_integrated, out_coordinate2d, out_sdf, condition, false);
+    cudaDeviceSynchronize();
+    ctx->P = P; ctx->R = R; ctx->W = W; ctx->H = H;
+    return R;
+  } catch (const std::exception& e) {
+    snprintf(g_err, sizeof g_err, "%s", e.what());
+    return -1;
+  }
+}
+
 void ref_mark_visible(int P, float* means3D, float* viewmatrix, float* projmatrix, bool* present) {
   CudaRasterizer::Rasterizer::markVisible(P, means3D, viewmatrix, projmatrix, present);
 }

@@ -34,6 +34,9 @@ def lib():
                                    + [c_int, c_int, c_int])
         L.ref_get_state.restype = c_int
         L.ref_get_state.argtypes = [c_void_p] + [P] * 17
+        L.ref_integrate.restype = c_int
+        L.ref_integrate.argtypes = ([c_void_p, c_int, c_int, c_int, c_int, P, c_int, c_int] + [P] * 6 + [c_float]
+                                    + [P] * 5 + [c_float, c_float, c_float] + [P] * 10)
         L.ref_dist_cuda2.argtypes = [c_int, P, P]
         L.ref_mark_visible.argtypes = [c_int, P, P, P, P]
         _lib = L
@@ -114,6 +117,37 @@ class RefRasterizer:
         if st != 0:
             raise RuntimeError(lib().ref_last_error().decode())
         return res
+
+    def integrate(self, rs, points3D, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                  cov3D_precomp=None):
+        """IntegrateGaussiansToPointsCUDA (rasterize_points.cu:273-392) as GaussianRasterizer.integrate calls it
+        (__init__.py:245-312: kernel_size 0.0, zero subpixel_offset); outputs pre-filled like the reference."""
+        dev = means3D.device
+        P, PN = means3D.shape[0], points3D.shape[0]
+        H, W = int(rs.image_height), int(rs.image_width)
+        f = lambda v, *s: torch.full(s, v, dtype=torch.float32, device=dev)  # noqa: E731
+        out = dict(color=f(0.0, 9, H, W), alpha_integrated=f(1.0, PN), color_integrated=f(0.0, PN, 3),
+                   point_coordinate=f(0.0, PN, 2), point_sdf=f(-1000.0, PN),
+                   radii=torch.zeros(P, dtype=torch.int32, device=dev), invraycov=f(0.0, P, 6),
+                   condition=torch.zeros(max(P, PN), dtype=torch.bool, device=dev))
+        accum_alpha = f(0.0, 1, H, W)
+        subpixel = f(0.0, H, W, 2)
+        M = shs.shape[1] if shs is not None and shs.numel() else 0
+        R = 0
+        if P != 0 and PN != 0:
+            torch.cuda.synchronize()
+            R = lib().ref_integrate(
+                self.ctx, PN, P, int(rs.sh_degree), M, _p(rs.bg), W, H, _p(points3D), _p(means3D), _p(shs),
+                _p(colors_precomp), _p(opacities), _p(scales), float(rs.scale_modifier), _p(rotations),
+                _p(cov3D_precomp), _p(rs.viewmatrix), _p(rs.projmatrix), _p(rs.campos), float(rs.tanfovx),
+                float(rs.tanfovy), 0.0, _p(subpixel), _p(out["color"]), _p(accum_alpha), _p(out["invraycov"]),
+                _p(out["radii"]), _p(out["alpha_integrated"]), _p(out["color_integrated"]),
+                _p(out["point_coordinate"]), _p(out["point_sdf"]), _p(out["condition"]))
+            torch.cuda.synchronize()
+            if R < 0:
+                raise RuntimeError(lib().ref_last_error().decode())
+        self.R = R
+        return R, out
 
     def state(self):
         s = self.saved

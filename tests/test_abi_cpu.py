@@ -36,6 +36,7 @@ def test_size_queries_are_pure_host_functions():
     assert lib.ed3dgs_rasterize_backward_scratch_bytes(1000, 0) >= 1000 * 16 * 4
     assert lib.ed3dgs_rasterize_backward_scratch_bytes(1000, 1) >= 1000 * 32 * 4
     assert lib.ed3dgs_dist_cuda2_workspace_bytes(5000) > 5000 * 16
+    assert lib.ed3dgs_integrate_workspace_bytes(1000, 5000, 640, 480) >= 1000 * 32 + 5000 * 44 + 1200 * 4
     a = lib.ed3dgs_deform_workspace_bytes(128, 1, 1000)
     b = lib.ed3dgs_deform_workspace_bytes(128, 2, 1000)
     assert b > a > 1000 * (128 + 640) * 2 * 4
@@ -67,8 +68,11 @@ def test_rasterizer_argument_contract():
         r(g["means3D"], g["means3D"], g["opacities"], g["tongue_class"])
     with pytest.raises(Exception, match="scale/rotation pair"):
         r(g["means3D"], g["means3D"], g["opacities"], g["tongue_class"], shs=g["shs"], scales=g["scales"])
-    with pytest.raises(NotImplementedError):
-        r.integrate()
+    pts = torch.rand(5, 3)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r.integrate(pts, g["means3D"], g["means3D"], g["opacities"])
+    with pytest.raises(Exception, match="scale/rotation pair"):
+        r.integrate(pts, g["means3D"], g["means3D"], g["opacities"], shs=g["shs"], rotations=g["rotations"])
 
 
 def test_drop_in_module_names_resolve():
