@@ -128,6 +128,38 @@ def render(viewpoint_camera, pc, pipe, bg_color, kernel_size, scaling_modifier=1
             "deformed_gaussian_positions": means3D_final, "tongue_mask": rendered_tongue}
 
 
+def integrate(points3D, viewpoint_camera, pc, pipe, bg_color, kernel_size, loaded_iter, scaling_modifier=1.0,
+              override_color=None, num_down_emb_c=5, num_down_emb_f=5):
+    """gaussian_renderer/__init__.py:551-665 (the call mesh_extract_tetrahedra.py:29,45 makes per view): deform the
+    Gaussians to the camera's time, apply the 3D filter, and integrate them to the query points. pc.filter_3D must
+    be set (compute_3D_filter, mesh_extract_tetrahedra.py:78)."""
+    means3D = pc.get_xyz
+    raster_settings = GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+        tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5),
+        kernel_size=kernel_size, bg=bg_color, scale_modifier=scaling_modifier,
+        viewmatrix=viewpoint_camera.world_view_transform, projmatrix=viewpoint_camera.full_proj_transform,
+        sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center, prefiltered=False,
+        debug=getattr(pipe, "debug", False), require_depth=True, require_coord=True)
+    rasterizer = GaussianRasterizer(raster_settings=raster_settings)
+    time = torch.full((1, 1), float(viewpoint_camera.time), dtype=torch.float32, device=means3D.device)
+    with torch.no_grad():
+        means3D_final, scales_deformed, rotations_deformed, opacity_deformed, shs_final, _extras = pc._deformation(
+            means3D, pc._scaling, pc._rotation, pc._opacity, time, None, pc, None, pc.get_features, iter=loaded_iter,
+            num_down_emb_c=num_down_emb_c, num_down_emb_f=num_down_emb_f)
+        scales_final, opacity_final = pc.apply_scaling_n_opacity_with_3D_filter(opacity=opacity_deformed,
+                                                                                scales=scales_deformed)
+        rotations_final = pc.rotation_activation(rotations_deformed)
+        rendered_image, alpha_integrated, color_integrated, point_coordinate, point_sdf, radii = rasterizer.integrate(
+            points3D=points3D, means3D=means3D_final, means2D=None,
+            shs=shs_final if override_color is None else None, colors_precomp=override_color,
+            opacities=opacity_final, scales=scales_final, rotations=rotations_final, cov3D_precomp=None,
+            view2gaussian_precomp=None)
+    return {"render": rendered_image, "alpha_integrated": alpha_integrated, "color_integrated": color_integrated,
+            "point_coordinate": point_coordinate, "point_sdf": point_sdf, "visibility_filter": radii > 0,
+            "radii": radii}
+
+
 def training_loss(pkg, gt_image, reg=True):
     """Per-view loss with the reference's structure (train.py:195-271): L1 on the image plus, once
     the depth/normal regulariser is on (iteration > 15000), terms on expected/median depth, normal

@@ -291,6 +291,8 @@ struct Geom {  // GeometryState (rasterizer_impl.h:29-49), AoS on the host
   float tongue;
   bool clamped[3];
   uint32_t tiles_touched;
+  float invraycov[6];  // integration flavour only (computeCov2D<true>, forward.cu:187-236)
+  bool condition;
 };
 
 struct Ctx {
@@ -321,19 +323,20 @@ extern "C" {
 void* orc_create() { return new Ctx(); }
 void orc_destroy(void* c) { delete static_cast<Ctx*>(c); }
 
-// CudaRasterizer::Rasterizer::forward (rasterizer_impl.cu:255-432) on host pointers.
-int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, const float* means3D, const float* shs,
-                const float* colors_precomp, const float* opacities, const float* tongue_class, const float* scales,
-                float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
-                const float* projmatrix, const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size,
-                float* out_color, float* out_coord, float* out_mcoord, float* out_depth, float* out_mdepth,
-                float* out_alpha, float* out_tongue, float* out_normal, int* radii, int require_coord,
-                int require_depth) {
-  Ctx& ctx = *static_cast<Ctx*>(cv);
+}  // extern "C"
+
+namespace {
+// The part Rasterizer::forward (rasterizer_impl.cu:255-400) and Rasterizer::integrate (:580-712) share:
+// per-Gaussian preprocess, scan, key emission, sort, tile ranges. inte = preprocessCUDA<C, true>
+// (forward.cu:307-424: no tongue class, invraycov3Ds + condition outputs).
+int orc_front(Ctx& ctx, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+              const float* colors_precomp, const float* opacities, const float* tongue_class, const float* scales,
+              float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+              const float* projmatrix, const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size,
+              int* radii, bool inte) {
   ctx.P = P; ctx.W = W; ctx.H = H;
   const float focal_y = H / (2.0f * tan_fovy), focal_x = W / (2.0f * tan_fovx);
   const uint32_t gx = (W + BLOCK_X - 1) / BLOCK_X, gy = (H + BLOCK_Y - 1) / BLOCK_Y;
-  const size_t HW = (size_t)H * W;
   ctx.geom.assign(P, Geom{});
   const V3 campos = {cam_pos[0], cam_pos[1], cam_pos[2]};
 
@@ -389,6 +392,38 @@ int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, co
       const float l = std::sqrt(t.x * t.x + t.y * t.y + t.z * t.z);
       const M3 nJ = cols(1 / t.z, 0.0f, -(t.x) / (t.z * t.z), 0.0f, 1 / t.z, -(t.y) / (t.z * t.z), t.x / l, t.y / l, t.z / l);
       const M3 nJ_inv = cols(v2 + 1, -uv, 0, -uv, u2 + 1, 0, -c.txtz, -c.tytz, 0);
+      if (inte) {  // forward.cu:187-236
+        M3 inv_cov_ray;
+        if (well) {
+          const float ltz = u2 + v2 + 1;
+          const float f = t.z / (u2 + v2 + 1);
+          M3 full = cols(v2 + 1, -uv, c.txtz / l * ltz, -uv, u2 + 1, c.tytz / l * ltz, -c.txtz, -c.tytz, 1 / l * ltz);
+          for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) full.m[a][b] = full.m[a][b] * f;
+          const M3 T2 = mul(c.W, tr(full));
+          inv_cov_ray = mul(mul(tr(T2), Vrk_inv), T2);
+        } else {
+          // The reference assigns this branch's result to a shadowed local (:222) and stores an uninitialised
+          // matrix; the value it meant to store is restated here. Tests avoid ill-conditioned covariances.
+          const M3 T2 = mul(c.W, nJ);
+          const M3 cov_ray = mul(mul(tr(T2), Vrk_inv), T2);
+          M3 rvec;
+          float rval[3];
+          findEigenvaluesSymReal(cov_ray, rval, rvec);
+          const int mn = rval[0] > rval[1] ? (rval[1] > rval[2] ? 2 : 1) : (rval[0] > rval[2] ? 2 : 0);
+          const int i1 = (mn + 1) % 3, i2 = (mn + 2) % 3;
+          const float l1 = rval[i1], l2 = rval[i2];
+          M3 nv;
+          for (int r = 0; r < 3; ++r) { nv.m[0][r] = rvec.m[i1][r]; nv.m[1][r] = rvec.m[i2][r]; nv.m[2][r] = rvec.m[mn][r]; }
+          const float r3[3] = {nv.m[0][2], nv.m[1][2], nv.m[2][2]};
+          const M3 c2 = cols(1 / l1, 0, -r3[0] / r3[2] / l1, 0, 1 / l2, -r3[1] / r3[2] / l2, -r3[0] / r3[2] / l1,
+                             -r3[1] / r3[2] / l2, 0);
+          inv_cov_ray = mul(mul(nv, c2), tr(nv));
+        }
+        const M3 sc = cols(1 / focal_x, 0, 0, 0, 1 / focal_y, 0, 0, 0, 1);
+        inv_cov_ray = mul(mul(sc, inv_cov_ray), sc);
+        g.invraycov[0] = inv_cov_ray.m[0][0]; g.invraycov[1] = inv_cov_ray.m[0][1]; g.invraycov[2] = inv_cov_ray.m[0][2];
+        g.invraycov[3] = inv_cov_ray.m[1][1]; g.invraycov[4] = inv_cov_ray.m[1][2]; g.invraycov[5] = inv_cov_ray.m[2][2];
+      }
       const float vbn = dot(uvh_mn, uvh);
       const float factor_normal = l / (u2 + v2 + 1);
       const float vb = std::max(vbn, 0.0000001f);
@@ -406,7 +441,11 @@ int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, co
       const V3 nv = normalize(mulv(nJ, ray_n));
       g.normal[0] = nv.x; g.normal[1] = nv.y; g.normal[2] = nv.z;
     }
-    g.ts = std::sqrt(p_view.x * p_view.x + p_view.y * p_view.y + p_view.z * p_view.z);
+    g.condition = well;
+    // nvcc contracts x*x+y*y+z*z to fma(z,z,fma(x,x,y*y)); the integration subtracts nearly equal depths, so the
+    // oracle reproduces that rounding there (one ulp of ts moves alpha by ~1e-4)
+    g.ts = inte ? std::sqrt(std::fmaf(p_view.z, p_view.z, std::fmaf(p_view.x, p_view.x, p_view.y * p_view.y)))
+                : std::sqrt(p_view.x * p_view.x + p_view.y * p_view.y + p_view.z * p_view.z);
     const float det = (cov_x * cov_z - cov_y * cov_y);
     if (det == 0.0f) continue;
     const float det_inv = 1.f / det;
@@ -428,7 +467,7 @@ int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, co
     g.conic_opacity[0] = conic[0]; g.conic_opacity[1] = conic[1]; g.conic_opacity[2] = conic[2];
     g.conic_opacity[3] = opacities[idx] * coef;
     g.tiles_touched = (rmax[1] - rmin[1]) * (rmax[0] - rmin[0]);
-    g.tongue = tongue_class[idx];
+    g.tongue = inte ? 0.f : tongue_class[idx];
   }
 
   // ---- InclusiveSum (rasterizer_impl.cu:355) + duplicateWithKeys (:70-111) ----
@@ -481,6 +520,27 @@ int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, co
     }
     if (idx == R - 1) ctx.ranges[2 * cur + 1] = R;
   }
+  return R;
+}
+}  // namespace
+
+extern "C" {
+
+// CudaRasterizer::Rasterizer::forward (rasterizer_impl.cu:255-432) on host pointers.
+int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, const float* means3D, const float* shs,
+                const float* colors_precomp, const float* opacities, const float* tongue_class, const float* scales,
+                float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                const float* projmatrix, const float* cam_pos, float tan_fovx, float tan_fovy, float kernel_size,
+                float* out_color, float* out_coord, float* out_mcoord, float* out_depth, float* out_mdepth,
+                float* out_alpha, float* out_tongue, float* out_normal, int* radii, int require_coord,
+                int require_depth) {
+  Ctx& ctx = *static_cast<Ctx*>(cv);
+  const int R = orc_front(ctx, P, D, M, W, H, means3D, shs, colors_precomp, opacities, tongue_class, scales,
+                          scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
+                          kernel_size, radii, false);
+  const float focal_y = H / (2.0f * tan_fovy), focal_x = W / (2.0f * tan_fovx);
+  const uint32_t gx = (W + BLOCK_X - 1) / BLOCK_X, gy = (H + BLOCK_Y - 1) / BLOCK_Y;
+  const size_t HW = (size_t)H * W;
 
   // ---- renderCUDA forward (forward.cu:550-822), one pixel at a time ----
   const bool COORD = require_coord, DEPTH = require_depth, NORMAL = require_coord || require_depth;
@@ -568,6 +628,226 @@ int orc_forward(void* cv, int P, int D, int M, const float* bg, int W, int H, co
             for (int ch = 0; ch < 3; ch++) out_normal[ch * HW + pix_id] = 0;
           }
         }
+      }
+  }
+  return R;
+}
+
+// CudaRasterizer::Rasterizer::integrate (rasterizer_impl.cu:580-851) on host pointers, restated pixel by
+// pixel the way integrateCUDA (forward.cu:1109-1543) does it: first walk = five-sample visibility test that
+// records the contributing list positions (uint16, at most MAX_NUM_CONTRIBUTORS*4 = 2048), then, per round of
+// at most MAX_NUM_PROJECTED = 256 points that fall into the pixel, a second walk over the recorded positions.
+// Outputs must be pre-filled by the caller like rasterize_points.cu:312-322 does (out_color 0, alpha 1,
+// colour 0, coordinate 0, sdf -1000). invraycov[P,6] / condition[P] may be null.
+int orc_integrate(void* cv, int PN, int P, int D, int M, const float* bg, int W, int H, const float* points3D,
+                  const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                  const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                  const float* viewmatrix, const float* projmatrix, const float* cam_pos, float tan_fovx,
+                  float tan_fovy, float kernel_size, float* out_color, int* radii, float* out_alpha_integrated,
+                  float* out_color_integrated, float* out_coordinate2d, float* out_sdf, float* invraycov,
+                  uint8_t* condition) {
+  Ctx& ctx = *static_cast<Ctx*>(cv);
+  const int R = orc_front(ctx, P, D, M, W, H, means3D, shs, colors_precomp, opacities, nullptr, scales, scale_modifier,
+                          rotations, cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, kernel_size,
+                          radii, true);
+  const float focal_y = H / (2.0f * tan_fovy), focal_x = W / (2.0f * tan_fovx);
+  const uint32_t gx = (W + BLOCK_X - 1) / BLOCK_X, gy = (H + BLOCK_Y - 1) / BLOCK_Y;
+  const size_t HW = (size_t)H * W;
+  for (int i = 0; i < P; ++i) {
+    if (invraycov) std::memcpy(invraycov + 6 * i, ctx.geom[i].invraycov, 24);
+    if (condition) condition[i] = ctx.geom[i].condition ? 1 : 0;
+  }
+
+  // ---- preprocessPointsCUDA (forward.cu:1027-1071) + createWithKeys (rasterizer_impl.cu:114-146) ----
+  struct Pt { float x, y, depth; };
+  std::vector<Pt> pt(PN);
+  std::vector<uint64_t> pkeys;
+  std::vector<uint32_t> pvals;
+  for (int idx = 0; idx < PN; ++idx) {
+    const V3 p_orig = {points3D[3 * idx], points3D[3 * idx + 1], points3D[3 * idx + 2]};
+    const V3 p_view = transformPoint4x3(p_orig, viewmatrix);
+    if (p_view.z <= 0.2f) continue;
+    const float ix = (float)(focal_x * p_view.x / (p_view.z + 0.0000001f) + W / 2.);
+    const float iy = (float)(focal_y * p_view.y / (p_view.z + 0.0000001f) + H / 2.);
+    if (ix < 0 || ix >= W || iy < 0 || iy >= H) continue;
+    pt[idx] = {ix, iy, std::sqrt(std::fmaf(p_view.z, p_view.z, std::fmaf(p_view.x, p_view.x, p_view.y * p_view.y)))};
+    const int x = std::min((int)gx - 1, std::max(0, (int)(ix / BLOCK_X)));
+    const int y = std::min((int)gy - 1, std::max(0, (int)(iy / BLOCK_Y)));
+    uint64_t key = (uint64_t)(y * gx + x);
+    key <<= 32;
+    uint32_t dbits;
+    std::memcpy(&dbits, &pt[idx].depth, 4);
+    key |= dbits;
+    pkeys.push_back(key);
+    pvals.push_back((uint32_t)idx);
+  }
+  const int NI = (int)pkeys.size();
+  const int bit = (int)getHigherMsb(gx * gy);
+  const uint64_t mask = (bit + 32 >= 64) ? ~0ull : ((1ull << (32 + bit)) - 1);
+  std::vector<uint32_t> order(NI);
+  std::iota(order.begin(), order.end(), 0u);
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return (pkeys[a] & mask) < (pkeys[b] & mask); });
+  std::vector<uint32_t> plist(NI), pranges((size_t)gx * gy * 2, 0);
+  for (int i = 0; i < NI; ++i) plist[i] = pvals[order[i]];
+  for (int idx = 0; idx < NI; ++idx) {
+    const uint32_t cur = (uint32_t)(pkeys[order[idx]] >> 32);
+    if (idx == 0) pranges[2 * cur] = 0;
+    else {
+      const uint32_t prev = (uint32_t)(pkeys[order[idx - 1]] >> 32);
+      if (cur != prev) { pranges[2 * prev + 1] = idx; pranges[2 * cur] = idx; }
+    }
+    if (idx == NI - 1) pranges[2 * cur + 1] = NI;
+  }
+
+  // ---- integrateCUDA (forward.cu:1109-1543) ----
+  constexpr int MAXC = 512 * 4, MAXP = 256;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int tile = 0; tile < (int)(gx * gy); ++tile) {
+    const uint32_t tx = tile % gx, ty = tile / gx;
+    const uint32_t r0 = ctx.ranges[2 * tile], r1 = ctx.ranges[2 * tile + 1];
+    const uint32_t q0 = pranges[2 * tile], q1 = pranges[2 * tile + 1];
+    std::vector<uint16_t> contributed_ids(MAXC);
+    for (uint32_t ly = 0; ly < BLOCK_Y; ++ly)
+      for (uint32_t lx = 0; lx < BLOCK_X; ++lx) {
+        const uint32_t px = tx * BLOCK_X + lx, py = ty * BLOCK_Y + ly;
+        if (px >= (uint32_t)W || py >= (uint32_t)H) continue;
+        const size_t pix_id = (size_t)W * py + px;
+        const float pixf[2] = {(float)px + 0.5f, (float)py + 0.5f};
+        float T = 1.0f;
+        uint32_t contributor = 0, last_contributor = 0, n_contrib_local = 0;
+        float C[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // CHANNELS*2+2
+        float mid_depth_center = 0, mid_plane[2] = {0, 0}, mid_mean2d[2] = {0, 0};
+        std::fill(contributed_ids.begin(), contributed_ids.end(), (uint16_t)0);
+        float corner_Ts[5] = {1.0f, 1.0f, 1.0f, 1.0f, 1.0f};
+        const float offset_xs[5] = {0.0f, -0.5f, 0.5f, -0.5f, 0.5f};
+        const float offset_ys[5] = {0.0f, -0.5f, -0.5f, 0.5f, 0.5f};
+        for (uint32_t i = r0; i < r1; ++i) {  // :1197-1303
+          contributor++;
+          const Geom& g = ctx.geom[ctx.point_list[i]];
+          const float* con_o = g.conic_opacity;
+          const float depth_center = g.ts;
+          bool used = false;
+          for (int k = 0; k < 5; ++k) {
+            const float d[2] = {g.means2D[0] - pixf[0] - offset_xs[k], g.means2D[1] - pixf[1] - offset_ys[k]};
+            const float depth = depth_center + (g.ray_plane[0] * d[0] + g.ray_plane[1] * d[1]);
+            const float power = -0.5f * (con_o[0] * d[0] * d[0] + con_o[2] * d[1] * d[1]) - con_o[1] * d[0] * d[1];
+            if (power > 0.0f) continue;
+            const float alpha = std::min(0.99f, con_o[3] * std::exp(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = corner_Ts[k] * (1 - alpha);
+            if (test_T < 0.0001f) continue;
+            if (k == 0)
+              for (int ch = 0; ch < 3; ch++) C[ch] += g.rgb[ch] * alpha * T;
+            if (depth > C[6]) C[6] = depth;
+            if (k == 0) {
+              C[7] += alpha * T;
+              C[3] += depth * alpha * T;
+              if (T > 0.5) {
+                C[4] = depth;
+                mid_depth_center = depth_center;
+                mid_plane[0] = g.ray_plane[0]; mid_plane[1] = g.ray_plane[1];
+                mid_mean2d[0] = g.means2D[0]; mid_mean2d[1] = g.means2D[1];
+              }
+              T = test_T;
+            }
+            corner_Ts[k] = test_T;
+            used = true;
+          }
+          if (used) {
+            last_contributor = contributor;
+            contributed_ids[n_contrib_local] = (uint16_t)contributor;
+            n_contrib_local += 1;
+            if (n_contrib_local >= (uint32_t)MAXC) break;  // done = true (:1297-1301)
+          }
+        }
+        for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = C[ch] + T * bg[ch];
+        out_color[3 * HW + pix_id] = C[3];
+        out_color[4 * HW + pix_id] = C[4];
+        out_color[6 * HW + pix_id] = C[6];
+        out_color[7 * HW + pix_id] = C[7];
+
+        // rounds of at most 256 points of this pixel (:1337-1537). A pixel whose points fit one round stops
+        // there; the reference keeps such a thread looping while another pixel of the tile needs more rounds,
+        // which rewrites identical values and is not restated.
+        uint32_t point_counter_last = 0;
+        int total_projected = 0;
+        bool point_done = false;
+        while (!point_done) {
+          int num_projected = 0;
+          bool exceed = false;
+          uint32_t point_counter = 0;
+          int projected_ids[MAXP];
+          float projected_xy[MAXP][2], projected_depth[MAXP];
+          for (uint32_t i = q0; i < q1; ++i) {
+            point_counter++;
+            if (point_counter <= point_counter_last) continue;
+            const Pt& p = pt[plist[i]];
+            if ((p.x >= (pixf[0] - 0.5)) && (p.x < (pixf[0] + 0.5)) && (p.y >= (pixf[1] - 0.5)) && (p.y < (pixf[1] + 0.5))) {
+              if (num_projected >= MAXP) { exceed = true; break; }
+              projected_ids[num_projected] = (int)plist[i];
+              projected_xy[num_projected][0] = p.x; projected_xy[num_projected][1] = p.y;
+              projected_depth[num_projected] = p.depth;
+              num_projected += 1;
+            }
+          }
+          point_counter_last = point_counter - 1;
+          point_done = !exceed;
+          total_projected += num_projected;
+          float point_alphas[MAXP], point_Ts[MAXP];
+          for (int k = 0; k < num_projected; ++k) { point_alphas[k] = 0.f; point_Ts[k] = 1.f; }
+          uint32_t num_iterated = 0;
+          uint16_t num_contributed_second = 0;
+          for (uint32_t i = r0; i < r1; ++i) {  // :1452-1511
+            num_iterated++;
+            if (num_iterated > last_contributor) break;
+            if (num_iterated != (uint32_t)contributed_ids[num_contributed_second]) continue;
+            num_contributed_second += 1;
+            const Geom& g = ctx.geom[ctx.point_list[i]];
+            const float* con_o = g.conic_opacity;
+            const float depth_center = g.ts;
+            const float* iv = g.invraycov;
+            for (int k = 0; k < num_projected; ++k) {
+              const float d[2] = {g.means2D[0] - projected_xy[k][0], g.means2D[1] - projected_xy[k][1]};
+              const float depth = depth_center + std::fmaf(g.ray_plane[0], d[0], g.ray_plane[1] * d[1]);
+              float alpha;
+              // a x + b y + c z as the GPU evaluates the glm expression: fma(c, z, fma(a, x, b y))
+              auto quad = [&](const V3& u) {
+                const float mx = std::fmaf(iv[2], u.z, std::fmaf(iv[0], u.x, iv[1] * u.y));
+                const float my = std::fmaf(iv[4], u.z, std::fmaf(iv[1], u.x, iv[3] * u.y));
+                const float mz = std::fmaf(iv[5], u.z, std::fmaf(iv[2], u.x, iv[4] * u.y));
+                return std::fmaf(u.z, mz, std::fmaf(u.x, mx, u.y * my));
+              };
+              if (g.condition) {
+                const V3 du = {d[0], d[1], depth_center - std::min(projected_depth[k], depth)};
+                const float power = -0.5f * quad(du);
+                alpha = std::min(0.99f, con_o[3] * std::exp(power));
+              } else if (projected_depth[k] < depth) {
+                alpha = 0;
+              } else {
+                const V3 du = {d[0], d[1], depth_center};
+                const float power = -0.5f * quad(du);
+                alpha = std::min(0.99f, con_o[3] * std::exp(power));
+              }
+              if (alpha < 1.0f / 255.0f) continue;
+              const float test_T = point_Ts[k] * (1 - alpha);
+              point_alphas[k] += alpha * point_Ts[k];
+              point_Ts[k] = test_T;
+            }
+          }
+          for (int k = 0; k < num_projected; ++k) {  // :1519-1536
+            const int id = projected_ids[k];
+            out_alpha_integrated[id] = point_alphas[k];
+            for (int ch = 0; ch < 3; ch++) out_color_integrated[3 * id + ch] = C[ch] + T * bg[ch];
+            out_coordinate2d[2 * id] = projected_xy[k][0];
+            out_coordinate2d[2 * id + 1] = projected_xy[k][1];
+            if (projected_depth[k] > 0) {
+              const float d[2] = {mid_mean2d[0] - projected_xy[k][0], mid_mean2d[1] - projected_xy[k][1]};
+              const float depth = mid_depth_center + (mid_plane[0] * d[0] + mid_plane[1] * d[1]);
+              out_sdf[id] = depth - projected_depth[k];
+            }
+          }
+        }
+        out_color[8 * HW + pix_id] = (float)total_projected;
       }
   }
   return R;

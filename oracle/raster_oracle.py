@@ -32,6 +32,9 @@ def lib():
         L.orc_get_state.argtypes = [c_void_p] + [P] * 15
         L.orc_backward.argtypes = ([c_void_p, c_int, c_int, c_int, P, c_int, c_int] + [P] * 4 + [c_float] + [P] * 5
                                    + [c_float] * 3 + [P] * 2 + [P] * 7 + [P] * 8 + [c_int, c_int])
+        L.orc_integrate.restype = c_int
+        L.orc_integrate.argtypes = ([c_void_p, c_int, c_int, c_int, c_int, P, c_int, c_int] + [P] * 6 + [c_float]
+                                    + [P] * 5 + [c_float] * 3 + [P] * 8)
         L.orc_dist_cuda2.argtypes = [c_int, P, P]
         _lib = L
     return _lib
@@ -74,6 +77,31 @@ class OracleRasterizer:
                               _p(out["mdepth"]), _p(out["alpha"]), _p(out["tongue"]), _p(out["normal"]),
                               _p(out["radii"]), int(rs.require_coord), int(rs.require_depth))
         self.saved = dict(a=a, rs=rs, out=out, M=M, R=R, P=P)
+        return R, out
+
+    def integrate(self, rs, points3D, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                  cov3D_precomp=None, kernel_size=0.0):
+        """Rasterizer::integrate as GaussianRasterizer.integrate calls it (__init__.py:245-312: kernel_size 0.0).
+        Returns (R, dict) with the reference's six outputs plus invraycov / condition."""
+        a = dict(points=_c(points3D), means3D=_c(means3D), opacities=_c(opacities), shs=_c(shs), colors=_c(colors_precomp),
+                 scales=_c(scales), rots=_c(rotations), cov=_c(cov3D_precomp), bg=_c(rs.bg), view=_c(rs.viewmatrix),
+                 proj=_c(rs.projmatrix), campos=_c(rs.campos))
+        P, PN = a["means3D"].shape[0], a["points"].shape[0]
+        H, W = int(rs.image_height), int(rs.image_width)
+        f = lambda v, *s: torch.full(s, v, dtype=torch.float32)  # noqa: E731
+        out = dict(color=f(0.0, 9, H, W), alpha_integrated=f(1.0, PN), color_integrated=f(0.0, PN, 3),
+                   point_coordinate=f(0.0, PN, 2), point_sdf=f(-1000.0, PN), radii=torch.zeros(P, dtype=torch.int32),
+                   invraycov=f(0.0, P, 6), condition=torch.zeros(P, dtype=torch.uint8))
+        M = a["shs"].shape[1] if a["shs"] is not None and a["shs"].numel() else 0
+        R = 0
+        if P != 0 and PN != 0:
+            R = lib().orc_integrate(self.ctx, PN, P, int(rs.sh_degree), M, _p(a["bg"]), W, H, _p(a["points"]),
+                                    _p(a["means3D"]), _p(a["shs"]), _p(a["colors"]), _p(a["opacities"]), _p(a["scales"]),
+                                    float(rs.scale_modifier), _p(a["rots"]), _p(a["cov"]), _p(a["view"]), _p(a["proj"]),
+                                    _p(a["campos"]), float(rs.tanfovx), float(rs.tanfovy), float(kernel_size),
+                                    _p(out["color"]), _p(out["radii"]), _p(out["alpha_integrated"]),
+                                    _p(out["color_integrated"]), _p(out["point_coordinate"]), _p(out["point_sdf"]),
+                                    _p(out["invraycov"]), _p(out["condition"]))
         return R, out
 
     def state(self):

@@ -124,3 +124,32 @@ def test_integrate_properties_with_degenerate_gaussians():
     inside = out[4] != -1000.0
     assert float(out[1][inside].min()) >= 0.0 and float(out[1][inside].max()) <= 1.0 + 1e-6
     assert int(out[0][8].sum()) == int(inside.sum())
+
+
+def test_renderer_integrate_glue_matches_manual_pipeline():
+    """ed3dgs_b200.renderer.integrate (mirror of gaussian_renderer.integrate, __init__.py:551-665) = deformation
+    network + 3D filter + activations + GaussianRasterizer.integrate."""
+    from types import SimpleNamespace as NS
+    from ed3dgs_b200.renderer import GaussianScene, default_hyper, integrate
+    dev = "cuda"
+    g = synthetic.make_gaussians(4000, splat_scale=1.0, device=dev)
+    scene = GaussianScene(g, default_hyper()).to(dev)
+    scene.filter_3D = torch.full((4000, 1), 3e-4, device=dev)
+    cam = synthetic.make_camera(2, 8, 128, 96, 8200.0 * 128 / 3208.0 * 3.0, frame=40, frames=150, device=dev)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
+    pts = (g["xyz"] + 0.003 * torch.randn_like(g["xyz"])).contiguous()
+    ret = integrate(pts, cam, scene, NS(debug=False), bg, 0.0, loaded_iter=20000, num_down_emb_c=30, num_down_emb_f=30)
+    assert set(ret) == {"render", "alpha_integrated", "color_integrated", "point_coordinate", "point_sdf",
+                        "visibility_filter", "radii"}
+    with torch.no_grad():
+        t = torch.full((1, 1), cam.time, device=dev)
+        m, s, r, o, sh, _ = scene._deformation(scene._xyz, scene._scaling, scene._rotation, scene._opacity, t, None,
+                                               scene, None, scene.get_features, iter=20000, num_down_emb_c=30,
+                                               num_down_emb_f=30)
+        s, o = scene.apply_scaling_n_opacity_with_3D_filter(opacity=o, scales=s)
+        rs = synthetic.raster_settings(cam, 3, bg=bg, require_coord=True)
+        out = GaussianRasterizer(rs).integrate(pts, m, None, o, shs=sh, scales=s,
+                                               rotations=torch.nn.functional.normalize(r))
+    assert torch.equal(ret["alpha_integrated"], out[1]) and torch.equal(ret["render"], out[0])
+    inside = ret["point_sdf"] != -1000.0
+    assert int(inside.sum()) > 300 and float(ret["alpha_integrated"][inside].max()) > 0.05
