@@ -31,7 +31,7 @@ UNIT = "views/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3")
@@ -334,6 +334,12 @@ def run_ours(args, rank, local, world):
     from ed3dgs_b200.rasterizer import _RasterizeGaussians  # noqa: F401
     R = int(state["pkg"]["render"].grad_fn.num_rendered) if hasattr(state["pkg"]["render"].grad_fn, "num_rendered") else 0
 
+    # No cyclic-GC pass inside a timed region (a generation-2 sweep over the ctypes / tensor wrappers a step
+    # creates shows up as a multi-millisecond bubble in a 16 ms step); reference counting still frees everything.
+    import gc
+    gc.collect()
+    gc.disable()
+
     # ---- timed region 1: inputs resident in HBM ----
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -353,19 +359,25 @@ def run_ours(args, rank, local, world):
 
     # ---- timed region 2 (e2e): host buffers, H2D of the step's inputs and D2H of the loss inside ----
     h2d = 3 * H * W * 4 + (16 + 16 + 3) * 4
+
+    def e2e_step(i):
+        v = view_of(i)
+        cam = cam_to(cams_host[v], device, non_blocking=True)
+        gt = gts_host[v % 4].to(device, non_blocking=True)
+        return step(i, cam, gt).item()  # device -> host read of the step's result
+
+    for i in range(3):   # untimed: lets the caching allocator settle on this region's allocation pattern
+        e2e_step(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     host_losses = []
     for i in range(args.steps):
-        v = view_of(i)
-        cam = cam_to(cams_host[v], device, non_blocking=True)
-        gt = gts_host[v % 4].to(device, non_blocking=True)
-        loss = step(i, cam, gt)
-        host_losses.append(loss.item())  # device -> host read of the step's result
+        host_losses.append(e2e_step(i))
     e1.record()
     barrier()
     ms_e2e = e0.elapsed_time(e1)
+    gc.enable()
 
     # ---- roofline pass: per-kernel CUDA-event times from the library's own scopes ----
     prof_steps = min(args.steps, 5)

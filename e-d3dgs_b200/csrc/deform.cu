@@ -152,21 +152,33 @@ __global__ void layer0_temporal_bias(const float* __restrict__ W0, const float* 
 }
 
 // db0 += dc1 ; dW0[f][j] += dc1[f] * tau[j] ; dtau[j] = sum_f W0[f][j] * dc1[f]
-__global__ void layer0_temporal_backward(const float* __restrict__ W0, long ld, int temb, int W,
-                                         const float* __restrict__ tau, const float* __restrict__ dc1,
-                                         float* __restrict__ dW0, float* __restrict__ db0, float* __restrict__ dtau) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+// One block per 32 temporal columns j; its 8 warps split the W features, partial sums meet in shared memory.
+__global__ void __launch_bounds__(256)
+layer0_temporal_backward(const float* __restrict__ W0, long ld, int temb, int W, const float* __restrict__ tau,
+                         const float* __restrict__ dc1, float* __restrict__ dW0, float* __restrict__ db0,
+                         float* __restrict__ dtau) {
+  __shared__ float s_part[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
+  float acc = 0.f;
   if (j < temb) {
     const float tj = tau[j];
-    float acc = 0.f;
-    for (int f = 0; f < W; ++f) {
+    for (int f = warp; f < W; f += 8) {
       const float g = dc1[f];
       acc += W0[(long)f * ld + j] * g;
       if (dW0) dW0[(long)f * ld + j] += g * tj;
     }
-    dtau[j] = acc;
   }
-  if (db0 && j < W) db0[j] += dc1[j];
+  s_part[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && j < temb) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_part[w][lane];
+    dtau[j] = t;
+  }
+  if (db0 && blockIdx.x == 0)
+    for (int i = threadIdx.x; i < W; i += blockDim.x) db0[i] += dc1[i];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -466,7 +478,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     a.b[0] = TcBatch{dh, w->feat_w[0] + temb, d_emb, nullptr, nullptr, nullptr, gemb, 0, gemb, 0, 0, 1.f};
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
   }
-  layer0_temporal_backward<<<(max(temb, W) + 127) / 128, 128, 0, stream>>>(
+  layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, W, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
   TC_TRY(cudaGetLastError());
   return ED3DGS_OK;

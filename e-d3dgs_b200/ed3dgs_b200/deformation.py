@@ -131,8 +131,15 @@ class _DeformFunction(torch.autograd.Function):
 
         d_sub = [prep(gouts[h], h) for h in range(5)]
         d_out = [prep(gouts[5 + h], h) for h in range(5)]
-        gc = [torch.zeros_like(p) for p in pc]
-        gf = [torch.zeros_like(p) for p in pf]
+        # one zero fill for all parameter gradients of both stages (they are slices of one buffer)
+        pad = lambda n: (n + 63) // 64 * 64  # noqa: E731  (every slice starts on a 256-byte boundary)
+        flat = torch.zeros(sum(pad(p.numel()) for p in pc) + sum(pad(p.numel()) for p in pf), dtype=torch.float32,
+                           device=dev)
+        gc, gf, o = [], [], 0
+        for src, dst in ((pc, gc), (pf, gf)):
+            for p in src:
+                dst.append(flat[o:o + p.numel()].view(p.shape))
+                o += pad(p.numel())
         # the first stage that runs overwrites d_emb (accumulate flag), so it needs no zero fill
         d_emb = (torch.empty if (N > 0 and (cfg["coarse"] or cfg["fine"])) else torch.zeros)(
             N, gemb, dtype=torch.float32, device=dev)
