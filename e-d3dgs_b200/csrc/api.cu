@@ -283,4 +283,12 @@ int ed3dgs_dist_cuda2(int P, const float* points, float* mean_dists, void* works
   return dist_cuda2(P, points, mean_dists, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
+size_t ed3dgs_knn_workspace_bytes(int P) { return knn_workspace(P > 0 ? P : 0); }
+
+int ed3dgs_knn(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,
+               size_t workspace_bytes, void* stream) {
+  g_error[0] = 0;
+  return knn_exact(P, K, points, sq_dists, indices, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

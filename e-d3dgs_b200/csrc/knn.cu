@@ -209,6 +209,177 @@ knn_mean_dist(int P, const float4* __restrict__ sorted_pts, const float* __restr
   if (live) dists[__float_as_uint(me.w)] = (best[0] + best[1] + best[2]) / 3.0f;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Exact K nearest neighbours of every point (K <= 32), squared distances in double, ascending, self excluded.
+// Replaces utils/extra_utils.py:5-16 (o3d_knn: a python loop of P Open3D/FLANN kd-tree queries on the CPU in
+// float64, run by train.py:218-229 for the embedding regulariser every time the number of Gaussians changes).
+// Same Morton / box machinery as distCUDA2 above with boxes of 256 points; one thread per point in Morton
+// order, so the 32 points of a warp are neighbours in space and visit the same boxes: the box scan is
+// warp-uniform (a box is scanned if any lane needs it) and every candidate load is a broadcast. Candidates are
+// filtered in fp32 against the current K-th distance (with a 1e-6 relative margin); survivors are measured in
+// double -- exact for fp32 inputs up to the final rounding -- and inserted into a sorted list ordered by
+// (distance, index). The +-K Morton window only provides the initial pruning bound, as in simple_knn.cu:150-170.
+constexpr int KNN2_BOX = 256;
+constexpr int KNN2_MAXK = 32;
+constexpr int KNN2_THREADS = 128;
+constexpr int KNN2_CHUNK = 1024;   // box bounds staged per pass: 1024 boxes x 6 floats = 24 KB
+
+__global__ void __launch_bounds__(KNN2_BOX)
+knn_box_bounds256(int P, const float4* __restrict__ sorted_pts, float* __restrict__ box_min, float* __restrict__ box_max) {
+  __shared__ float s_mn[3][8], s_mx[3][8];
+  const int idx = blockIdx.x * KNN2_BOX + threadIdx.x;
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  if (idx < P) {
+    const float4 p = sorted_pts[idx];
+    mn[0] = mx[0] = p.x; mn[1] = mx[1] = p.y; mn[2] = mx[2] = p.z;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+      mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+      mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+    }
+    if (lane == 0) { s_mn[c][warp] = mn[c]; s_mx[c][warp] = mx[c]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int c = threadIdx.x;
+    float a = s_mn[c][0], b = s_mx[c][0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { a = fminf(a, s_mn[c][w]); b = fmaxf(b, s_mx[c][w]); }
+    box_min[3 * blockIdx.x + c] = a;
+    box_max[3 * blockIdx.x + c] = b;
+  }
+}
+
+struct TopK {
+  double d[KNN2_MAXK];
+  uint32_t id[KNN2_MAXK];
+  int K;
+  __device__ __forceinline__ void reset() {
+    for (int j = 0; j < K; ++j) { d[j] = DBL_MAX; id[j] = 0xffffffffu; }
+  }
+  __device__ __forceinline__ double worst() const { return d[K - 1]; }
+  // sorted ascending by (distance, index)
+  __device__ __forceinline__ void push(double dist, uint32_t index) {
+    if (dist > d[K - 1] || (dist == d[K - 1] && index >= id[K - 1])) return;
+    int j = K - 1;
+    while (j > 0 && (d[j - 1] > dist || (d[j - 1] == dist && id[j - 1] > index))) {
+      d[j] = d[j - 1];
+      id[j] = id[j - 1];
+      --j;
+    }
+    d[j] = dist;
+    id[j] = index;
+  }
+};
+
+__device__ __forceinline__ double knn_dist64(const float4 a, const float4 b) {
+  const double dx = (double)a.x - (double)b.x, dy = (double)a.y - (double)b.y, dz = (double)a.z - (double)b.z;
+  // every product and sum rounded on its own (no fma): the value a float64 CPU implementation produces
+  return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+__global__ void __launch_bounds__(KNN2_THREADS)
+knn_topk(int P, int K, const float4* __restrict__ sorted_pts, const float* __restrict__ box_min,
+         const float* __restrict__ box_max, double* __restrict__ out_d, int* __restrict__ out_i) {
+  __shared__ float s_mn[KNN2_CHUNK * 3], s_mx[KNN2_CHUNK * 3];
+  const int idx = blockIdx.x * KNN2_THREADS + threadIdx.x;
+  const bool live = idx < P;
+  float4 me = make_float4(0, 0, 0, 0);
+  TopK top;
+  top.K = K;
+  top.reset();
+  double reject = DBL_MAX;
+  if (live) {
+    me = sorted_pts[idx];
+    for (int i = max(0, idx - K); i <= min(P - 1, idx + K); ++i) {
+      if (i == idx) continue;
+      const float4 q = sorted_pts[i];
+      top.push(knn_dist64(me, q), __float_as_uint(q.w));
+    }
+    reject = top.worst();
+    top.reset();
+  }
+  const float3 p = make_float3(me.x, me.y, me.z);
+  const int nboxes = (P + KNN2_BOX - 1) / KNN2_BOX;
+  for (int b0 = 0; b0 < nboxes; b0 += KNN2_CHUNK) {
+    const int nb = min(KNN2_CHUNK, nboxes - b0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb * 3; i += KNN2_THREADS) {
+      s_mn[i] = box_min[3 * b0 + i];
+      s_mx[i] = box_max[3 * b0 + i];
+    }
+    __syncthreads();
+    for (int b = 0; b < nb; ++b) {
+      // current pruning bound in fp32, rounded up; a box (or candidate) is skipped only when its fp32 distance,
+      // rounded down, is still beyond it
+      const double bound = fmin(reject, top.worst());
+      const float bound32 = (bound >= (double)FLT_MAX) ? FLT_MAX : (float)bound * 1.000001f + 1e-37f;
+      const bool need = live && !(knn_box_dist(s_mn + 3 * b, s_mx + 3 * b, p) * 0.999999f > bound32);
+      if (!__any_sync(0xffffffffu, need)) continue;
+      const int lo = (b0 + b) * KNN2_BOX, hi = min(P, lo + KNN2_BOX);
+      for (int i = lo; i < hi; ++i) {
+        const float4 q = sorted_pts[i];   // same address for the whole warp
+        const float3 d = make_float3(q.x - p.x, q.y - p.y, q.z - p.z);
+        const float d32 = d.x * d.x + d.y * d.y + d.z * d.z;
+        const double cur = fmin(reject, top.worst());
+        const float cur32 = (cur >= (double)FLT_MAX) ? FLT_MAX : (float)cur * 1.000001f + 1e-37f;
+        if (!live || i == idx || d32 * 0.999999f > cur32) continue;
+        const double d64 = knn_dist64(me, q);
+        if (d64 <= reject) top.push(d64, __float_as_uint(q.w));
+      }
+    }
+  }
+  if (live) {
+    const size_t o = (size_t)__float_as_uint(me.w) * K;
+    for (int j = 0; j < K; ++j) { out_d[o + j] = top.d[j]; out_i[o + j] = (int)top.id[j]; }
+  }
+}
+
+size_t knn_workspace(int P) {
+  char* p = nullptr;
+  carve_knn(p, (size_t)P);
+  float* f;
+  const size_t nb = ((size_t)P + KNN2_BOX - 1) / KNN2_BOX;
+  carve(p, f, 3 * nb);
+  carve(p, f, 3 * nb);
+  return reinterpret_cast<size_t>(p) + 256;
+}
+
+int knn_exact(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,
+              size_t workspace_bytes, cudaStream_t stream) {
+  if (P <= 0) return ED3DGS_OK;
+  if (K < 1 || K > KNN2_MAXK || P <= K) {
+    set_error("ed3dgs_knn: need 1 <= K <= %d and more than K points (K = %d, P = %d)", KNN2_MAXK, K, P);
+    return ED3DGS_ERR_ARG;
+  }
+  if (workspace == nullptr || workspace_bytes < knn_workspace(P)) {
+    set_error("ed3dgs_knn workspace too small: need %zu bytes", knn_workspace(P));
+    return ED3DGS_ERR_ARG;
+  }
+  char* p = reinterpret_cast<char*>(workspace);
+  KnnWork w = carve_knn(p, (size_t)P);
+  const int nb256 = (P + KNN2_BOX - 1) / KNN2_BOX;
+  float *bmin, *bmax;
+  carve(p, bmin, 3 * (size_t)nb256);
+  carve(p, bmax, 3 * (size_t)nb256);
+  cudaMemsetAsync(w.bounds, 0, 8 * sizeof(float), stream);
+  knn_bounds<<<min((P + 255) / 256, 1184), 256, 0, stream>>>(P, points, w.bounds);
+  knn_morton<<<(P + 255) / 256, 256, 0, stream>>>(P, points, w.bounds, w.bin.keys[2], w.bin.vals[2]);
+  const int sel = radix_sort_pairs(w.bin, (uint32_t)P, 30, stream);
+  const int nboxes = (P + KNN_BOX - 1) / KNN_BOX;
+  knn_gather_boxes<<<nboxes, KNN_BOX, 0, stream>>>(P, points, w.bin.vals[sel], w.sorted_pts, w.box_min, w.box_max);
+  knn_box_bounds256<<<nb256, KNN2_BOX, 0, stream>>>(P, w.sorted_pts, bmin, bmax);
+  knn_topk<<<(P + KNN2_THREADS - 1) / KNN2_THREADS, KNN2_THREADS, 0, stream>>>(P, K, w.sorted_pts, bmin, bmax, sq_dists,
+                                                                             indices);
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) { set_error("ed3dgs_knn launch failed: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
+  return ED3DGS_OK;
+}
+
 int dist_cuda2(int P, const float* points, float* mean_dists, void* workspace, size_t workspace_bytes,
                cudaStream_t stream) {
   if (P <= 0) return ED3DGS_OK;

@@ -65,5 +65,8 @@ int mark_visible(int P, const float* means3D, const float* viewmatrix, const flo
 int dist_cuda2(int P, const float* points, float* mean_dists, void* workspace, size_t workspace_bytes,
                cudaStream_t stream);
 size_t dist_cuda2_workspace(int P);
+int knn_exact(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,
+              size_t workspace_bytes, cudaStream_t stream);
+size_t knn_workspace(int P);
 
 }  // namespace ed3dgs

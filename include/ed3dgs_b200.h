@@ -157,6 +157,17 @@ int ed3dgs_dist_cuda2(int P, const float* points, float* mean_dists, void* works
                       size_t workspace_bytes, void* stream);
 
 /*
+ * Exact K nearest neighbours of every point (self excluded), K <= 32: sq_dists[P,K] (double, ascending) and
+ * indices[P,K] (int32). Replaces utils/extra_utils.py:5-16 (`o3d_knn`: P Open3D KDTreeFlann queries in a python
+ * loop on the CPU, float64), which train.py:218-229 runs for the embedding regulariser whenever the number
+ * of Gaussians changed. Ties are ordered by index. P must exceed K.
+ * workspace: ed3dgs_knn_workspace_bytes(P) bytes of device scratch.
+ */
+size_t ed3dgs_knn_workspace_bytes(int P);
+int ed3dgs_knn(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,
+               size_t workspace_bytes, void* stream);
+
+/*
  * Per-Gaussian deformation network (coarse + fine stage), fused. Replaces the torch module
  * scene/deformation.py:15-148 (deform_network.forward :108-141, query_time :72-88, deform :90-106,
  * create_net :38-51). See include/ed3dgs_deform.h.
