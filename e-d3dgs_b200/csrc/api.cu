@@ -283,6 +283,13 @@ int ed3dgs_dist_cuda2(int P, const float* points, float* mean_dists, void* works
   return dist_cuda2(P, points, mean_dists, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int ed3dgs_compute_3d_filter(int P, const float* xyz, int num_cameras, const float* cameras, float focal_length,
+                             float* filter_3d, void* scratch, int* any_valid, void* stream) {
+  g_error[0] = 0;
+  return compute_3d_filter(P, xyz, num_cameras, cameras, focal_length, filter_3d, scratch, any_valid,
+                           static_cast<cudaStream_t>(stream));
+}
+
 size_t ed3dgs_knn_workspace_bytes(int P) { return knn_workspace(P > 0 ? P : 0); }
 
 int ed3dgs_knn(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,

@@ -403,3 +403,86 @@ int dist_cuda2(int P, const float* points, float* mean_dists, void* workspace, s
 }
 
 }  // namespace ed3dgs
+
+// ---------------------------------------------------------------------------------------------
+// 3D smoothing filter size per Gaussian. Replaces GaussianModel.compute_3D_filter
+// (scene/gaussian_model.py:538-592): a python loop over every training camera with ~15 torch kernels per
+// camera (and a lazy image load) becomes one pass: a thread per point walks the camera table in shared memory.
+// Camera record (16 floats): R[9] row-major as stored by the reference (camera.R, used as xyz @ R), T[3],
+// focal_x, focal_y, width, height. filter = min over cameras that see the point (depth > 0.2, inside the
+// image widened by 15 %) of the clamped depth, the maximum of those for points no camera sees,
+// / max focal_x * sqrt(0.2).
+namespace ed3dgs {
+
+constexpr int F3D_MAX_CAMS_SMEM = 512;
+
+__global__ void __launch_bounds__(256)
+filter3d_min_depth(int P, const float* __restrict__ xyz, int C, const float* __restrict__ cams,
+                   float* __restrict__ distance, unsigned int* __restrict__ max_valid_bits) {
+  __shared__ float s_cam[F3D_MAX_CAMS_SMEM * 16];
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  float3 p = make_float3(0, 0, 0);
+  if (idx < P) p = make_float3(xyz[3 * idx], xyz[3 * idx + 1], xyz[3 * idx + 2]);
+  float dist = 100000.0f;
+  bool any = false;
+  for (int c0 = 0; c0 < C; c0 += F3D_MAX_CAMS_SMEM) {
+    const int nc = min(F3D_MAX_CAMS_SMEM, C - c0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nc * 16; i += blockDim.x) s_cam[i] = cams[(size_t)c0 * 16 + i];
+    __syncthreads();
+    for (int c = 0; c < nc; ++c) {
+      const float* m = s_cam + 16 * c;
+      // xyz @ R (an fma chain, as an fp32 GEMM with K = 3 computes it), then + T as a separate op (:558)
+      const float x = __fadd_rn(__fmaf_rn(p.z, m[6], __fmaf_rn(p.y, m[3], __fmul_rn(p.x, m[0]))), m[9]);
+      const float y = __fadd_rn(__fmaf_rn(p.z, m[7], __fmaf_rn(p.y, m[4], __fmul_rn(p.x, m[1]))), m[10]);
+      float z = __fadd_rn(__fmaf_rn(p.z, m[8], __fmaf_rn(p.y, m[5], __fmul_rn(p.x, m[2]))), m[11]);
+      const bool valid_depth = z > 0.2f;
+      z = fmaxf(z, 0.001f);
+      const float W = m[14], H = m[15];
+      // three separately rounded torch ops in the reference (:566-567)
+      const float sx = __fadd_rn(__fmul_rn(__fdiv_rn(x, z), m[12]), W / 2.0f);
+      const float sy = __fadd_rn(__fmul_rn(__fdiv_rn(y, z), m[13]), H / 2.0f);
+      const bool in_screen = sx >= -0.15f * W && sx <= W * 1.15f && sy >= -0.15f * H && sy <= 1.15f * H;
+      if (valid_depth && in_screen && idx < P) {
+        dist = fminf(dist, z);
+        any = true;
+      }
+    }
+  }
+  float mx = any ? dist : 0.f;   // depths are > 0.2, so 0 never wins
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0 && mx > 0.f) atomicMax(max_valid_bits, __float_as_uint(mx));
+  if (idx < P) distance[idx] = any ? dist : -1.0f;   // -1 marks "seen by no camera"
+}
+
+__global__ void __launch_bounds__(256)
+filter3d_finish(int P, float* __restrict__ filter, const unsigned int* __restrict__ max_valid_bits, float focal_length) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float d = filter[idx];
+  if (d < 0.f) d = __uint_as_float(*max_valid_bits);
+  filter[idx] = d / focal_length * 0.4472135954999579f;   // (0.2 ** 0.5)
+}
+
+// scratch: at least 4 bytes of device memory; *any_valid (host) = 0 when no camera sees any point (the reference
+// raises in that case: max() of an empty tensor, gaussian_model.py:587).
+int compute_3d_filter(int P, const float* xyz, int C, const float* cams, float focal_length, float* filter,
+                      void* scratch, int* any_valid, cudaStream_t stream) {
+  if (any_valid) *any_valid = 1;
+  if (P <= 0) return ED3DGS_OK;
+  if (C <= 0 || !xyz || !cams || !filter || !scratch) { set_error("compute_3d_filter: bad argument"); return ED3DGS_ERR_ARG; }
+  unsigned int* mx = static_cast<unsigned int*>(scratch);
+  cudaMemsetAsync(mx, 0, sizeof(unsigned int), stream);
+  filter3d_min_depth<<<(P + 255) / 256, 256, 0, stream>>>(P, xyz, C, cams, filter, mx);
+  filter3d_finish<<<(P + 255) / 256, 256, 0, stream>>>(P, filter, mx, focal_length);
+  unsigned int host_mx = 0;
+  cudaError_t err = cudaMemcpyAsync(&host_mx, mx, sizeof(host_mx), cudaMemcpyDeviceToHost, stream);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(stream);
+  if (err == cudaSuccess) err = cudaGetLastError();
+  if (err != cudaSuccess) { set_error("compute_3d_filter failed: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
+  if (any_valid) *any_valid = host_mx != 0 ? 1 : 0;
+  return ED3DGS_OK;
+}
+
+}  // namespace ed3dgs

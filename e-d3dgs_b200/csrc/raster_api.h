@@ -68,5 +68,7 @@ size_t dist_cuda2_workspace(int P);
 int knn_exact(int P, int K, const float* points, double* sq_dists, int* indices, void* workspace,
               size_t workspace_bytes, cudaStream_t stream);
 size_t knn_workspace(int P);
+int compute_3d_filter(int P, const float* xyz, int C, const float* cams, float focal_length, float* filter,
+                      void* scratch, int* any_valid, cudaStream_t stream);
 
 }  // namespace ed3dgs

@@ -51,6 +51,8 @@ def _declare(lib):
     lib.ed3dgs_dist_cuda2_workspace_bytes.argtypes = [c_int]
     lib.ed3dgs_dist_cuda2.restype = c_int
     lib.ed3dgs_dist_cuda2.argtypes = [c_int, P, P, P, c_size_t, c_void_p]
+    lib.ed3dgs_compute_3d_filter.restype = c_int
+    lib.ed3dgs_compute_3d_filter.argtypes = [c_int, P, c_int, P, c_float, P, P, POINTER(c_int), c_void_p]
     lib.ed3dgs_knn_workspace_bytes.restype = c_size_t
     lib.ed3dgs_knn_workspace_bytes.argtypes = [c_int]
     lib.ed3dgs_knn.restype = c_int

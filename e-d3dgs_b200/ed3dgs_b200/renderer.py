@@ -63,6 +63,12 @@ class GaussianScene(nn.Module):
     def get_embedding(self):
         return self._embedding
 
+    @torch.no_grad()
+    def compute_3D_filter(self, cameras):
+        """gaussian_model.py:538-592"""
+        from .filter3d import compute_3D_filter
+        self.filter_3D = compute_3D_filter(self.get_xyz, cameras)
+
     def apply_scaling_n_opacity_with_3D_filter(self, opacity, scales):
         """gaussian_model.py:594-603"""
         opacity = self.opacity_activation(opacity)

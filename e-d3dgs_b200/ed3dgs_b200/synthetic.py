@@ -98,7 +98,11 @@ def make_camera(k, n_cams, W, H, focal, frame=0, frames=1, radius=1.0, device="c
     proj = _projection(0.01, 100.0, fovx, fovy).transpose(0, 1)
     full = (w2v.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0)
     center = w2v.inverse()[3, :3]
+    # R, T as scene/cameras.py keeps them (numpy; R is the transpose of the world-to-camera rotation, so that
+    # xyz @ R + T is the camera-space position, gaussian_model.py:556-558)
+    Rt = w2v.transpose(0, 1).numpy()
     return SimpleNamespace(
+        R=np.ascontiguousarray(Rt[:3, :3].T), T=np.ascontiguousarray(Rt[:3, 3]), original_image=True,
         image_width=W, image_height=H, FoVx=fovx, FoVy=fovy,
         world_view_transform=w2v.contiguous().to(device), full_proj_transform=full.contiguous().to(device),
         camera_center=center.contiguous().to(device), time=float(frame) / float(max(frames, 1)), uid=k)

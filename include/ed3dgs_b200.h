@@ -168,6 +168,18 @@ int ed3dgs_knn(int P, int K, const float* points, double* sq_dists, int* indices
                size_t workspace_bytes, void* stream);
 
 /*
+ * 3D smoothing filter size per Gaussian. Replaces GaussianModel.compute_3D_filter (scene/gaussian_model.py:538-592;
+ * called at every densification and every 100 iterations late in training, train.py:115,421,439-442).
+ *   cameras[num_cameras,16]: R[9] (camera.R as stored, applied as xyz @ R), T[3], focal_x, focal_y, width, height
+ *   focal_length: the largest focal_x of the set (:584-585)      filter_3d[P] (the reference keeps it as [P,1])
+ *   scratch: >= 4 bytes of device memory       *any_valid (host): 0 when no camera sees any point (the reference
+ *   raises there, :587); filter_3d is then meaningless.
+ * Synchronises the stream (to report any_valid).
+ */
+int ed3dgs_compute_3d_filter(int P, const float* xyz, int num_cameras, const float* cameras, float focal_length,
+                             float* filter_3d, void* scratch, int* any_valid, void* stream);
+
+/*
  * Per-Gaussian deformation network (coarse + fine stage), fused. Replaces the torch module
  * scene/deformation.py:15-148 (deform_network.forward :108-141, query_time :72-88, deform :90-106,
  * create_net :38-51). See include/ed3dgs_deform.h.
