@@ -379,6 +379,33 @@ def run_ours(args, rank, local, world):
     ms_e2e = e0.elapsed_time(e1)
     gc.enable()
 
+    # ---- multi-GPU breakdown (untimed for the headline): the collective alone, and steps without it ----
+    multi = None
+    if world > 1:
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a0.record()
+        for _ in range(10):
+            arena.allreduce(1.0 / world)
+        a1.record()
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        keep = arena.allreduce
+        arena.allreduce = lambda *_a, **_k: None
+        c0.record()
+        for i in range(10):
+            v = view_of(i)
+            step(i, cams_dev[v], gts_dev[v % 4])
+        c1.record()
+        barrier()
+        arena.allreduce = keep
+        mt = torch.tensor([a0.elapsed_time(a1) / 10, c0.elapsed_time(c1) / 10], dtype=torch.float64, device=device)
+        mt_max = mt.clone()
+        dist.all_reduce(mt_max, op=dist.ReduceOp.MAX)
+        dist.all_reduce(mt, op=dist.ReduceOp.MIN)
+        multi = {"allreduce_ms": float(mt_max[0]), "compute_only_ms_per_step_max_rank": float(mt_max[1]),
+                 "compute_only_ms_per_step_min_rank": float(mt[1])}
+
     # ---- roofline pass: per-kernel CUDA-event times from the library's own scopes ----
     prof_steps = min(args.steps, 5)
     profile_enable(True)
@@ -443,7 +470,7 @@ def run_ours(args, rank, local, world):
                    "splat_scale": args.splat_scale, "views_per_step": world,
                    "l2_policy": "per-step working set (Gaussian records 64 MB + keys/lists %.0f MB + MLP activations "
                                 "%.1f GB) exceeds the 126 MB L2" % (R * 36 / 1e6, cfg["P"] * 9.9e3 / 1e9),
-                   "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0},
+                   "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi},
         "clocks": clocks,
         "e2e": {"value": world * 1e3 / ms_step_e2e, "unit": UNIT, "ms_per_step": ms_step_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,

@@ -50,6 +50,10 @@ class GradArena:
     def allreduce(self, scale=None):
         """Sum over ranks (no-op for world size 1); optional scale (1/global batch)."""
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            world = dist.get_world_size()
+            if scale is not None and abs(scale * world - 1.0) < 1e-12 and dist.get_backend() == "nccl":
+                dist.all_reduce(self.flat, op=dist.ReduceOp.AVG)   # the mean in the collective: no second pass
+                return self.flat
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
         if scale is not None and scale != 1.0:
             self.flat.mul_(scale)
