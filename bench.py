@@ -171,6 +171,11 @@ def algorithmic_work(cfg, hyper, R, visible_frac, sort_passes):
         "blend_bwd": ("hbm", 128 * R + 68 * px),
         "gaussian_bwd": ("hbm", (367 + 260) * V * P),
         "build_head_grads": ("hbm", (236 + 320) * P),
+        # fused image losses: image + target read, three derivative maps written / read back, gradient written
+        "ssim_l1_forward": ("hbm", 3 * px * 4 * (2 + 3)),
+        "ssim_l1_backward": ("hbm", 3 * px * 4 * (2 + 3 + 1)),
+        "depth_normal_forward": ("hbm", px * 4 * 5),
+        "depth_normal_backward": ("hbm", px * 4 * (5 + 5)),
     }
 
 
@@ -191,6 +196,7 @@ def cpu_step_sample(cfg, splat_scale, sample_P, scale_div, iters=1):
     the first sample_P Gaussians of the scene, image and focal divided by scale_div."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import deform_oracle
+    import loss_oracle
     import raster_oracle
     from ed3dgs_b200 import synthetic
     from ed3dgs_b200.renderer import default_hyper
@@ -219,12 +225,13 @@ def cpu_step_sample(cfg, splat_scale, sample_P, scale_div, iters=1):
         t1 = time.perf_counter()
         orc = raster_oracle.OracleRasterizer()
         R, o = orc.forward(rs, means, opac, g["tongue_class"], shs=out[4], scales=scales, rotations=rots)
-        n = o["normal"]
-        gr = dict(color=torch.sign(o["color"] - gt) / gt.numel(), normal=torch.zeros_like(n),
-                  depth=torch.sign(o["depth"] - o["mdepth"]) * 0.01 / (H * W),
-                  mdepth=-torch.sign(o["depth"] - o["mdepth"]) * 0.01 / (H * W),
-                  alpha=torch.full_like(o["alpha"], 0.01 / (H * W)))
-        gr["normal"][2] = -0.05 * torch.sign(1.0 - n[2]) / (H * W)
+        # the step's loss (renderer.training_loss) through the torch restatement of the reference's losses
+        names = ("color", "depth", "mdepth", "alpha", "normal")
+        leaf = {k: o[k].clone().requires_grad_(True) for k in names}
+        loss = (loss_oracle.l1_loss(leaf["color"], gt) + 0.2 * (1 - loss_oracle.ssim(leaf["color"], gt)) / 2
+                + 0.05 * loss_oracle.depth_normal_loss(cam, leaf["depth"], leaf["mdepth"], leaf["normal"])
+                + 0.01 * leaf["alpha"].mean())
+        gr = dict(zip(names, torch.autograd.grad(loss, [leaf[k] for k in names])))
         gb = orc.backward(gr)
         t2 = time.perf_counter()
         # chain through the activations and the deformation oracle (torch autograd on CPU)
@@ -311,7 +318,7 @@ def run_ours(args, rank, local, world):
         arena.zero()
         pkg = render(cam, scene, pipe, bg, 0.0, require_coord=False, require_depth=True, cam_no=cam.uid % 30,
                      iter=20000, num_down_emb_c=hyper.min_embeddings, num_down_emb_f=hyper.min_embeddings)
-        loss = training_loss(pkg, gt, reg=True)
+        loss = training_loss(pkg, gt, view=cam, reg=True)
         loss.backward()
         arena.allreduce(1.0 / world)
         state["pkg"] = pkg

@@ -1,0 +1,184 @@
+"""Drop-ins for the image losses train.py evaluates either side of the rasterizer, fused into single CUDA passes
+(libed3dgs_b200.so): ``l1_loss`` / ``ssim`` of utils/loss_utils.py:24-72 and ``depth_double_to_normal`` +
+the normal-consistency error of utils/graphics_utils.py:240-267 / train.py:249-267. Same names, arguments and
+return values; plus two fused entry points that return the scalar loss terms directly."""
+import math
+
+import torch
+
+from . import _lib
+
+
+def _check(t):
+    if not t.is_cuda:
+        raise _lib.Ed3dgsError("ed3dgs_b200 losses run on CUDA tensors only (there is no CPU fallback)")
+
+
+class _SsimL1(torch.autograd.Function):
+    """(img, gt) -> (sum |img - gt| / n, sum ssim_map / n); gradients flow to img only (gt is data)."""
+
+    @staticmethod
+    def forward(ctx, img, gt):
+        _check(img)
+        x = img.detach().contiguous().float()
+        y = gt.detach().contiguous().float()
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        sums = torch.empty(2, dtype=torch.float64, device=x.device)
+        maps = torch.empty((3, B * C, H, W), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ed3dgs_ssim_l1_forward(B * C, H, W, x.data_ptr(), y.data_ptr(), sums.data_ptr(),
+                                                        maps.data_ptr(), _lib.stream_handle()))
+        ctx.save_for_backward(x, y, maps)
+        ctx.shape = img.shape
+        out = (sums / x.numel()).float()
+        return out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_l1, g_ssim):
+        x, y, maps = ctx.saved_tensors
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        n = float(x.numel())
+        # the two upstream scalars enter as device-side coefficients: d_img = g_l1/n * sign + g_ssim/n * dssim
+        d = torch.empty_like(x)
+        d2 = None
+        with torch.cuda.device(x.device):
+            lib = _lib.lib()
+            if g_l1 is not None and g_ssim is not None:
+                # two upstream scalars: run the L1 part scaled by g_l1 and the SSIM part scaled by g_ssim
+                d2 = torch.empty_like(x)
+                _lib.check(lib.ed3dgs_ssim_l1_backward(B * C, H, W, x.data_ptr(), y.data_ptr(), maps.data_ptr(),
+                                                      g_l1.contiguous().float().data_ptr(), 1.0 / n, 0.0, d.data_ptr(),
+                                                      _lib.stream_handle()))
+                _lib.check(lib.ed3dgs_ssim_l1_backward(B * C, H, W, x.data_ptr(), y.data_ptr(), maps.data_ptr(),
+                                                      g_ssim.contiguous().float().data_ptr(), 0.0, 1.0 / n,
+                                                      d2.data_ptr(), _lib.stream_handle()))
+                d = d + d2
+            else:
+                g = g_l1 if g_l1 is not None else g_ssim
+                _lib.check(lib.ed3dgs_ssim_l1_backward(B * C, H, W, x.data_ptr(), y.data_ptr(), maps.data_ptr(),
+                                                      g.contiguous().float().data_ptr(),
+                                                      (1.0 / n) if g_l1 is not None else 0.0,
+                                                      (1.0 / n) if g_ssim is not None else 0.0, d.data_ptr(),
+                                                      _lib.stream_handle()))
+        return d.view(ctx.shape), None
+
+
+class _PhotometricLoss(torch.autograd.Function):
+    """Ll1 + lambda_dssim * (1 - ssim) / 2 in one forward and one backward kernel."""
+
+    @staticmethod
+    def forward(ctx, img, gt, lambda_dssim):
+        _check(img)
+        x = img.detach().contiguous().float()
+        y = gt.detach().contiguous().float()
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        sums = torch.empty(2, dtype=torch.float64, device=x.device)
+        maps = torch.empty((3, B * C, H, W), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ed3dgs_ssim_l1_forward(B * C, H, W, x.data_ptr(), y.data_ptr(), sums.data_ptr(),
+                                                        maps.data_ptr(), _lib.stream_handle()))
+        ctx.save_for_backward(x, y, maps)
+        ctx.shape, ctx.lam = img.shape, float(lambda_dssim)
+        m = (sums / x.numel()).float()
+        return m[0] + ctx.lam * (1 - m[1]) / 2, m[0], m[1]
+
+    @staticmethod
+    def backward(ctx, g, _g_l1, _g_ssim):
+        x, y, maps = ctx.saved_tensors
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        n = float(x.numel())
+        d = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ed3dgs_ssim_l1_backward(B * C, H, W, x.data_ptr(), y.data_ptr(), maps.data_ptr(),
+                                                         g.contiguous().float().data_ptr(), 1.0 / n,
+                                                         -ctx.lam / (2.0 * n), d.data_ptr(), _lib.stream_handle()))
+        return d.view(ctx.shape), None, None
+
+
+def l1_loss(network_output, gt, keepdim=False):
+    """utils/loss_utils.py:24-28 (elementwise torch; the fused path is photometric_loss)."""
+    if keepdim:
+        return torch.abs((network_output - gt)).mean(dim=tuple(range(1, network_output.dim())))
+    return torch.abs((network_output - gt)).mean()
+
+
+def ssim(img1, img2, window_size=11, size_average=True):
+    """utils/loss_utils.py:44-52: returns (ssim_value, None) like the reference (its ssim_map is None too)."""
+    if window_size != 11 or not size_average:
+        raise _lib.Ed3dgsError("the fused SSIM implements the reference's only call: window_size=11, size_average=True")
+    _l1, s = _SsimL1.apply(img1, img2)
+    return s, None
+
+
+def photometric_loss(image, gt_image, lambda_dssim):
+    """Ll1 + lambda_dssim * (1 - ssim) / 2 (train.py:195-203). Returns (loss, Ll1, ssim_value); differentiate the
+    first."""
+    return _PhotometricLoss.apply(image, gt_image, lambda_dssim)
+
+
+def _focals(view):
+    W, H = view.image_width, view.image_height
+    return W / (2 * math.tan(view.FoVx / 2.)), H / (2 * math.tan(view.FoVy / 2.))
+
+
+class _DepthNormalLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, depth_e, depth_m, normal, fx, fy, w_e, w_m):
+        _check(normal)
+        de = depth_e.detach().contiguous().float()
+        dm = depth_m.detach().contiguous().float()
+        nr = normal.detach().contiguous().float()
+        H, W = nr.shape[-2], nr.shape[-1]
+        sums = torch.empty(2, dtype=torch.float64, device=nr.device)
+        with torch.cuda.device(nr.device):
+            _lib.check(_lib.lib().ed3dgs_depth_normal_forward(H, W, float(fx), float(fy), de.data_ptr(), dm.data_ptr(),
+                                                             nr.data_ptr(), None, sums.data_ptr(),
+                                                             _lib.stream_handle()))
+        ctx.save_for_backward(de, dm, nr)
+        ctx.cfg = (float(fx), float(fy), float(w_e), float(w_m), depth_e.shape, depth_m.shape, normal.shape)
+        m = (sums / (H * W)).float()
+        return w_e * m[0] + w_m * m[1]
+
+    @staticmethod
+    def backward(ctx, g):
+        de, dm, nr = ctx.saved_tensors
+        fx, fy, w_e, w_m, s_e, s_m, s_n = ctx.cfg
+        H, W = nr.shape[-2], nr.shape[-1]
+        g_e, g_m, g_n = torch.empty_like(de), torch.empty_like(dm), torch.empty_like(nr)
+        with torch.cuda.device(nr.device):
+            _lib.check(_lib.lib().ed3dgs_depth_normal_backward(H, W, fx, fy, de.data_ptr(), dm.data_ptr(), nr.data_ptr(),
+                                                              g.contiguous().float().data_ptr(), w_e, w_m,
+                                                              g_e.data_ptr(), g_m.data_ptr(), g_n.data_ptr(),
+                                                              _lib.stream_handle()))
+        return g_e.view(s_e), g_m.view(s_m), g_n.view(s_n), None, None, None, None
+
+
+def depth_normal_loss(view, rendered_expected_depth, rendered_median_depth, rendered_normal, depth_ratio=0.6):
+    """train.py:249-267 for require_depth: (1 - depth_ratio) * mean(err_expected) + depth_ratio * mean(err_median)
+    with err_k = 1 - <rendered_normal, normal_from_depth_k>."""
+    fx, fy = _focals(view)
+    return _DepthNormalLoss.apply(rendered_expected_depth, rendered_median_depth, rendered_normal, fx, fy,
+                                  1.0 - depth_ratio, depth_ratio)
+
+
+@torch.no_grad()
+def depth_double_to_normal(view, depth1, depth2):
+    """utils/graphics_utils.py:264-267: [2,3,H,W] normals from two depth maps (no gradient on this entry point; the
+    differentiable use is depth_normal_loss)."""
+    _check(depth1)
+    d1 = depth1.detach().contiguous().float()
+    d2 = depth2.detach().contiguous().float()
+    H, W = d1.shape[-2], d1.shape[-1]
+    fx, fy = _focals(view)
+    out = torch.empty((2, 3, H, W), dtype=torch.float32, device=d1.device)
+    dummy_n = torch.zeros((3, H, W), dtype=torch.float32, device=d1.device)
+    sums = torch.empty(2, dtype=torch.float64, device=d1.device)
+    with torch.cuda.device(d1.device):
+        _lib.check(_lib.lib().ed3dgs_depth_normal_forward(H, W, float(fx), float(fy), d1.data_ptr(), d2.data_ptr(),
+                                                         dummy_n.data_ptr(), out.data_ptr(), sums.data_ptr(),
+                                                         _lib.stream_handle()))
+    return out

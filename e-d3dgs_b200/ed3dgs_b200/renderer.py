@@ -166,13 +166,55 @@ def integrate(points3D, viewpoint_camera, pc, pipe, bg_color, kernel_size, loade
             "radii": radii}
 
 
-def training_loss(pkg, gt_image, reg=True):
-    """Per-view loss with the reference's structure (train.py:195-271): L1 on the image plus, once
-    the depth/normal regulariser is on (iteration > 15000), terms on expected/median depth, normal
-    and alpha so that every rasterizer output carries an upstream gradient."""
-    loss = (pkg["render"] - gt_image).abs().mean()
+def training_loss(pkg, gt_image, view=None, reg=True, lambda_dssim=0.2, lambda_depth_normal=0.05, fused=True):
+    """Per-view loss with the reference's structure (train.py:195-271): Ll1 + lambda_dssim * (1 - ssim) / 2 on the
+    image and, once the depth/normal regulariser is on (iteration > 15000, `reg`), lambda_depth_normal times the
+    depth-normal consistency of the expected / median depth maps against the rendered normals (depth_ratio 0.6),
+    plus a small alpha-mask term so that every rasterizer output carries an upstream gradient.
+    fused=True uses the CUDA losses of ed3dgs_b200.loss_utils; fused=False issues the reference's torch ops
+    (`view` is needed for the depth-normal term; without it that term is skipped)."""
+    if fused:
+        from . import loss_utils as L
+        loss = L.photometric_loss(pkg["render"], gt_image, lambda_dssim)[0]
+        if reg and view is not None:
+            loss = loss + lambda_depth_normal * L.depth_normal_loss(view, pkg["expected_depth"], pkg["median_depth"],
+                                                                    pkg["normal"])
+    else:
+        loss = _torch_losses(pkg, gt_image, view, reg, lambda_dssim, lambda_depth_normal)
     if reg:
-        n = pkg["normal"]
-        loss = loss + 0.05 * (1.0 - n[2]).abs().mean() + 0.01 * (pkg["expected_depth"] - pkg["median_depth"]).abs().mean()
         loss = loss + 0.01 * pkg["mask"].mean()
+    return loss
+
+
+def _torch_losses(pkg, gt_image, view, reg, lambda_dssim, lambda_depth_normal):
+    """The same terms written with the torch ops the reference issues (utils/loss_utils.py:24-72,
+    utils/graphics_utils.py:240-267); used by the GPU-vs-reference timing scripts as the reference arm's loss."""
+    import torch.nn.functional as F
+    img = pkg["render"]
+    loss = (img - gt_image).abs().mean()
+    if lambda_dssim > 0:
+        C = img.shape[-3]
+        g = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+        w1 = (g / g.sum()).unsqueeze(1)
+        win = w1.mm(w1.t()).float()[None, None].expand(C, 1, 11, 11).contiguous().to(img.device)
+        conv = lambda t: F.conv2d(t, win, padding=5, groups=C)  # noqa: E731
+        mu1, mu2 = conv(img), conv(gt_image)
+        s1, s2, s12 = conv(img * img) - mu1.pow(2), conv(gt_image * gt_image) - mu2.pow(2), conv(img * gt_image) - mu1 * mu2
+        m = ((2 * mu1 * mu2 + 0.01 ** 2) * (2 * s12 + 0.03 ** 2)) / ((mu1.pow(2) + mu2.pow(2) + 0.01 ** 2) * (s1 + s2 + 0.03 ** 2))
+        loss = loss + lambda_dssim * (1 - m.mean()) / 2
+    if reg and view is not None:
+        W, H = view.image_width, view.image_height
+        fx, fy = W / (2 * math.tan(view.FoVx / 2.)), H / (2 * math.tan(view.FoVy / 2.))
+        dev = img.device
+        Kinv = torch.tensor([[1 / fx, 0., -W / (2 * fx)], [0., 1 / fy, -H / (2 * fy)], [0., 0., 1.0]]).float().to(dev)
+        gx, gy = torch.meshgrid(torch.arange(W) + 0.5, torch.arange(H) + 0.5, indexing='xy')
+        rays = Kinv @ torch.stack([gx, gy, torch.ones_like(gx)], dim=0).reshape(3, -1).float().to(dev)
+        pts = torch.stack([(pkg["expected_depth"].reshape(1, -1) * rays).reshape(3, H, W),
+                           (pkg["median_depth"].reshape(1, -1) * rays).reshape(3, H, W)], dim=0)
+        out = torch.zeros_like(pts)
+        dx = pts[..., 2:, 1:-1] - pts[..., :-2, 1:-1]
+        dy = pts[..., 1:-1, 2:] - pts[..., 1:-1, :-2]
+        out[..., 1:-1, 1:-1] = F.normalize(torch.cross(dx, dy, dim=1), dim=1)
+        err = (1 - (pkg["normal"].unsqueeze(0) * out).sum(dim=1))
+        loss = loss + lambda_depth_normal * (0.4 * err[0].mean() + 0.6 * err[1].mean())
     return loss

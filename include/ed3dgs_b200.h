@@ -180,6 +180,34 @@ int ed3dgs_compute_3d_filter(int P, const float* xyz, int num_cameras, const flo
                              float* filter_3d, void* scratch, int* any_valid, void* stream);
 
 /*
+ * Image losses either side of the rasterizer, fused.
+ *
+ * L1 + SSIM of utils/loss_utils.py:24-72 (`l1_loss`, `ssim` with the 11x11 sigma-1.5 window and zero padding;
+ * train.py:195-205). Forward: sums[0] = sum |img - gt|, sums[1] = sum of the SSIM map (device doubles; the caller
+ * divides by C*H*W), maps[3,C,H,W] = per-pixel partial derivatives kept for the backward. Backward:
+ * d_img = (*upstream) * (coef_l1 * sign(img - gt) + coef_ssim * d(sum ssim)/d img); upstream may be NULL (= 1).
+ */
+int ed3dgs_ssim_l1_forward(int C, int H, int W, const float* img, const float* gt, double* sums, float* maps,
+                           void* stream);
+int ed3dgs_ssim_l1_backward(int C, int H, int W, const float* img, const float* gt, const float* maps,
+                            const float* upstream, float coef_l1, float coef_ssim, float* d_img, void* stream);
+/*
+ * Depth -> normal consistency of train.py:249-267 with utils/graphics_utils.py:240-267
+ * (`depth_double_to_normal`): normals from the expected and the median depth map by back-projection and central
+ * differences, err_k = 1 - <normal, n_k>. Forward: sums[k] = sum over all H*W pixels of err_k (device doubles),
+ * out_normals[2,3,H,W] optional (the tensor depth_double_to_normal returns). Backward of
+ * w_expected * mean(err_0) + w_median * mean(err_1): d_depth_*[H,W] and d_normal[3,H,W], fully written
+ * (any may be NULL).
+ */
+int ed3dgs_depth_normal_forward(int H, int W, float focal_x, float focal_y, const float* depth_expected,
+                                const float* depth_median, const float* normal, float* out_normals, double* sums,
+                                void* stream);
+int ed3dgs_depth_normal_backward(int H, int W, float focal_x, float focal_y, const float* depth_expected,
+                                 const float* depth_median, const float* normal, const float* upstream, float w_expected,
+                                 float w_median, float* d_depth_expected, float* d_depth_median, float* d_normal,
+                                 void* stream);
+
+/*
  * Per-Gaussian deformation network (coarse + fine stage), fused. Replaces the torch module
  * scene/deformation.py:15-148 (deform_network.forward :108-141, query_time :72-88, deform :90-106,
  * create_net :38-51). See include/ed3dgs_deform.h.

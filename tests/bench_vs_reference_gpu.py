@@ -64,14 +64,14 @@ def main():
         color, depth, mdepth, alpha, normal = RefRaster.apply(out[0], out[4], opac, scales, rots, rs,
                                                               scene.tongue_class, ref)
         pkg = dict(render=color, expected_depth=depth, median_depth=mdepth, mask=alpha, normal=normal)
-        training_loss(pkg, gt).backward()
+        training_loss(pkg, gt, view=cam, fused=False).backward()   # the reference's torch losses
 
     def our_step():
         for p in scene.parameters():
             p.grad = None
         pkg = render(cam, scene, NS(debug=False), bg, 0.0, require_coord=False, require_depth=True, cam_no=1,
                      iter=20000, num_down_emb_c=30, num_down_emb_f=30)
-        training_loss(pkg, gt).backward()
+        training_loss(pkg, gt, view=cam).backward()
 
     def timeit(fn, warm=3, iters=8):
         for _ in range(warm):

@@ -32,7 +32,7 @@ for it in range(6):
     phase("zero", arena.zero, acc)
     pkg = phase("render", lambda: render(cam, scene, pipe, bg, 0.0, require_coord=False, require_depth=True, cam_no=1,
                                          iter=20000, num_down_emb_c=30, num_down_emb_f=30), acc)
-    loss = phase("loss", lambda: training_loss(pkg, gt), acc)
+    loss = phase("loss", lambda: training_loss(pkg, gt, view=cam), acc)
     phase("backward", loss.backward, acc)
 for k, v in acc.items():
     v = v[2:]
@@ -43,7 +43,7 @@ for it in range(5):
     arena.zero()
     pkg = render(cam, scene, pipe, bg, 0.0, require_coord=False, require_depth=True, cam_no=1, iter=20000,
                  num_down_emb_c=30, num_down_emb_f=30)
-    training_loss(pkg, gt).backward()
+    training_loss(pkg, gt, view=cam).backward()
 torch.cuda.synchronize(); print("free-running ms/step", (time.perf_counter() - t0) / 5 * 1e3)
 
 def loop(n, sync_each):
@@ -52,7 +52,7 @@ def loop(n, sync_each):
         arena.zero()
         pkg = render(cam, scene, pipe, bg, 0.0, require_coord=False, require_depth=True, cam_no=1, iter=20000,
                      num_down_emb_c=30, num_down_emb_f=30)
-        training_loss(pkg, gt).backward()
+        training_loss(pkg, gt, view=cam).backward()
         if sync_each:
             torch.cuda.synchronize()
     torch.cuda.synchronize()
