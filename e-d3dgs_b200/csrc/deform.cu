@@ -7,6 +7,7 @@
 //  * All GEMMs (forward, input-gradient, weight-gradient) run through one tcgen05/TMEM building
 //    kernel pair (tc_rows.cuh, tc_wgrad.cuh) with bias / ReLU / ReLU-mask / head-update epilogues fused in.
 //  * Bias gradients are the column sums of the ReLU-masked gradients, accumulated in that epilogue.
+#include <cstdint>
 #include <cstdio>
 #include "raster_api.h"
 #include "tc_gemm.cuh"
@@ -198,34 +199,59 @@ struct GradPtrs {
   float coef[5];
 };
 
-__global__ void __launch_bounds__(256)
+// Thread = (row, 16-byte chunk of the 80-float row): chunks 0..7 hold the four small heads (one head per pair of
+// chunks, second chunk all padding), chunks 8..19 the 48 rgb columns as aligned float4 loads. A block covers 16
+// rows per round, four rounds in flight per thread; column sums go thread -> shared -> one atomic per column.
+constexpr int BHG_THREADS = 320;                 // 16 rows x 20 chunks
+constexpr int BHG_UNROLL = 4;
+
+__device__ __forceinline__ float4 head_grad_chunk(const float* __restrict__ src, int h, int c, long n) {
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (src == nullptr) return v;
+  if (h == 4) return __ldg(reinterpret_cast<const float4*>(src + n * 48) + (c - 8));
+  if (c & 1) return v;                           // columns 4..7 of a small head: padding
+  if (h == 2) return __ldg(reinterpret_cast<const float4*>(src) + n);
+  if (h == 3) { v.x = __ldg(src + n); return v; }
+  v.x = __ldg(src + n * 3); v.y = __ldg(src + n * 3 + 1); v.z = __ldg(src + n * 3 + 2);
+  return v;
+}
+
+__global__ void __launch_bounds__(BHG_THREADS)
 build_head_grads(int N, GradPtrs gp, int use_sub, float* __restrict__ G, float* __restrict__ colsum) {
   __shared__ float s_sum[GW];
   for (int i = threadIdx.x; i < GW; i += blockDim.x) s_sum[i] = 0.f;
   __syncthreads();
-  const int col = threadIdx.x % GW;              // 256 threads: 3 rows x 80 cols (+16 idle)
-  const int rsub = threadIdx.x / GW;
-  int h = 0, j = col;
-  if (col >= 32) { h = 4; j = col - 32; } else { h = col >> 3; j = col & 7; }
-  const bool live_col = j < kHeadDim[h];
+  const int c = threadIdx.x % 20, r = threadIdx.x / 20;
+  const int h = c >= 8 ? 4 : (c >> 1);
   const float* src = gp.d_out[h];
   const float* src2 = use_sub ? gp.d_sub[h] : nullptr;
   const float cf = gp.coef[h];
-  const int kd = kHeadDim[h];
-  float acc = 0.f;
-  if (rsub < 3) {
-    for (int n = blockIdx.x * 3 + rsub; n < N; n += gridDim.x * 3) {
-      float v = 0.f;
-      if (live_col) {
-        if (src) v = src[(long)n * kd + j];
-        if (src2) v += src2[(long)n * kd + j];
-        v *= cf;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const long S = (long)gridDim.x * 16;
+  for (long n0 = (long)blockIdx.x * 16 + r; n0 < N; n0 += S * BHG_UNROLL) {
+    float4 v[BHG_UNROLL];
+#pragma unroll
+    for (int u = 0; u < BHG_UNROLL; ++u) {
+      const long n = n0 + u * S;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (n < N) {
+        const float4 a = head_grad_chunk(src, h, c, n), b = head_grad_chunk(src2, h, c, n);
+        v[u] = make_float4((a.x + b.x) * cf, (a.y + b.y) * cf, (a.z + b.z) * cf, (a.w + b.w) * cf);
       }
-      G[(long)n * GW + col] = v;
-      acc += v;
     }
-    atomicAdd(&s_sum[col], acc);
+#pragma unroll
+    for (int u = 0; u < BHG_UNROLL; ++u) {
+      const long n = n0 + u * S;
+      if (n < N) {
+        reinterpret_cast<float4*>(G + n * GW)[c] = v[u];
+        acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w;
+      }
+    }
   }
+  atomicAdd(&s_sum[c * 4 + 0], acc.x);
+  atomicAdd(&s_sum[c * 4 + 1], acc.y);
+  atomicAdd(&s_sum[c * 4 + 2], acc.z);
+  atomicAdd(&s_sum[c * 4 + 3], acc.w);
   __syncthreads();
   for (int i = threadIdx.x; i < GW; i += blockDim.x)
     if (s_sum[i] != 0.f) atomicAdd(colsum + i, s_sum[i]);
@@ -586,17 +612,21 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
     gp.d_sub[h] = d_sub ? d_sub[h] : nullptr;
     gp.coef[h] = coef[h];
     any_sub = any_sub || gp.d_sub[h] != nullptr;
+    if ((h == 2 || h == 4) && (((uintptr_t)gp.d_out[h] | (uintptr_t)gp.d_sub[h]) & 15u)) {
+      set_error("deform_backward: the rotation / rgb upstream gradients must be 16-byte aligned");
+      return ED3DGS_ERR_ARG;
+    }
   }
-  const int gblocks = 592;
+  const int gblocks = 148 * 6;
   // fine stage sees d_out only; coarse stage sees d_out + d_sub
   cudaMemsetAsync(wk.colsum[1], 0, GW * sizeof(float), stream);
   { ProfScope ps("build_head_grads", stream);
-  build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 0, wk.G[1], wk.colsum[1]); }
+  build_head_grads<<<gblocks, BHG_THREADS, 0, stream>>>(N, gp, 0, wk.G[1], wk.colsum[1]); }
   const float* Gc = wk.G[1];
   const float* colc = wk.colsum[1];
   if (any_sub && coarse) {
     cudaMemsetAsync(wk.colsum[0], 0, GW * sizeof(float), stream);
-    build_head_grads<<<gblocks, 256, 0, stream>>>(N, gp, 1, wk.G[0], wk.colsum[0]);
+    build_head_grads<<<gblocks, BHG_THREADS, 0, stream>>>(N, gp, 1, wk.G[0], wk.colsum[0]);
     Gc = wk.G[0];
     colc = wk.colsum[0];
   }

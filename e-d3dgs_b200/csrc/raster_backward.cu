@@ -393,8 +393,8 @@ blend_bwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_l
 // SH backward for one Gaussian (backward.cu:21-140). Writes dL_dsh[M][3] (zero above `deg`) and
 // returns the view-direction part of dL/dmean.
 __device__ __forceinline__ float3 sh_bwd(int deg, int M, const float3 pos, const float3 campos,
-                                         const float* __restrict__ sh, uint8_t clamp_bits, float3 dL_dRGB,
-                                         float* __restrict__ dL_dsh) {
+                                         const float* sh, uint8_t clamp_bits, float3 dL_dRGB,
+                                         float* dL_dsh) {
   const float3 dir_orig = f3_sub(pos, campos);
   const float len = sqrtf(dot3(dir_orig, dir_orig));
   const float3 dir = make_float3(dir_orig.x / len, dir_orig.y / len, dir_orig.z / len);
@@ -516,42 +516,18 @@ __device__ __forceinline__ void cov3d_bwd(const float3 scale, float mod, const f
                2 * y * (dMt.m[1][2] + dMt.m[2][1]) - 4 * z * (dMt.m[1][1] + dMt.m[0][0]);
 }
 
+// Per-Gaussian chain rule for one visible Gaussian (backward.cu:145-628). sh_in / sh_out are this
+// Gaussian's [M][3] rows (they may be the same shared-memory row: every read precedes the writes).
 template <bool COORD>
-__global__ void __launch_bounds__(128)
-gaussian_bwd(int P, int D, int M, const float* __restrict__ means, const int* __restrict__ radii,
-             const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
-             const float* __restrict__ scales, const float* __restrict__ rots, float scale_mod,
-             const float* __restrict__ cov3D_pre, const float* __restrict__ view,
-             const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
-             float kernel_size, const float* __restrict__ campos, const float* __restrict__ grad,
-             float* __restrict__ dL_dmean2D, float* __restrict__ dL_dcolor, float* __restrict__ dL_dopacity,
-             float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-             float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+__device__ __forceinline__ void gaussian_bwd_one(
+    int idx, int D, int M, const float* __restrict__ means, const float* sh_in, uint8_t clamp_bits,
+    const float* __restrict__ scales, const float* __restrict__ rots, float scale_mod,
+    const float* __restrict__ cov3D_pre, const float* __restrict__ view, const float* __restrict__ proj, float h_x,
+    float h_y, float tan_fovx, float tan_fovy, float kernel_size, const float* __restrict__ campos,
+    const float* __restrict__ grad, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dcolor,
+    float* __restrict__ dL_dopacity, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* sh_out,
+    float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
   constexpr int V = COORD ? 32 : 16;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
-  if (!(radii[idx] > 0)) {
-    // The reference leaves its zero-initialised outputs untouched for culled Gaussians.
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      dL_dmean2D[3 * idx + i] = 0;
-      dL_dcolor[3 * idx + i] = 0;
-      dL_dmean3D[3 * idx + i] = 0;
-    }
-    dL_dopacity[idx] = 0;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) dL_dcov3D[6 * idx + i] = 0;
-    if (shs)
-      for (int i = 0; i < 3 * M; ++i) dL_dsh[(size_t)idx * M * 3 + i] = 0;
-    if (scales) {
-#pragma unroll
-      for (int i = 0; i < 3; ++i) dL_dscale[3 * idx + i] = 0;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) dL_drot[4 * idx + i] = 0;
-    }
-    return;
-  }
-
   const float4* gq = reinterpret_cast<const float4*>(grad + (size_t)idx * V);
   const float4 g0 = gq[0], g1 = gq[1], g2 = gq[2], g3 = gq[3];
   const float3 dmean2D = make_float3(g0.x, g0.y, g0.z);
@@ -819,9 +795,9 @@ gaussian_bwd(int P, int D, int M, const float* __restrict__ means, const int* __
     dmean.y += d1.y + d2.y;
     dmean.z += d1.z + d2.z;
   }
-  if (shs) {
-    const float3 dsh_mean = sh_bwd(D, M, mean, make_float3(campos[0], campos[1], campos[2]),
-                                   shs + (size_t)idx * M * 3, clamped[idx], dcolor, dL_dsh + (size_t)idx * M * 3);
+  if (sh_in) {
+    const float3 dsh_mean = sh_bwd(D, M, mean, make_float3(campos[0], campos[1], campos[2]), sh_in, clamp_bits, dcolor,
+                                   sh_out);
     dmean.x += dsh_mean.x;
     dmean.y += dsh_mean.y;
     dmean.z += dsh_mean.z;
@@ -830,6 +806,91 @@ gaussian_bwd(int P, int D, int M, const float* __restrict__ means, const int* __
   dL_dmean3D[3 * idx + 1] = dmean.y;
   dL_dmean3D[3 * idx + 2] = dmean.z;
   if (scales) cov3d_bwd(scale, scale_mod, quat, dcov, dL_dscale + 3 * idx, dL_drot + 4 * idx);
+}
+
+// One thread per Gaussian. The SH rows (48 floats per Gaussian at M = 16: the bulk of this kernel's
+// traffic) go through shared memory: a warp loads the rows of its visible Gaussians with coalesced
+// 16-byte reads, every thread works in place on its own row (row stride 49 words: conflict-free), and the
+// warp writes the 32 gradient rows back as one contiguous 6 KB run.
+constexpr int GB_THREADS = 128;
+constexpr int GB_SH_ROW = 49;
+
+template <bool COORD>
+__global__ void __launch_bounds__(GB_THREADS, 4)
+gaussian_bwd(int P, int D, int M, const float* __restrict__ means, const int* __restrict__ radii,
+             const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+             const float* __restrict__ scales, const float* __restrict__ rots, float scale_mod,
+             const float* __restrict__ cov3D_pre, const float* __restrict__ view,
+             const float* __restrict__ proj, float h_x, float h_y, float tan_fovx, float tan_fovy,
+             float kernel_size, const float* __restrict__ campos, const float* __restrict__ grad,
+             float* __restrict__ dL_dmean2D, float* __restrict__ dL_dcolor, float* __restrict__ dL_dopacity,
+             float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+             float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+  __shared__ float s_sh[GB_THREADS / 32][32 * GB_SH_ROW];
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool inb = idx < P;
+  const bool vis = inb && radii[idx] > 0;
+  const bool staged = shs != nullptr && M == 16;
+  const unsigned vmask = __ballot_sync(0xffffffffu, vis);
+  const long wbase = (long)blockIdx.x * blockDim.x + wrp * 32;   // first Gaussian of this warp
+  float* const wsh = s_sh[wrp];
+  float* const srow = wsh + lane * GB_SH_ROW;
+  if (staged && vmask != 0u) {
+    const float4* g4 = reinterpret_cast<const float4*>(shs + wbase * 48);
+#pragma unroll 4
+    for (int q = lane; q < 32 * 12; q += 32) {
+      const int row = q / 12, c4 = q - row * 12;
+      if ((vmask >> row) & 1u) {
+        const float4 v = __ldg(g4 + q);
+        float* d = wsh + row * GB_SH_ROW + c4 * 4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      }
+    }
+    __syncwarp();
+  }
+  if (vis) {
+    const float* sh_in = staged ? srow : (shs ? shs + (size_t)idx * M * 3 : nullptr);
+    float* sh_out = staged ? srow : (shs ? dL_dsh + (size_t)idx * M * 3 : nullptr);
+    gaussian_bwd_one<COORD>(idx, D, M, means, sh_in, clamped[idx], scales, rots, scale_mod, cov3D_pre, view, proj, h_x,
+                            h_y, tan_fovx, tan_fovy, kernel_size, campos, grad, dL_dmean2D, dL_dcolor, dL_dopacity,
+                            dL_dmean3D, dL_dcov3D, sh_out, dL_dscale, dL_drot);
+  } else if (inb) {
+    // The reference leaves its zero-initialised outputs untouched for culled Gaussians.
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      dL_dmean2D[3 * idx + i] = 0;
+      dL_dcolor[3 * idx + i] = 0;
+      dL_dmean3D[3 * idx + i] = 0;
+    }
+    dL_dopacity[idx] = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dL_dcov3D[6 * idx + i] = 0;
+    if (staged) {
+#pragma unroll
+      for (int i = 0; i < 48; ++i) srow[i] = 0.f;
+    } else if (shs) {
+      for (int i = 0; i < 3 * M; ++i) dL_dsh[(size_t)idx * M * 3 + i] = 0;
+    }
+    if (scales) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) dL_dscale[3 * idx + i] = 0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dL_drot[4 * idx + i] = 0;
+    }
+  }
+  if (staged) {
+    __syncwarp();
+    float4* o4 = reinterpret_cast<float4*>(dL_dsh + wbase * 48);
+#pragma unroll 4
+    for (int q = lane; q < 32 * 12; q += 32) {
+      const int row = q / 12, c4 = q - row * 12;
+      if (wbase + row < P) {
+        const float* d = wsh + row * GB_SH_ROW + c4 * 4;
+        o4[q] = make_float4(d[0], d[1], d[2], d[3]);
+      }
+    }
+  }
 }
 
 template <bool COORD, bool DEPTH>
@@ -893,7 +954,7 @@ int raster_backward(const RasterBwdArgs& a, cudaStream_t stream) {
     err = cudaStreamSynchronize(stream);
     if (err != cudaSuccess) { set_error("[CUDA ERROR] after blend_bwd: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
   }
-  const int threads = 128, blocks = (P + threads - 1) / threads;
+  const int threads = GB_THREADS, blocks = (P + threads - 1) / threads;
 #define ED_GBWD(C_)                                                                                          \
   gaussian_bwd<C_><<<blocks, threads, 0, stream>>>(                                                          \
       P, a.D, a.M, a.means3D, a.radii, a.shs, geom.clamped, a.scales, a.rotations, a.scale_modifier,         \

@@ -33,6 +33,7 @@
 namespace ed3dgs {
 
 constexpr int ROWS_TG = 256;                             // Gaussians per tile = UMMA N
+static_assert(ROWS_TG == 256, "the epilogue assumes four 32-Gaussian blocks per warp");
 constexpr int ROWS_EPI_WARPS = 8;                        // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int ROWS_MMA_WARP = 8;
 constexpr int ROWS_LOAD_WARP = 9;
@@ -73,7 +74,7 @@ __device__ __forceinline__ float4 split_lo(float4 x) {
 // Returns the sum of the values it stored (MASK only: the bias gradient of the layer below).
 template <int LD, bool FULL>
 __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
-                                                    int jmax) {
+                                                    int jmax, uint32_t mword) {
   const long ldc = LD ? LD : bt.ldc;
   const long ldx = LD ? LD : bt.ldaux;
   float* dst = bt.C + g0 * ldc + f;
@@ -103,7 +104,7 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
         if (FULL || j < jmax) dst[j * ldc] = v[j] + b;
     }
   } else if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr) {
-    const uint32_t word = bt.mask_in[(g0 >> 5) * bt.mask_ld + bt.mask_col + f];
+    const uint32_t word = mword;   // loaded by the caller before it waited for the accumulator
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       const float r = ((word >> j) & 1u) ? v[j] : 0.f;
@@ -144,9 +145,9 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
 
 template <int LD>
 __device__ __forceinline__ float rows_epilogue_dispatch(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
-                                                        int jmax) {
-  if (jmax == 32) return rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32);
-  return rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax);
+                                                        int jmax, uint32_t mword) {
+  if (jmax == 32) return rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32, mword);
+  return rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax, mword);
 }
 
 // Step word (TcArgs::steps): batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
@@ -349,13 +350,29 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
       for (int o = 0; o < p.nbatch; ++o, ++go) {
         const TcBatch& bt = p.b[o];
         const int buf = go & 1;
+        // ReLU-mask words of this warp's four blocks: a dependent global load per block otherwise (the dZ
+        // launches, K = 16 per head, are epilogue-latency bound); issued before the accumulator wait
+        uint32_t mw[ROWS_TG / 64] = {};
+        if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr && f < bt.n_valid) {
+#pragma unroll
+          for (int i = 0; i < ROWS_TG / 64; ++i) {
+            long g0 = tile * ROWS_TG + (par + 2 * i) * 32;
+            if (g0 < (long)p.M) {
+              if (p.dbg & 64) g0 &= 16383;
+              mw[i] = __ldg(bt.mask_in + (g0 >> 5) * bt.mask_ld + bt.mask_col + f);
+            }
+          }
+        }
         mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
         tc_fence_after();
         if (q * 32 < bt.n_valid) {
           const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
           const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
           float colsum = 0.f;
-          for (int blk = par; blk < ROWS_TG / 32; blk += 2) {
+#pragma unroll 1
+          for (int bi = 0; bi < ROWS_TG / 64; ++bi) {
+            const int blk = par + 2 * bi;
+            const uint32_t mword = bi == 0 ? mw[0] : (bi == 1 ? mw[1] : (bi == 2 ? mw[2] : mw[3]));
             long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
             if (jmax <= 0) break;
@@ -363,9 +380,9 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
             if (f < bt.n_valid && !(p.dbg & 16)) {
-              if (ld_case == 640) colsum += rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax);
-              else if (ld_case == 128) colsum += rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax);
-              else colsum += rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax);
+              if (ld_case == 640) colsum += rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax, mword);
+              else if (ld_case == 128) colsum += rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax, mword);
+              else colsum += rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax, mword);
             }
           }
           // column sums of a masked gradient = bias gradient of the layer that produced the mask

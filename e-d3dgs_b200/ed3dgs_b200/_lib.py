@@ -53,6 +53,10 @@ def _declare(lib):
     lib.ed3dgs_dist_cuda2.argtypes = [c_int, P, P, P, c_size_t, c_void_p]
     lib.ed3dgs_compute_3d_filter.restype = c_int
     lib.ed3dgs_compute_3d_filter.argtypes = [c_int, P, c_int, P, c_float, P, P, POINTER(c_int), c_void_p]
+    lib.ed3dgs_activations_forward.restype = c_int
+    lib.ed3dgs_activations_forward.argtypes = [c_int] + [P] * 7 + [c_void_p]
+    lib.ed3dgs_activations_backward.restype = c_int
+    lib.ed3dgs_activations_backward.argtypes = [c_int] + [P] * 10 + [c_void_p]
     lib.ed3dgs_ssim_l1_forward.restype = c_int
     lib.ed3dgs_ssim_l1_forward.argtypes = [c_int, c_int, c_int, P, P, P, P, c_void_p]
     lib.ed3dgs_ssim_l1_backward.restype = c_int

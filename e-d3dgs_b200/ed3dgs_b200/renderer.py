@@ -9,6 +9,7 @@ from types import SimpleNamespace
 import torch
 import torch.nn as nn
 
+from .activations import gaussian_activations
 from .deformation import deform_network
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 
@@ -43,6 +44,7 @@ class GaussianScene(nn.Module):
         self._embedding = nn.Parameter(g["embedding"].clone())
         self.register_buffer("tongue_class", g["tongue_class"].clone())
         self.filter_3D = None
+        self.fused_activations = True   # csrc/activations.cu instead of the torch statements (same values)
         self._deformation = deform_network(W=hyper.net_width, D=hyper.defor_depth,
                                            min_embeddings=hyper.min_embeddings, max_embeddings=hyper.max_embeddings,
                                            num_frames=hyper.total_num_frames, args=hyper)
@@ -115,12 +117,18 @@ def render(viewpoint_camera, pc, pipe, bg_color, kernel_size, scaling_modifier=1
     means3D_final, scales_final, rotations_final, opacity_final, shs_final, extras = pc._deformation(
         means3D, scales, rotations, opacity, time, cam_no, pc, None, shs, iter=iter, num_down_emb_c=num_down_emb_c,
         num_down_emb_f=num_down_emb_f)
-    rotations_final = pc.rotation_activation(rotations_final)
-    if disable_filter3D:
-        scales_final = pc.scaling_activation(scales_final)
-        opacity = pc.opacity_activation(opacity_final)
+    if getattr(pc, "fused_activations", False):
+        # same values as the statements below, one kernel each way (csrc/activations.cu)
+        scales_final, rotations_final, opacity = gaussian_activations(
+            scales_final, rotations_final, opacity_final, None if disable_filter3D else pc.filter_3D)
     else:
-        scales_final, opacity = pc.apply_scaling_n_opacity_with_3D_filter(opacity=opacity_final, scales=scales_final)
+        rotations_final = pc.rotation_activation(rotations_final)
+        if disable_filter3D:
+            scales_final = pc.scaling_activation(scales_final)
+            opacity = pc.opacity_activation(opacity_final)
+        else:
+            scales_final, opacity = pc.apply_scaling_n_opacity_with_3D_filter(opacity=opacity_final,
+                                                                              scales=scales_final)
     outputs = rasterizer(means3D=means3D_final, means2D=means2D, shs=shs_final if override_color is None else None,
                          colors_precomp=override_color, opacities=opacity, tongue_class=pc.tongue_class,
                          scales=scales_final, rotations=rotations_final, cov3D_precomp=None)

@@ -180,6 +180,25 @@ int ed3dgs_compute_3d_filter(int P, const float* xyz, int num_cameras, const flo
                              float* filter_3d, void* scratch, int* any_valid, void* stream);
 
 /*
+ * Per-Gaussian activations between the deformation network and the rasterizer, fused.
+ * Replaces the torch statements of gaussian_renderer/__init__.py:77-83: rotation_activation = F.normalize
+ * (eps 1e-12), scaling_activation = exp, opacity_activation = sigmoid (scene/gaussian_model.py:37-45) and, when
+ * filter_3d != NULL, GaussianModel.apply_scaling_n_opacity_with_3D_filter (scene/gaussian_model.py:594-603):
+ * scales = sqrt(exp(s)^2 + f^2), opacity = sigmoid(o) * sqrt(prod exp(s)^2 / prod (exp(s)^2 + f^2)).
+ *   scales[P,3], rotations[P,4], opacity[P] (the reference's [P,1]), filter_3d[P] or NULL: raw (pre-activation)
+ *   *_out: activated values, fully written.
+ * Backward: g_* = gradients w.r.t. the activated values (any may be NULL = zero), d_* = gradients w.r.t. the raw
+ * inputs, fully written; everything is recomputed from the raw inputs (nothing saved by the forward).
+ */
+int ed3dgs_activations_forward(int P, const float* scales, const float* rotations, const float* opacity,
+                               const float* filter_3d, float* scales_out, float* rotations_out, float* opacity_out,
+                               void* stream);
+int ed3dgs_activations_backward(int P, const float* scales, const float* rotations, const float* opacity,
+                                const float* filter_3d, const float* g_scales, const float* g_rotations,
+                                const float* g_opacity, float* d_scales, float* d_rotations, float* d_opacity,
+                                void* stream);
+
+/*
  * Image losses either side of the rasterizer, fused.
  *
  * L1 + SSIM of utils/loss_utils.py:24-72 (`l1_loss`, `ssim` with the 11x11 sigma-1.5 window and zero padding;

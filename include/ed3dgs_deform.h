@@ -80,7 +80,8 @@ int ed3dgs_deform_forward(const ed3dgs_deform_weights* coarse, const ed3dgs_defo
 
 /*
  * Backward of both stages.
- *   d_out[h]: dL/d out[h] (NULL = zero); d_sub[h]: extra dL/d sub[h] (NULL = zero).
+ *   d_out[h]: dL/d out[h] (NULL = zero); d_sub[h]: extra dL/d sub[h] (NULL = zero). The rotation and rgb rows
+ *   (h = 2, 4) are read as float4: those pointers must be 16-byte aligned (ED3DGS_ERR_ARG otherwise).
  *   Writes d_embedding[N, gemb_dim], d_tau_c[temb_dim], d_tau_f[temb_dim]; accumulates weight
  *   gradients into g_coarse / g_fine. The gradient w.r.t. in[h] is d_out[h] + d_sub[h]
  *   (identity path) and is left to the caller.
