@@ -350,29 +350,27 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
       for (int o = 0; o < p.nbatch; ++o, ++go) {
         const TcBatch& bt = p.b[o];
         const int buf = go & 1;
-        // ReLU-mask words of this warp's four blocks: a dependent global load per block otherwise (the dZ
-        // launches, K = 16 per head, are epilogue-latency bound); issued before the accumulator wait
-        uint32_t mw[ROWS_TG / 64] = {};
-        if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr && f < bt.n_valid) {
-#pragma unroll
-          for (int i = 0; i < ROWS_TG / 64; ++i) {
-            long g0 = tile * ROWS_TG + (par + 2 * i) * 32;
-            if (g0 < (long)p.M) {
-              if (p.dbg & 64) g0 &= 16383;
-              mw[i] = __ldg(bt.mask_in + (g0 >> 5) * bt.mask_ld + bt.mask_col + f);
-            }
-          }
-        }
+        // ReLU-mask word of the next block, loaded one block ahead (the first one before the accumulator wait):
+        // a dependent global load per block otherwise, and the dZ launches (K = 16 per head) are
+        // epilogue-latency bound
+        const bool use_mask = p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr && f < bt.n_valid;
+        auto mask_word = [&](int blk) -> uint32_t {
+          long g0 = tile * ROWS_TG + blk * 32;
+          if (!use_mask || g0 >= (long)p.M) return 0u;
+          if (p.dbg & 64) g0 &= 16383;
+          return __ldg(bt.mask_in + (g0 >> 5) * bt.mask_ld + bt.mask_col + f);
+        };
+        uint32_t mnext = mask_word(par);
         mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
         tc_fence_after();
         if (q * 32 < bt.n_valid) {
           const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
           const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
           float colsum = 0.f;
-#pragma unroll 1
           for (int bi = 0; bi < ROWS_TG / 64; ++bi) {
             const int blk = par + 2 * bi;
-            const uint32_t mword = bi == 0 ? mw[0] : (bi == 1 ? mw[1] : (bi == 2 ? mw[2] : mw[3]));
+            const uint32_t mword = mnext;
+            if (bi + 1 < ROWS_TG / 64) mnext = mask_word(blk + 2);
             long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
             if (jmax <= 0) break;

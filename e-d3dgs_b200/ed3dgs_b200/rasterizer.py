@@ -33,10 +33,21 @@ class _Buffer:
         self.device = device
         self.callback = _lib.ALLOC_FN(self._resize)
 
+    @staticmethod
+    def _bucket(nbytes):
+        """Requests above 1 MiB are rounded up to eight steps per octave (<= 12.5 % slack). The instance count, and
+        with it the binning buffer, changes with every view; bucketed sizes let torch's caching allocator hand
+        the same blocks back instead of calling cudaMalloc (a multi-millisecond stall) whenever a view needs a
+        few bytes more than any earlier one."""
+        if nbytes <= (1 << 20):
+            return nbytes
+        step = 1 << max(0, int(nbytes - 1).bit_length() - 4)   # 1/8 of the enclosing octave's lower bound
+        return (nbytes + step - 1) // step * step
+
     def _resize(self, _user, nbytes):
         try:
             if self.tensor.numel() < nbytes:
-                self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+                self.tensor = torch.empty(self._bucket(int(nbytes)), dtype=torch.uint8, device=self.device)
             return self.tensor.data_ptr()
         except Exception:  # noqa: BLE001 - must not propagate through the C frame
             return None
