@@ -48,6 +48,64 @@ def load_peaks():
     return dict(hbm_gbs=6650.0, tensor_tflops=1400.0, source="fallback")
 
 
+class SmiClockSampler:
+    """Same report as ClockSampler, sampled by an `nvidia-smi -lms 250` child process (the profiling recipe's own
+    line) started before the warm-up, so that its driver attach is outside the timed region; its csv rows carry
+    wall-clock timestamps and only rows between mark_begin() and mark_end() are reported."""
+
+    def __init__(self, gpu_index):
+        import subprocess
+        import tempfile
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[0].isdigit() else gpu_index
+        self.out = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.t0 = self.t1 = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(idx), "--query-gpu=timestamp,clocks.sm,clocks.max.sm,"
+                 "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                 "--format=csv,noheader,nounits", "-lms", "250"], stdout=self.out, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
+    def stop(self):
+        import datetime
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        self.out.flush()
+        self.out.seek(0)
+        rows = []
+        for ln in self.out.read().splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(f[1]), float(f[2]), f[3:7]))
+            except (ValueError, IndexError):
+                continue
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        inside = [r for r in rows if self.t0 is not None and self.t0 <= r[0] <= (self.t1 or 1e30)]
+        if not inside and rows:
+            inside = sorted(rows, key=lambda r: abs(r[0] - (self.t0 or 0)))[:1]
+        if not inside:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no nvidia-smi samples"])
+        sm = sorted(r[1] for r in inside)
+        reasons = sorted({n for r in inside for n, v in zip(names, r[3]) if v.lower().startswith("active")})
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=inside[0][2], reasons=reasons, samples=len(sm),
+                    how="nvidia-smi -lms 250 child")
+
+
 class ClockSampler:
     """SM clocks / throttle reasons sampled every 250 ms through NVML (pynvml) from a thread of this process
     (every NVML query takes a driver lock that delays kernel launches by a millisecond or more, so the polling
@@ -336,7 +394,9 @@ def run_ours(args, rank, local, world):
             dist.barrier()
         torch.cuda.synchronize()
 
-    sampler = ClockSampler(local) if rank == 0 else None
+    # BENCH_CLOCKS = thread (NVML from a thread of this process) | smi (nvidia-smi child, the recipe's line)
+    sampler_cls = SmiClockSampler if os.environ.get("BENCH_CLOCKS", "thread") == "smi" else ClockSampler
+    sampler = sampler_cls(local) if rank == 0 and os.environ.get("BENCH_CLOCKS") != "off" else None  # off: experiments only
     # untimed, before the W warm-up steps: every distinct view once, so that torch's caching allocator has seen the
     # largest per-view buffer sizes (a cudaMalloc inside the timed region is a multi-millisecond host stall)
     for v in range(n_cams):
@@ -360,13 +420,28 @@ def run_ours(args, rank, local, world):
     barrier()
     if sampler:
         sampler.mark_begin()
+    mallocs0 = torch.cuda.memory_stats(device).get("num_device_alloc", 0)
+    host_t = [time.perf_counter()]
+    trace, trace_rows = bool(os.environ.get("BENCH_TRACE")), []
     ev0.record()
     for i in range(args.steps):
         v = view_of(i)
         step(i, cams_dev[v], gts_dev[v % 4])
+        host_t.append(time.perf_counter())
+        if trace:
+            trace_rows.append((v, torch.cuda.memory_stats(device).get("num_device_alloc", 0),
+                               torch.cuda.memory_reserved(device) >> 20))
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
+    # host-side evidence for the region: per-step issue times (a step contains one blocking read of the instance
+    # count, so host time tracks device time) and cudaMalloc calls made by the caching allocator inside it
+    host_ms = sorted((b - a) * 1e3 for a, b in zip(host_t[:-1], host_t[1:]))
+    host_info = {"step_issue_ms_median": host_ms[len(host_ms) // 2], "step_issue_ms_max": host_ms[-1],
+                 "device_mallocs_in_region": torch.cuda.memory_stats(device).get("num_device_alloc", 0) - mallocs0}
+    if os.environ.get("BENCH_TRACE"):
+        print("view/mallocs/reserved_MiB:", " ".join(f"{a}/{b - mallocs0}/{c}" for a, b, c in trace_rows), file=sys.stderr)
+        print("step issue ms:", " ".join(f"{(b - a) * 1e3:.1f}" for a, b in zip(host_t[:-1], host_t[1:])), file=sys.stderr)
     clocks = None
     if sampler:
         sampler.mark_end()
@@ -382,26 +457,43 @@ def run_ours(args, rank, local, world):
     main_stream = torch.cuda.current_stream(device)
     loss_host = torch.zeros(args.steps + 3, dtype=torch.float32).pin_memory()
 
+    # three device-side staging slots (allocated once: tensors created on a side stream every step made the
+    # caching allocator defer their reuse and cudaMalloc again); slot s is rewritten only after the main stream
+    # has passed the step that last read it
+    NSLOT = 3
+    slots = [{"gt": torch.empty(3, H, W, device=device),
+              "mats": torch.empty(35, device=device),
+              "done": None} for _ in range(NSLOT)]
+    mats_host = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1),
+                            c.camera_center.reshape(-1)]).pin_memory() for c in cams_host]
+
     def prefetch(i):
         v = view_of(i)
+        sl = slots[i % NSLOT]
+        if sl["done"] is not None:
+            copy_stream.wait_event(sl["done"])
         with torch.cuda.stream(copy_stream):
-            cam = cam_to(cams_host[v], device, non_blocking=True)
-            gt = gts_host[v % 4].to(device, non_blocking=True)
+            sl["mats"].copy_(mats_host[v], non_blocking=True)
+            sl["gt"].copy_(gts_host[v % 4], non_blocking=True)
             ready = torch.cuda.Event()
             ready.record(copy_stream)
-        for t in (cam.world_view_transform, cam.full_proj_transform, cam.camera_center, gt):
-            t.record_stream(main_stream)
-        return cam, gt, ready
+        cam = NS(**vars(cams_host[v]))
+        cam.world_view_transform = sl["mats"][0:16].view(4, 4)
+        cam.full_proj_transform = sl["mats"][16:32].view(4, 4)
+        cam.camera_center = sl["mats"][32:35]
+        return cam, sl["gt"], ready, sl
 
     def e2e_loop(n, slot0):
         nxt = prefetch(0)
         for i in range(n):
-            cam, gt, ready = nxt
+            cam, gt, ready, sl = nxt
             if i + 1 < n:
                 nxt = prefetch(i + 1)
             main_stream.wait_event(ready)
             loss = step(i, cam, gt)
             loss_host[slot0 + i].copy_(loss.detach(), non_blocking=True)   # device -> host read of the step's result
+            sl["done"] = torch.cuda.Event()
+            sl["done"].record(main_stream)
 
     e2e_loop(3, args.steps)   # untimed: lets the caching allocator settle on this region's allocation pattern
     barrier()
@@ -505,7 +597,8 @@ def run_ours(args, rank, local, world):
                    "splat_scale": args.splat_scale, "views_per_step": world,
                    "l2_policy": "per-step working set (Gaussian records 64 MB + keys/lists %.0f MB + MLP activations "
                                 "%.1f GB) exceeds the 126 MB L2" % (R * 36 / 1e6, cfg["P"] * 9.9e3 / 1e9),
-                   "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi},
+                   "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi,
+                   "host": host_info},
         "clocks": clocks,
         "e2e": {"value": world * 1e3 / ms_step_e2e, "unit": UNIT, "ms_per_step": ms_step_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,

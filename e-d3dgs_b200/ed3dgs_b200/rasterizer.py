@@ -28,26 +28,39 @@ class _Buffer:
     """Growable uint8 CUDA buffer handed to the C side as a resize callback
     (replaces resizeFunctional, rasterize_points.cu:27-33)."""
 
-    def __init__(self, device):
+    _high_water = {}   # (device, tag) -> largest bucketed request so far
+
+    def __init__(self, device, tag=None):
         self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
         self.device = device
+        self.tag = tag
         self.callback = _lib.ALLOC_FN(self._resize)
 
     @staticmethod
     def _bucket(nbytes):
-        """Requests above 1 MiB are rounded up to eight steps per octave (<= 12.5 % slack). The instance count, and
-        with it the binning buffer, changes with every view; bucketed sizes let torch's caching allocator hand
-        the same blocks back instead of calling cudaMalloc (a multi-millisecond stall) whenever a view needs a
-        few bytes more than any earlier one."""
+        """Requests above 1 MiB are rounded up to eight steps per octave (<= 12.5 % slack)."""
         if nbytes <= (1 << 20):
             return nbytes
         step = 1 << max(0, int(nbytes - 1).bit_length() - 4)   # 1/8 of the enclosing octave's lower bound
         return (nbytes + step - 1) // step * step
 
+    def _size(self, nbytes):
+        """The instance count, and with it the binning buffer, changes with every view. Tagged buffers are
+        requested at the high-water mark of their kind, so every view asks torch's caching allocator for the same
+        block sizes and gets the same blocks back; varying sizes made it split and re-malloc (cudaMalloc is a
+        multi-millisecond host stall in the middle of a step)."""
+        n = self._bucket(int(nbytes))
+        if self.tag is None:
+            return n
+        key = (str(self.device), self.tag)
+        n = max(n, _Buffer._high_water.get(key, 0))
+        _Buffer._high_water[key] = n
+        return n
+
     def _resize(self, _user, nbytes):
         try:
             if self.tensor.numel() < nbytes:
-                self.tensor = torch.empty(self._bucket(int(nbytes)), dtype=torch.uint8, device=self.device)
+                self.tensor = torch.empty(self._size(nbytes), dtype=torch.uint8, device=self.device)
             return self.tensor.data_ptr()
         except Exception:  # noqa: BLE001 - must not propagate through the C frame
             return None
@@ -100,7 +113,7 @@ def rasterize_forward_raw(bg, means3D, colors_precomp, opacities, tongue_class, 
     out_normal, out_depth, out_mdepth = planes[9:12], planes[12:13], planes[13:14]
     out_alpha, out_tongue = planes[14:15], planes[15:16]
     radii = torch.zeros((P,), dtype=torch.int32, device=dev)
-    geom, binning, img = _Buffer(dev), _Buffer(dev), _Buffer(dev)
+    geom, binning, img = _Buffer(dev, "geom"), _Buffer(dev, "binning"), _Buffer(dev, "image")
     rendered = ctypes.c_int(0)
     if P != 0:
         M = sh.shape[1] if sh.numel() != 0 else 0

@@ -84,3 +84,40 @@ def test_activations_refuse_cpu_tensors():
     s, q, o, _ = _inputs(4, torch.device("cpu"))
     with pytest.raises(_lib.Ed3dgsError):
         gaussian_activations(s, q, o, None)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("with_filter", [False, True])
+def test_render_same_with_and_without_fused_activations(with_filter):
+    """The whole step (network -> activations -> rasterizer -> loss -> backward) through renderer.render with
+    the fused kernels and with the reference's torch statements: same images, same parameter gradients."""
+    from types import SimpleNamespace as NS
+    from ed3dgs_b200 import synthetic
+    from ed3dgs_b200.renderer import GaussianScene, default_hyper, render, training_loss
+    dev = torch.device("cuda:0")
+    P, W, H = 6000, 160, 112
+    g = synthetic.make_gaussians(P, splat_scale=1.0, device=dev)
+    cam = synthetic.make_camera(3, 8, W, H, 8200.0 * W / 3208.0 * 3.0, frame=20, frames=150, device=dev)
+    bg = torch.tensor([0.2, 0.1, 0.3], device=dev)
+    gt = torch.rand(3, H, W, device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+    results = []
+    for fused in (True, False):
+        torch.manual_seed(1)
+        scene = GaussianScene(g, default_hyper()).to(dev)
+        scene.fused_activations = fused
+        with torch.no_grad():
+            scene._deformation.weight.mul_(30.0)
+        if with_filter:
+            scene.filter_3D = torch.full((P, 1), 2e-3, device=dev)
+        pkg = render(cam, scene, NS(debug=False), bg, 0.0, require_coord=False, require_depth=True, cam_no=1,
+                     iter=20000, num_down_emb_c=30, num_down_emb_f=30, disable_filter3D=not with_filter)
+        training_loss(pkg, gt, view=cam).backward()
+        results.append((pkg["render"].detach(), pkg["radii"], scene._scaling.grad.clone(), scene._rotation.grad.clone(),
+                        scene._opacity.grad.clone(), scene._embedding.grad.clone()))
+    a, b = results
+    assert int((a[1] != b[1]).sum()) <= 2           # radii: an ulp in a scale can move a ceil()
+    assert float((a[0] - b[0]).abs().max()) < 2e-4
+    for x, y in zip(a[2:], b[2:]):
+        scale = float(y.abs().max()) + 1e-30
+        bad = ((x - y).abs() > 1e-3 * scale + 1e-4 * y.abs()).float().mean()
+        assert float(bad) < 2e-3, float(bad)
