@@ -57,6 +57,12 @@ class _Buffer:
         _Buffer._high_water[key] = n
         return n
 
+    def close(self):
+        """Drops the ctypes callback. It holds a bound method of this object, i.e. a reference cycle that only the
+        cyclic garbage collector would break: until then the buffer (hundreds of MB) stays allocated, and a loop
+        that runs with the collector off or rarely triggered grows by one set of buffers per step."""
+        self.callback = None
+
     def _resize(self, _user, nbytes):
         try:
             if self.tensor.numel() < nbytes:
@@ -128,6 +134,8 @@ def rasterize_forward_raw(bg, means3D, colors_precomp, opacities, tongue_class, 
                 _lib.ptr(out_mdepth), _lib.ptr(out_alpha), _lib.ptr(out_tongue), _lib.ptr(out_normal),
                 _lib.ptr(radii), int(bool(require_coord)), int(bool(require_depth)), int(bool(debug)),
                 _lib.stream_handle(), ctypes.byref(rendered))
+        for b in (geom, binning, img):
+            b.close()
         _lib.check(status)
     return (rendered.value, out_color, out_coord, out_mcoord, out_alpha, out_tongue, out_normal, out_depth,
             out_mdepth, radii, geom.tensor, binning.tensor, img.tensor)
@@ -237,6 +245,8 @@ def integrate_gaussians_to_points_raw(bg, points3D, means3D, colors_precomp, opa
                 _lib.ptr(radii), _lib.ptr(alpha_integrated), _lib.ptr(color_integrated), _lib.ptr(coordinate2d),
                 _lib.ptr(sdf), _lib.ptr(work), work.numel(), int(bool(debug)), _lib.stream_handle(),
                 ctypes.byref(rendered))
+        for b in (geom, binning, img):
+            b.close()
         _lib.check(status)
     else:  # the reference launches nothing and returns its pre-filled tensors (rasterize_points.cu:312-344)
         out_color = torch.zeros((9, H, W), **f32)

@@ -113,3 +113,56 @@ def test_mark_visible():
                                        ref.data_ptr())
     torch.cuda.synchronize()
     assert torch.equal(mine, ref) and 0 < int(mine.sum()) < 4096
+
+
+def test_steps_free_their_buffers_without_the_cyclic_gc():
+    """A training step must release its opaque geometry / binning / image buffers by reference counting alone:
+    with the cyclic collector off (bench.py's timed regions, or any loop where it triggers rarely) a reference
+    cycle through the resize callback kept one set of buffers per step alive (512 MB per step at C3)."""
+    import gc
+    from types import SimpleNamespace as NS
+    from ed3dgs_b200 import synthetic
+    from ed3dgs_b200.renderer import GaussianScene, default_hyper, render, training_loss
+    dev = torch.device("cuda:0")
+    P, W, H = 20000, 320, 240
+    scene = GaussianScene(synthetic.make_gaussians(P, splat_scale=1.0, device=dev), default_hyper()).to(dev)
+    cam = synthetic.make_camera(3, 8, W, H, 8200.0 * W / 3208.0 * 3.0, frame=20, frames=150, device=dev)
+    bg = torch.zeros(3, device=dev)
+    gt = torch.rand(3, H, W, device=dev)
+
+    def step():
+        for p in scene.parameters():
+            p.grad = None
+        pkg = render(cam, scene, NS(debug=False), bg, 0.0, require_coord=False, require_depth=True, cam_no=1,
+                     iter=20000, num_down_emb_c=30, num_down_emb_f=30)
+        training_loss(pkg, gt, view=cam).backward()
+
+    gc.collect()
+    gc.disable()
+    try:
+        step()
+        step()
+        torch.cuda.synchronize()
+        before = torch.cuda.memory_allocated(dev)
+        for _ in range(4):
+            step()
+        torch.cuda.synchronize()
+        after = torch.cuda.memory_allocated(dev)
+    finally:
+        gc.enable()
+    assert after <= before, (before, after)
+
+
+def test_buffer_callback_cycle_is_broken_on_cpu_objects():
+    import gc
+    import weakref
+    from ed3dgs_b200.rasterizer import _Buffer
+    gc.disable()
+    try:
+        b = _Buffer(torch.device("cpu"), "t")
+        r = weakref.ref(b)
+        b.close()
+        del b
+        assert r() is None
+    finally:
+        gc.enable()
