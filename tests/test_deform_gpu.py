@@ -183,3 +183,50 @@ def test_state_dict_keys_match_reference_names():
     assert set(net.state_dict().keys()) == set(rec["state"].keys())
     assert all(n != "offsets" for n, _ in zip(["x"], net.get_mlp_parameters()))
     assert len(net.get_mlp_parameters()) == len(list(net.parameters())) - 1
+
+
+def test_full_c3_size_rows_match_fp64_oracle():
+    """BASELINE's C3 size (1 M Gaussians, ragged by 3): the network is row-independent, so 4 096 oracle rows are
+    scattered into a 1 000 003-row problem (first tile, last ragged tile, random positions) and the product's
+    outputs and per-row input gradients at those positions must match the fp64 oracle of the small problem."""
+    from ed3dgs_b200.deformation import deform_network
+    n_s, N = 4096, 1_000_003
+    rec = oracle_record(N=n_s, kink_free=True, seed=11)
+    c, args = rec["case"], NS(**rec["args"])
+    g = torch.Generator().manual_seed(3)
+    pos = torch.cat([torch.arange(0, 300), torch.arange(N - 300, N),
+                     torch.randperm(N - 600, generator=g)[:n_s - 600] + 300])
+    assert pos.unique().numel() == n_s
+    dev = "cuda"
+    net = deform_network(D=c["D"], W=c["W"], min_embeddings=30, max_embeddings=150, num_frames=300, args=args)
+    net.load_state_dict(rec["state"])
+    net = net.to(dev)
+    shapes = dict(point=(N, 3), scales=(N, 3), rotations=(N, 4), opacity=(N, 1), sh=(N, 16, 3), embedding=(N, 32))
+    leaves = {}
+    for k, shp in shapes.items():
+        full = torch.randn(*shp, generator=g) * (0.5 if k == "embedding" else 1.0)
+        full[pos] = rec["inputs"][k]
+        leaves[k] = full.to(dev).requires_grad_(True)
+    ups = {}
+    for i, shp in enumerate([(N, 3), (N, 3), (N, 4), (N, 1), (N, 16, 3)]):
+        for kind, sc in (("w_out", 1.0), ("w_sub", 0.3)):
+            full = torch.randn(*shp, generator=g) * sc
+            full[pos] = rec["upstream"][f"{kind}{i}"]
+            ups[f"{kind}{i}"] = full.to(dev)
+    time_emb = torch.tensor(c["t"], device=dev).repeat(N, 1)
+    out = net(leaves["point"], leaves["scales"], leaves["rotations"], leaves["opacity"], time_emb, c["cam_no"],
+              NS(get_embedding=leaves["embedding"]), None, leaves["sh"], iter=c["it"], num_down_emb_c=30,
+              num_down_emb_f=30)
+    finals, (subs, _o) = out[:5], out[5]
+    loss = 0
+    for i, (a, b) in enumerate(zip(finals, subs)):
+        loss = loss + (a * ups[f"w_out{i}"]).sum() + (b * ups[f"w_sub{i}"]).sum()
+    loss.backward()
+    torch.cuda.synchronize()
+    p = pos.to(dev)
+    for a, b in zip(list(finals) + list(subs), rec["finals"] + rec["subs"]):
+        assert _rel(a[p], b) <= OUT_TOL
+    for k, gref in rec["grads_in"].items():
+        assert _rel(leaves[k].grad[p], gref) <= GRAD_TOL, k
+    for k in leaves:
+        assert torch.isfinite(leaves[k].grad).all()
