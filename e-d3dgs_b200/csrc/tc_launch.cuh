@@ -60,6 +60,19 @@ inline tc_encode_tiled_fn tc_encode_tiled() {
   return fn;
 }
 
+template <int EPI>
+inline cudaError_t tc_rows_run(const TcArgs& a, int grid, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    const cudaError_t e =
+        cudaFuncSetAttribute(tc_rows_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  tc_rows_kernel<EPI><<<grid, ROWS_THREADS, ROWS_SMEM_BYTES, stream>>>(a);
+  return cudaGetLastError();
+}
+
 inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stream) {
   if ((a.lda & 3) || !tc_rows_build(a)) return cudaErrorInvalidValue;
   for (int i = 0; i < a.nbatch; ++i)
@@ -84,16 +97,15 @@ inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stre
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
   }
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
   const int grid = a.ntiles < tc_sm_count() ? a.ntiles : tc_sm_count();
   ProfScope ps(name, stream);
-  tc_rows_kernel<<<grid, ROWS_THREADS, ROWS_SMEM_BYTES, stream>>>(a);
-  return cudaGetLastError();
+  switch (a.epilogue) {
+    case TC_EPI_BIAS_ACT: return tc_rows_run<TC_EPI_BIAS_ACT>(a, grid, stream);
+    case TC_EPI_MASK: return tc_rows_run<TC_EPI_MASK>(a, grid, stream);
+    case TC_EPI_ACCUM: return tc_rows_run<TC_EPI_ACCUM>(a, grid, stream);
+    case TC_EPI_HEAD: return tc_rows_run<TC_EPI_HEAD>(a, grid, stream);
+    default: return cudaErrorInvalidValue;
+  }
 }
 
 // Weight gradients: D = P^T Q over all Gaussians, scattered into the gradient matrices (tc_wgrad.cuh).

@@ -72,14 +72,14 @@ __device__ __forceinline__ float4 split_lo(float4 x) {
 // LD > 0: compile-time row stride of C (and of aux), so every access is base + immediate.
 // FULL: all 32 Gaussians of the block exist (no per-row predicate).
 // Returns the sum of the values it stored (MASK only: the bias gradient of the layer below).
-template <int LD, bool FULL>
+template <int LD, bool FULL, int EPI>
 __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
                                                     int jmax, uint32_t mword) {
   const long ldc = LD ? LD : bt.ldc;
   const long ldx = LD ? LD : bt.ldaux;
   float* dst = bt.C + g0 * ldc + f;
   float csum = 0.f;
-  if (p.epilogue == TC_EPI_BIAS_ACT) {
+  if constexpr (EPI == TC_EPI_BIAS_ACT) {
     const float b = bt.bias != nullptr ? __ldg(bt.bias + f) : 0.f;
     if (p.relu) {
       if (bt.mask_out != nullptr) {
@@ -103,7 +103,7 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
       for (int j = 0; j < 32; ++j)
         if (FULL || j < jmax) dst[j * ldc] = v[j] + b;
     }
-  } else if (p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr) {
+  } else if (EPI == TC_EPI_MASK && bt.mask_in != nullptr) {
     const uint32_t word = mword;   // loaded by the caller before it waited for the accumulator
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -113,23 +113,23 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
   } else {
     // the three other epilogues read one value per output first; a clamped row index keeps the
     // loads unconditional, so they stay batched ahead of the stores
-    const float* src = (p.epilogue == TC_EPI_ACCUM) ? dst : (bt.aux + g0 * ldx + f);
-    const long lds = (p.epilogue == TC_EPI_ACCUM) ? ldc : ldx;
+    const float* src = (EPI == TC_EPI_ACCUM) ? dst : (bt.aux + g0 * ldx + f);
+    const long lds = (EPI == TC_EPI_ACCUM) ? ldc : ldx;
     float o[32];
-    if (p.epilogue == TC_EPI_ACCUM && !p.accumulate) {
+    if (EPI == TC_EPI_ACCUM && !p.accumulate) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) o[j] = 0.f;
     } else {
 #pragma unroll
       for (int j = 0; j < 32; ++j) o[j] = src[(FULL ? j : min(j, jmax - 1)) * lds];
     }
-    if (p.epilogue == TC_EPI_MASK) {
+    if (EPI == TC_EPI_MASK) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         const float r = o[j] > 0.f ? v[j] : 0.f;
         if (FULL || j < jmax) { dst[j * ldc] = r; csum += r; }
       }
-    } else if (p.epilogue == TC_EPI_ACCUM) {
+    } else if (EPI == TC_EPI_ACCUM) {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (FULL || j < jmax) dst[j * ldc] = o[j] + v[j];
@@ -143,11 +143,11 @@ __device__ __forceinline__ float rows_epilogue_block(const TcArgs& p, const TcBa
   return csum;
 }
 
-template <int LD>
+template <int LD, int EPI>
 __device__ __forceinline__ float rows_epilogue_dispatch(const TcArgs& p, const TcBatch& bt, const float* v, int f, long g0,
                                                         int jmax, uint32_t mword) {
-  if (jmax == 32) return rows_epilogue_block<LD, true>(p, bt, v, f, g0, 32, mword);
-  return rows_epilogue_block<LD, false>(p, bt, v, f, g0, jmax, mword);
+  if (jmax == 32) return rows_epilogue_block<LD, true, EPI>(p, bt, v, f, g0, 32, mword);
+  return rows_epilogue_block<LD, false, EPI>(p, bt, v, f, g0, jmax, mword);
 }
 
 // Step word (TcArgs::steps): batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24
@@ -178,6 +178,9 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, in
       : "memory");
 }
 
+// EPI (TC_EPI_*) is a template parameter: the epilogue is a 32-fold unrolled block per kind, and a run-time switch kept
+// the registers of all kinds alive in every launch.
+template <int EPI>
 __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_constant__ TcArgs p) {
   extern __shared__ __align__(128) unsigned char rows_smem_raw[];
   __shared__ RowsBars bars;
@@ -350,27 +353,29 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
       for (int o = 0; o < p.nbatch; ++o, ++go) {
         const TcBatch& bt = p.b[o];
         const int buf = go & 1;
-        // ReLU-mask word of the next block, loaded one block ahead (the first one before the accumulator wait):
-        // a dependent global load per block otherwise, and the dZ launches (K = 16 per head) are
-        // epilogue-latency bound
-        const bool use_mask = p.epilogue == TC_EPI_MASK && bt.mask_in != nullptr && f < bt.n_valid;
+        // ReLU-mask words, loaded before the accumulator wait: a dependent global load per block otherwise, and
+        // the dZ launches (K = 16 per head) are epilogue-latency bound
+        const bool use_mask = EPI == TC_EPI_MASK && bt.mask_in != nullptr && f < bt.n_valid;
         auto mask_word = [&](int blk) -> uint32_t {
           long g0 = tile * ROWS_TG + blk * 32;
           if (!use_mask || g0 >= (long)p.M) return 0u;
           if (p.dbg & 64) g0 &= 16383;
           return __ldg(bt.mask_in + (g0 >> 5) * bt.mask_ld + bt.mask_col + f);
         };
-        uint32_t mnext = mask_word(par);
+        // the mask kind has registers to spare: all four words of this warp's blocks before the wait
+        uint32_t mnext = 0u, mw1 = 0u, mw2 = 0u, mw3 = 0u;
+        if constexpr (EPI == TC_EPI_MASK) {
+          mnext = mask_word(par); mw1 = mask_word(par + 2); mw2 = mask_word(par + 4); mw3 = mask_word(par + 6);
+        }
         mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
         tc_fence_after();
         if (q * 32 < bt.n_valid) {
-          const bool same_ld = (p.epilogue == TC_EPI_BIAS_ACT || p.epilogue == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
+          const bool same_ld = (EPI == TC_EPI_BIAS_ACT || EPI == TC_EPI_ACCUM || bt.ldaux == bt.ldc);
           const int ld_case = !same_ld ? 0 : (bt.ldc == 640 ? 640 : (bt.ldc == 128 ? 128 : 0));
           float colsum = 0.f;
           for (int bi = 0; bi < ROWS_TG / 64; ++bi) {
             const int blk = par + 2 * bi;
-            const uint32_t mword = mnext;
-            if (bi + 1 < ROWS_TG / 64) mnext = mask_word(blk + 2);
+            const uint32_t mword = bi == 0 ? mnext : (bi == 1 ? mw1 : (bi == 2 ? mw2 : mw3));
             long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
             if (jmax <= 0) break;
@@ -378,13 +383,13 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
             if (f < bt.n_valid && !(p.dbg & 16)) {
-              if (ld_case == 640) colsum += rows_epilogue_dispatch<640>(p, bt, v, f, g0, jmax, mword);
-              else if (ld_case == 128) colsum += rows_epilogue_dispatch<128>(p, bt, v, f, g0, jmax, mword);
-              else colsum += rows_epilogue_dispatch<0>(p, bt, v, f, g0, jmax, mword);
+              if (ld_case == 640) colsum += rows_epilogue_dispatch<640, EPI>(p, bt, v, f, g0, jmax, mword);
+              else if (ld_case == 128) colsum += rows_epilogue_dispatch<128, EPI>(p, bt, v, f, g0, jmax, mword);
+              else colsum += rows_epilogue_dispatch<0, EPI>(p, bt, v, f, g0, jmax, mword);
             }
           }
           // column sums of a masked gradient = bias gradient of the layer that produced the mask
-          if (p.epilogue == TC_EPI_MASK && bt.bias_grad != nullptr && f < bt.n_valid) atomicAdd(bt.bias_grad + f, colsum);
+          if (EPI == TC_EPI_MASK && bt.bias_grad != nullptr && f < bt.n_valid) atomicAdd(bt.bias_grad + f, colsum);
         }
         tc_fence_before();
         mbar_arrive(&bars.acc_free[buf]);
