@@ -13,6 +13,8 @@
 #include "tc_gemm.cuh"
 #include "profiler.h"
 #include "tc_launch.cuh"
+#include "fused_mlp.cuh"
+#include <cstdlib>
 
 namespace ed3dgs {
 
@@ -277,6 +279,14 @@ struct DeformWork {
   // ReLU masks as bits: one word per (block of 32 Gaussians, feature)
   uint32_t* Mr[2][ED3DGS_DEFORM_MAX_DEPTH];  // trunk layers: [ceil(N/32)][W]
   uint32_t* Mz[2];                           // head hidden layers: [ceil(N/32)][5W]
+  // stage-resident path (fused_mlp.cuh): feature-major activations, both mask layouts, weight slab images
+  long npad;
+  float* zT[2];                              // [5*128][npad]
+  float* hT[2];                              // [128][npad]
+  uint32_t* Mg[2];                           // [npad][5][4]
+  uint32_t* MgH[2];                          // [npad][4]
+  uint32_t* Mf[2];                           // [npad/32][5*128]
+  float* wimg[2];                            // forward slab images of a stage
 };
 
 static inline void carve_f(char*& p, float*& out, size_t count) {
@@ -307,6 +317,19 @@ static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
   carve_f(p, w.Wpack, (size_t)5 * W * W);
   carve_f(p, w.Wprep, tc_prep_scratch_floats());
   carve_f(p, w.dc1, W);
+  if (W == 128 && depth == 1) {
+    const size_t npad = (N + FM_TG - 1) / FM_TG * FM_TG;
+    w.npad = (long)npad;
+    for (int s = 0; s < 2; ++s) {
+      float* t;
+      carve_f(p, w.zT[s], 5 * 128 * npad);
+      carve_f(p, w.hT[s], 128 * npad);
+      carve_f(p, t, npad * 5 * 4); w.Mg[s] = reinterpret_cast<uint32_t*>(t);
+      carve_f(p, t, npad * 4); w.MgH[s] = reinterpret_cast<uint32_t*>(t);
+      carve_f(p, t, npad / 32 * 5 * 128); w.Mf[s] = reinterpret_cast<uint32_t*>(t);
+      carve_f(p, w.wimg[s], (size_t)FM_MAX_SLABS * FM_W_SLOT_BYTES / 4);
+    }
+  }
   return w;
 }
 
@@ -347,10 +370,102 @@ static int active_heads(const ed3dgs_deform_weights* w, int* list) {
   return n;
 }
 
+// The stage-resident kernels cover the shape every dataset config uses; anything else takes the layered path.
+// ED3DGS_DEFORM_FUSED=0 forces the layered path (A/B timing, tests of the layered kernels).
+static bool fused_shape(const ed3dgs_deform_weights* w) {
+  static const int enabled = [] { const char* e = getenv("ED3DGS_DEFORM_FUSED"); return e ? atoi(e) : 1; }();
+  return enabled && w && w->W == 128 && w->depth == 1 && w->gemb_dim == 32;
+}
+
+static cudaError_t fused_func_attr(const void* fn, size_t smem) {
+  // per-device attribute: set on every launch (a cached flag would be wrong on the second GPU of a process)
+  return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+static int current_sm_count() {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+    sms = 148;
+  return sms;
+}
+
+// Forward of one stage in one launch (fused_mlp.cuh).
+static int stage_forward_fused(const ed3dgs_deform_weights* w, int s, int N, const float* emb, const float* tau,
+                               const float* const base[5], float* const dst[5], const float coef[5], DeformWork& wk,
+                               cudaStream_t stream) {
+  const int temb = w->temb_dim, gemb = w->gemb_dim;
+  const long ld0 = temb + gemb;
+  layer0_temporal_bias<<<(128 + 3) / 4, 128, 0, stream>>>(w->feat_w[0], w->feat_b[0], ld0, temb, tau, wk.c1[s], 128);
+  int act[5];
+  const int na = active_heads(w, act);
+  const bool has_rgb = w->head_w1[4] != nullptr;   // the rgb head is the last active slot
+  // weight slab images: layer 0 (2), hidden layers (8 per slot), rgb output layer (8, 48 rows)
+  PrepArgs pa{};
+  FusedFwdArgs fa{};
+  int ns = 0;
+  uint32_t off = 0;
+  auto add = [&](const float* src, long ld, int n_valid, int NT, int K) {
+    for (int k0 = 0; k0 < K; k0 += 16) {
+      pa.s[ns] = PrepSlab{src, ld, TC_K_MAJOR, n_valid, NT, k0, K, off};
+      fa.slab_off[ns] = off;
+      off += (uint32_t)NT * 8u;
+      ++ns;
+    }
+  };
+  add(w->feat_w[0] + temb, ld0, 128, 128, gemb);
+  for (int i = 0; i < na; ++i) add(w->head_w1[act[i]], 128, 128, 128, 128);
+  if (has_rgb) add(w->head_w2[4], 128, 48, 48, 128);
+  pa.dst = reinterpret_cast<float4*>(wk.wimg[s]);
+  {
+    ProfScope ps("fused_prepare", stream);
+    fused_prepare<<<ns, 128, 0, stream>>>(pa);
+  }
+  fa.wimg = reinterpret_cast<const float4*>(wk.wimg[s]);
+  fa.na = na; fa.has_rgb = has_rgb ? 1 : 0; fa.N = N; fa.npad = wk.npad;
+  fa.c1 = wk.c1[s];
+  for (int i = 0; i < na; ++i) {
+    const int h = act[i];
+    fa.b1[i] = w->head_b1[h]; fa.w2[i] = w->head_w2[h]; fa.b2[i] = w->head_b2[h];
+    fa.hdim[i] = hHeadDim[h]; fa.base[i] = base[h]; fa.dst[i] = dst[h]; fa.coef[i] = coef[h];
+    if (h == 4 && ((reinterpret_cast<uintptr_t>(base[h]) | reinterpret_cast<uintptr_t>(dst[h])) & 15u)) {
+      set_error("deform_forward: the rgb rows must be 16-byte aligned");
+      return ED3DGS_ERR_ARG;
+    }
+  }
+  fa.zT = wk.zT[s]; fa.hT = wk.hT[s]; fa.Mg = wk.Mg[s]; fa.MgH = wk.MgH[s]; fa.Mf = wk.Mf[s];
+  tc_encode_tiled_fn enc = tc_encode_tiled();
+  if (!enc || (reinterpret_cast<uintptr_t>(emb) & 15u)) { set_error("deform_forward: tensor map unavailable"); return ED3DGS_ERR_CUDA; }
+  {
+    const cuuint64_t dims[2] = {(cuuint64_t)gemb, (cuuint64_t)N};
+    const cuuint64_t strides[1] = {(cuuint64_t)gemb * sizeof(float)};
+    const cuuint32_t box[2] = {16, (cuuint32_t)FM_TG};
+    const cuuint32_t estr[2] = {1, 1};
+    if (enc(&fa.emap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(emb), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+      set_error("deform_forward: cuTensorMapEncodeTiled failed");
+      return ED3DGS_ERR_CUDA;
+    }
+  }
+  TC_TRY(fused_func_attr(reinterpret_cast<const void*>(fused_fwd_kernel), FM_FWD_SMEM));
+  const int ntiles = (N + FM_TG - 1) / FM_TG;
+  const int sms = current_sm_count();
+  {
+    ProfScope ps("fused_fwd_kernel", stream);
+    fused_fwd_kernel<<<ntiles < sms ? ntiles : sms, FM_THREADS, FM_FWD_SMEM, stream>>>(fa);
+  }
+  TC_TRY(cudaGetLastError());
+  for (int h = 0; h < 5; ++h)
+    if (!w->head_w1[h] && dst[h] != base[h])
+      TC_TRY(cudaMemcpyAsync(dst[h], base[h], (size_t)N * hHeadDim[h] * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  return ED3DGS_OK;
+}
+
 // One stage forward: base[h] -> dst[h] = base[h] + delta_h * coef[h].
+// acts_only: stop after the hidden layers (the activations and ReLU masks the layered backward reads).
 static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const float* emb, const float* tau,
                          const float* const base[5], float* const dst[5], const float coef[5], DeformWork& wk,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, bool acts_only = false) {
   const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
   layer0_temporal_bias<<<(W + 3) / 4, 128, 0, stream>>>(w->feat_w[0], w->feat_b[0], ld0, temb, tau, wk.c1[s], W);
@@ -381,6 +496,7 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
     }
     TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
   }
+  if (acts_only) return ED3DGS_OK;
   {  // head outputs fused with  x = x + delta * coef
     TcArgs a = tc_args(5L * W, W, N, W, 48, TC_EPI_HEAD);
     for (int i = 0; i < na; ++i) {
@@ -572,13 +688,17 @@ int ed3dgs_deform_forward(const ed3dgs_deform_weights* coarse, const ed3dgs_defo
   char* p = static_cast<char*>(workspace);
   DeformWork wk = carve_deform(p, any->W, any->depth, (size_t)N);
   if (coarse) {
-    if ((rc = stage_forward(coarse, 0, N, embedding, tau_c, in, sub, coef, wk, stream))) return rc;
+    if (fused_shape(coarse)) rc = stage_forward_fused(coarse, 0, N, embedding, tau_c, in, sub, coef, wk, stream);
+    else rc = stage_forward(coarse, 0, N, embedding, tau_c, in, sub, coef, wk, stream);
+    if (rc) return rc;
   } else {
     for (int h = 0; h < 5; ++h) cudaMemcpyAsync(sub[h], in[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
   }
   if (fine) {
     const float* base[5] = {sub[0], sub[1], sub[2], sub[3], sub[4]};
-    if ((rc = stage_forward(fine, 1, N, embedding, tau_f, base, out, coef, wk, stream))) return rc;
+    if (fused_shape(fine)) rc = stage_forward_fused(fine, 1, N, embedding, tau_f, base, out, coef, wk, stream);
+    else rc = stage_forward(fine, 1, N, embedding, tau_f, base, out, coef, wk, stream);
+    if (rc) return rc;
   } else {
     for (int h = 0; h < 5; ++h) cudaMemcpyAsync(out[h], sub[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
   }
@@ -630,6 +750,9 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
     Gc = wk.G[0];
     colc = wk.colsum[0];
   }
+  // interim: the stage-resident forward keeps feature-major activations; the layered backward reads row-major ones
+  if (fine && fused_shape(fine) && (rc = stage_forward(fine, 1, N, embedding, tau_f, nullptr, nullptr, coef, wk, stream, true))) return rc;
+  if (coarse && fused_shape(coarse) && (rc = stage_forward(coarse, 0, N, embedding, tau_c, nullptr, nullptr, coef, wk, stream, true))) return rc;
   int accumulate = 0;
   if (fine) {
     if ((rc = stage_backward(fine, g_fine, 1, N, embedding, tau_f, wk.G[1], wk.colsum[1], wk, d_embedding, accumulate,
