@@ -285,8 +285,11 @@ struct DeformWork {
   float* hT[2];                              // [128][npad]
   uint32_t* Mg[2];                           // [npad][5][4]
   uint32_t* MgH[2];                          // [npad][4]
-  uint32_t* Mf[2];                           // [npad/32][5*128]
   float* wimg[2];                            // forward slab images of a stage
+  float* wimg_b;                             // backward slab images (one stage at a time)
+  float* dzT;                                // [tile][5*128][128] gradients of the head hidden layers (one stage at a time)
+  float* dhT;                                // [tile][128][128]
+  float* GT;                                 // [tile][64][128] scaled upstream gradients
 };
 
 static inline void carve_f(char*& p, float*& out, size_t count) {
@@ -326,9 +329,12 @@ static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
       carve_f(p, w.hT[s], 128 * npad);
       carve_f(p, t, npad * 5 * 4); w.Mg[s] = reinterpret_cast<uint32_t*>(t);
       carve_f(p, t, npad * 4); w.MgH[s] = reinterpret_cast<uint32_t*>(t);
-      carve_f(p, t, npad / 32 * 5 * 128); w.Mf[s] = reinterpret_cast<uint32_t*>(t);
       carve_f(p, w.wimg[s], (size_t)FM_MAX_SLABS * FM_W_SLOT_BYTES / 4);
     }
+    carve_f(p, w.wimg_b, (size_t)FM_MAX_SLABS * FM_W_SLOT_BYTES / 4);
+    carve_f(p, w.dzT, 5 * 128 * npad);
+    carve_f(p, w.dhT, 128 * npad);
+    carve_f(p, w.GT, FB_GT_ROWS * npad);
   }
   return w;
 }
@@ -432,7 +438,7 @@ static int stage_forward_fused(const ed3dgs_deform_weights* w, int s, int N, con
       return ED3DGS_ERR_ARG;
     }
   }
-  fa.zT = wk.zT[s]; fa.hT = wk.hT[s]; fa.Mg = wk.Mg[s]; fa.MgH = wk.MgH[s]; fa.Mf = wk.Mf[s];
+  fa.zT = wk.zT[s]; fa.hT = wk.hT[s]; fa.Mg = wk.Mg[s]; fa.MgH = wk.MgH[s];
   tc_encode_tiled_fn enc = tc_encode_tiled();
   if (!enc || (reinterpret_cast<uintptr_t>(emb) & 15u)) { set_error("deform_forward: tensor map unavailable"); return ED3DGS_ERR_CUDA; }
   {
@@ -626,6 +632,128 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   return ED3DGS_OK;
 }
 
+// Backward of one stage on the stage-resident path: one chain kernel (dz, dh, dE, bias gradients, feature-major
+// gradient matrices) and three weight-gradient launches that contract those matrices over the Gaussians.
+static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
+                                const float* emb, const float* tau, const float* const d_out[5],
+                                const float* const d_sub[5], int use_sub, const float coef[5], DeformWork& wk,
+                                float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
+  const int temb = w->temb_dim, gemb = w->gemb_dim;
+  const long ld0 = temb + gemb;
+  int act[5];
+  const int na = active_heads(w, act);
+  const bool has_rgb = w->head_w1[4] != nullptr;
+  TC_TRY(cudaMemsetAsync(wk.dc1, 0, 128 * sizeof(float), stream));
+
+  // slab images in the order the chain kernel's MMA warp walks them (see fused_bwd_kernel)
+  PrepArgs pa{};
+  FusedBwdArgs ba{};
+  int nimg = 0;
+  uint32_t off = 0;
+  auto add_img = [&](const float* src, long ld, int n_valid, int NT, int k0, int kvalid) -> uint32_t {
+    pa.s[nimg] = PrepSlab{src, ld, TC_MN_MAJOR, n_valid, NT, k0, kvalid, off};
+    const uint32_t at = off;
+    off += (uint32_t)NT * 8u;
+    ++nimg;
+    return at;
+  };
+  uint32_t w1t[5][8], w2t[2][3], w0t[8];
+  for (int i = 0; i < na; ++i)
+    for (int sl = 0; sl < 8; ++sl) w1t[i][sl] = add_img(w->head_w1[act[i]], 128, 128, 128, sl * 16, 128);   // rows k, K = f
+  if (has_rgb)
+    for (int hf = 0; hf < 2; ++hf)
+      for (int sl = 0; sl < 3; ++sl) w2t[hf][sl] = add_img(w->head_w2[4] + hf * 64, 128, 64, 64, sl * 16, 48);  // rows f, K = o
+  for (int sl = 0; sl < 8; ++sl) w0t[sl] = add_img(w->feat_w[0] + temb, ld0, gemb, 32, sl * 16, 128);           // rows j, K = k
+  pa.dst = reinterpret_cast<float4*>(wk.wimg_b);
+  {
+    ProfScope ps("fused_prepare", stream);
+    fused_prepare<<<nimg, 128, 0, stream>>>(pa);
+  }
+  int nseq = 0;
+  auto push = [&](uint32_t at, int NT) { ba.seq_off[nseq] = at; ba.seq_bytes[nseq] = (uint16_t)(NT * 128); ++nseq; };
+  const int nunits = 2 * na;
+  for (int uu = 0; uu < nunits; ++uu) {
+    if (has_rgb && uu + 1 < nunits && ((uu + 1) >> 1) == na - 1)
+      for (int sl = 0; sl < 3; ++sl) push(w2t[(uu + 1) & 1][sl], 64);
+    for (int sl = 0; sl < 4; ++sl) push(w1t[uu >> 1][(uu & 1) * 4 + sl], 128);
+  }
+  for (int sl = 0; sl < 8; ++sl) push(w0t[sl], 32);
+  ba.nseq = nseq;
+  ba.wimg = reinterpret_cast<const float4*>(wk.wimg_b);
+  ba.na = na; ba.has_rgb = has_rgb ? 1 : 0; ba.N = N;
+  ba.use_sub = use_sub; ba.accumulate_emb = accumulate_emb; ba.store_dz = 1;
+  int goff = 0;
+  for (int i = 0; i < na; ++i) {
+    const int h = act[i];
+    ba.w2[i] = w->head_w2[h]; ba.hdim[i] = hHeadDim[h]; ba.goff[i] = goff; ba.coef[i] = coef[h];
+    goff += hHeadDim[h];
+    ba.d_out[i] = d_out ? d_out[h] : nullptr;
+    ba.d_sub[i] = d_sub ? d_sub[h] : nullptr;
+    ba.db1[i] = g ? g->head_b1[h] : nullptr;
+    ba.db2[i] = g ? g->head_b2[h] : nullptr;
+  }
+  ba.Mg = wk.Mg[s]; ba.MgH = wk.MgH[s];
+  ba.dzT = wk.dzT; ba.dhT = wk.dhT; ba.GT = wk.GT; ba.d_emb = d_emb; ba.dc1 = wk.dc1;
+  TC_TRY(fused_func_attr(reinterpret_cast<const void*>(fused_bwd_kernel), FM_BWD_SMEM));
+  const int ntiles = (N + FM_TG - 1) / FM_TG;
+  const int sms = current_sm_count();
+  {
+    ProfScope ps("fused_bwd_kernel", stream);
+    fused_bwd_kernel<<<ntiles < sms ? ntiles : sms, FM_THREADS, FM_BWD_SMEM, stream>>>(ba);
+  }
+  TC_TRY(cudaGetLastError());
+
+  if (g) {
+    {  // dW2_h[o][f] += sum_n GT[o][n] zT_h[f][n]: all gradient rows on the M side, two heads' activations on the N side
+      WgArgs a{};
+      a.N = N;
+      for (int i0 = 0; i0 < na; i0 += 2) {
+        WgGroup& gr = a.g[a.ngroups];
+        gr.P = wk.GT; gr.pk = 1; gr.prow_total = FB_GT_ROWS; gr.pcols = FB_GT_ROWS;
+        gr.Q = wk.zT[s] + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
+        for (int i = i0; i < i0 + 2 && i < na; ++i) {
+          const int h = act[i];
+          if (!g->head_w2[h]) continue;
+          gr.seg[gr.nseg++] = WgSegment{g->head_w2[h], 1, 128, (i - i0) * 128, 128, ba.goff[i], hHeadDim[h]};
+        }
+        if (gr.nseg > 0) ++a.ngroups;
+        else gr = WgGroup{};
+      }
+      TC_TRY(tc_wgrad_launch(a, stream));
+    }
+    {  // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n]
+      WgArgs a{};
+      a.N = N;
+      for (int i0 = 0; i0 < na; i0 += 2) {
+        WgGroup& gr = a.g[a.ngroups];
+        gr.P = wk.hT[s]; gr.pk = 1; gr.prow_total = 128; gr.pcols = 128;
+        gr.Q = wk.dzT + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
+        for (int i = i0; i < i0 + 2 && i < na; ++i) {
+          const int h = act[i];
+          if (!g->head_w1[h]) continue;
+          gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], 128, 1, (i - i0) * 128, 128, 0, 128};
+        }
+        if (gr.nseg > 0) ++a.ngroups;
+        else gr = WgGroup{};
+      }
+      TC_TRY(tc_wgrad_launch(a, stream));
+    }
+    if (g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dhT[o][n] emb[n][i]
+      WgArgs a{};
+      a.N = N; a.ngroups = 1;
+      a.g[0].P = emb; a.g[0].ldp = gemb; a.g[0].pcols = gemb;
+      a.g[0].Q = wk.dhT; a.g[0].qk = 1; a.g[0].qrow_total = 128; a.g[0].qcols = 128;
+      a.g[0].nseg = 1;
+      a.g[0].seg[0] = WgSegment{g->feat_w[0] + temb, ld0, 1, 0, 128, 0, gemb};
+      TC_TRY(tc_wgrad_launch(a, stream));
+    }
+  }
+  layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
+      w->feat_w[0], ld0, temb, 128, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
+  TC_TRY(cudaGetLastError());
+  return ED3DGS_OK;
+}
+
 }  // namespace ed3dgs
 
 using namespace ed3dgs;
@@ -737,6 +865,22 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
       return ED3DGS_ERR_ARG;
     }
   }
+  const bool fused = fused_shape(any);
+  if (fused) {
+    // fine stage sees d_out only; coarse stage sees d_out + d_sub
+    int accumulate = 0;
+    if (fine) {
+      if ((rc = stage_backward_fused(fine, g_fine, 1, N, embedding, tau_f, gp.d_out, gp.d_sub, 0, coef, wk, d_embedding,
+                                     accumulate, d_tau_f, stream)))
+        return rc;
+      accumulate = 1;
+    }
+    if (coarse) {
+      if ((rc = stage_backward_fused(coarse, g_coarse, 0, N, embedding, tau_c, gp.d_out, gp.d_sub, any_sub ? 1 : 0, coef,
+                                     wk, d_embedding, accumulate, d_tau_c, stream)))
+        return rc;
+    }
+  } else {
   const int gblocks = 148 * 6;
   // fine stage sees d_out only; coarse stage sees d_out + d_sub
   cudaMemsetAsync(wk.colsum[1], 0, GW * sizeof(float), stream);
@@ -750,9 +894,6 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
     Gc = wk.G[0];
     colc = wk.colsum[0];
   }
-  // interim: the stage-resident forward keeps feature-major activations; the layered backward reads row-major ones
-  if (fine && fused_shape(fine) && (rc = stage_forward(fine, 1, N, embedding, tau_f, nullptr, nullptr, coef, wk, stream, true))) return rc;
-  if (coarse && fused_shape(coarse) && (rc = stage_forward(coarse, 0, N, embedding, tau_c, nullptr, nullptr, coef, wk, stream, true))) return rc;
   int accumulate = 0;
   if (fine) {
     if ((rc = stage_backward(fine, g_fine, 1, N, embedding, tau_f, wk.G[1], wk.colsum[1], wk, d_embedding, accumulate,
@@ -764,6 +905,7 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
     if ((rc = stage_backward(coarse, g_coarse, 0, N, embedding, tau_c, Gc, colc, wk, d_embedding, accumulate, d_tau_c,
                              stream)))
       return rc;
+  }
   }
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("deform_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
@@ -777,7 +919,7 @@ int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, c
   if (amaj == TC_MN_MAJOR) {
     // weight-gradient form: A stored [K][lda] (P side, M columns), B stored [K][ldb] (Q side, n_valid columns)
     WgArgs wa{};
-    wa.N = K; wa.ngroups = 1; wa.dbg = dbg;
+    wa.N = K; wa.ngroups = 1;
     wa.g[0].P = A; wa.g[0].ldp = lda; wa.g[0].pcols = (M + 3) / 4 * 4;
     wa.g[0].Q = B; wa.g[0].ldq = ldb; wa.g[0].qcols = (n_valid + 3) / 4 * 4;
     wa.g[0].nseg = 1;

@@ -114,10 +114,10 @@ struct FusedFwdArgs {
   float* dst[5];
   float coef[5];
   float* zT;                     // [tile][na*128][128]  post-ReLU hidden activations of the heads, feature-major per tile
-  float* hT;                     // [tile][128][128]     post-ReLU trunk activations (rows of Gaussians >= N are zero)
+  float* hT;                     // [tile][128][128]     post-ReLU trunk activations
+                                 // (columns of Gaussians >= N hold finite junk: every consumer multiplies them by a zero gradient)
   uint32_t* Mg;                  // [npad][na][4]   ReLU masks of the heads, bit = feature % 32
   uint32_t* MgH;                 // [npad][4]       ReLU mask of the trunk
-  uint32_t* Mf;                  // [npad/32][na*128] the same masks, bit = Gaussian % 32 (for kernels with features on lanes)
   alignas(64) CUtensorMap emap;  // embedding [N][32]: box {16, 128}, SWIZZLE_64B
 };
 
@@ -335,7 +335,6 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
       const int gl = q * 32 + lane;
       const long g = tile * FM_TG + gl;
       const bool valid = g < (long)p.N;
-      const bool blk_valid = tile * FM_TG + q * 32 < (long)p.N;
       // the previous tile's rgb output MMAs read H_lo and write H_hi: they must be done before H is rewritten
       if (has_rgb && tl > 0 && ch == 1) { mbar_wait(&bars.out_full, (uint32_t)((tl - 1) & 1)); tc_fence_after(); }
       {  // ---- layer 0: h = relu(acc + c1) -> H_hi / H_lo (A operand of the five hidden layers), hT, trunk mask
@@ -362,7 +361,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
               v[j] = h;
               lo[j] = h - trunc_tf32(h);
               word |= (h > 0.f ? 1u : 0u) << j;
-              hp[j * 128] = valid ? h : 0.f;
+              hp[j * 128] = h;
             }
           }
           tmem_st32(lane_base + FM_H_HI + (uint32_t)col, v);
@@ -393,7 +392,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
           tmem_ld32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);
           const float4* b4 = reinterpret_cast<const float4*>(s_b1 + hs * 128 + col);
           float* zp = p.zT + ((tile * na + hs) * 128 + col) * 128 + gl;
-          uint32_t word = 0, fword = 0;
+          uint32_t word = 0;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 c = b4[j4];
@@ -405,12 +404,9 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
               v[j] = z;
               const bool pos = z > 0.f;
               word |= (pos ? 1u : 0u) << j;
-              const uint32_t bw = __ballot_sync(0xffffffffu, pos && valid);
-              if (lane == j) fword = bw;
-              zp[j * 128] = valid ? z : 0.f;
+              zp[j * 128] = z;
             }
           }
-          if (blk_valid) p.Mf[(tile * 4 + q) * (long)(na * 128) + hs * 128 + col + lane] = fword;
           if (blk == 0) mw0 = word; else mw1 = word;
           if (!is_rgb) {
             const float4* w2 = s_w2 + hs * 128 + col;
@@ -489,6 +485,411 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
 
   tc_fence_before();
   __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// =============================================================================================================
+// Backward of one stage, the per-Gaussian chain:
+//      upstream gradients --W2_i--> dz_i (masked) --W1_i--> dh (masked) --W0e--> dE
+// Same orientation as the forward (Gaussians on the TMEM lanes). The gradient of a small head's hidden layer is
+// k <= 4 FMAs per element and is formed in registers; the rgb head's (k = 48) is a UMMA on the staged upstream
+// gradients. Each half head (64 features) is written to TMEM as hi/lo and consumed as the A operand of
+// dh += dz_i W1_i, the sum over all heads stays in one accumulator, its masked value is the A operand of dE = dh W0e.
+// Side products: the feature-major matrices dzT, dhT, GT the weight-gradient GEMMs contract over Gaussians, and the
+// bias gradients (column sums, transposed-reduced across the warp and collected in shared memory).
+//
+// TMEM: [0,128) DH acc / dh_hi   [128,256) DZ[0] = hi 64 + lo 64 (DE acc reuses its first 32 columns)
+//       [256,384) DZ[1]          [384,512) dh_lo
+constexpr uint32_t FB_DH = 0, FB_DZ = 128, FB_DH_LO = 384;
+constexpr int FB_G_BYTES = 12 * 128 * 16;   // rgb upstream gradients [128 Gaussians][48], K-major no-swizzle image
+constexpr int FB_GT_ROWS = 64;              // rows of a GT tile (59 used)
+
+struct FusedBwdArgs {
+  const float4* wimg;
+  uint32_t seq_off[64];      // weight slabs of one tile in the order the MMA warp consumes them (float4 offsets)
+  uint16_t seq_bytes[64];
+  int nseq;
+  int na, has_rgb, N;
+  int use_sub, accumulate_emb, store_dz;
+  const float* w2[5];        // by slot, [k][128]
+  int hdim[5];
+  int goff[5];               // first row of the slot in a GT tile
+  float coef[5];
+  const float* d_out[5];     // may be null
+  const float* d_sub[5];     // may be null
+  const uint32_t* Mg;
+  const uint32_t* MgH;
+  float* dzT;                // [tile][na*128][128]
+  float* dhT;                // [tile][128][128]
+  float* GT;                 // [tile][64][128]
+  float* d_emb;              // [N][32]
+  float* db1[5];             // += column sums of dz_i (may be null)
+  float* db2[5];             // += column sums of the scaled upstream gradients (may be null)
+  float* dc1;                // += column sums of dh
+};
+
+struct BwdBars {
+  uint64_t w_full[FM_W_SLOTS], w_free[FM_W_SLOTS];
+  uint64_t g_ready;
+  uint64_t dzacc_full[2], dz_ready[2], dz_free[2];
+  uint64_t dh_full, dh_ready, de_full;
+};
+
+constexpr size_t FM_BWD_SMEM = (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES + 2 * FB_G_BYTES + 5 * 128 * 16 +
+                               (5 * 128 + 128 + 64) * 4 + 1024;
+
+// Column sums of a 32 x 32 block held one row per lane: lane l returns sum over lanes of v[l]. 31 shuffles.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float keep = up ? v[i + off] : v[i];
+      const float send = up ? v[i] : v[i + off];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_constant__ FusedBwdArgs p) {
+  extern __shared__ __align__(128) unsigned char fm_smem_raw[];
+  __shared__ BwdBars bars;
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  unsigned char* sW = fm_smem_raw + ((1024u - (smem_u32(fm_smem_raw) & 1023u)) & 1023u);
+  unsigned char* sGh = sW + (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES;
+  unsigned char* sGl = sGh + FB_G_BYTES;
+  float4* s_w2 = reinterpret_cast<float4*>(sGl + FB_G_BYTES);
+  float* s_db1 = reinterpret_cast<float*>(s_w2 + 5 * 128);   // [slot][128]
+  float* s_dc1 = s_db1 + 5 * 128;                            // [128]
+  float* s_db2 = s_dc1 + 128;                                // [64] rows of GT
+
+  if (warp == 0) tmem_alloc(&s_tmem, 512);
+  if (tid == 32) {
+    for (int i = 0; i < FM_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
+    mbar_init(&bars.g_ready, FM_EPI_WARPS * 32);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars.dzacc_full[i], 1); mbar_init(&bars.dz_ready[i], FM_EPI_WARPS * 32); mbar_init(&bars.dz_free[i], 1);
+    }
+    mbar_init(&bars.dh_full, 1); mbar_init(&bars.dh_ready, FM_EPI_WARPS * 32); mbar_init(&bars.de_full, 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < 5 * 128; i += FM_THREADS) {
+    const int s = i >> 7, f = i & 127;
+    float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (s < p.na && !(p.has_rgb && s == p.na - 1)) {
+      const int k = p.hdim[s];
+      w.x = p.w2[s][f];
+      if (k > 1) w.y = p.w2[s][128 + f];
+      if (k > 2) w.z = p.w2[s][256 + f];
+      if (k > 3) w.w = p.w2[s][384 + f];
+    }
+    s_w2[i] = w;
+    s_db1[i] = 0.f;
+  }
+  for (int i = tid; i < 128 + 64; i += FM_THREADS) s_dc1[i] = 0.f;   // s_dc1 and s_db2 are adjacent
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  const int ntiles = (p.N + FM_TG - 1) / FM_TG;
+  const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int na = p.na;
+  const bool has_rgb = p.has_rgb != 0;
+  const int nunits = 2 * na;
+
+  if (warp == FM_WLOAD_WARP) {
+    RingPos<FM_W_SLOTS> wr;
+    for (int tl = 0; tl < my_tiles; ++tl)
+      for (int i = 0; i < p.nseq; ++i) {
+        mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
+        if (elect_one()) {
+          const uint32_t bytes = (uint32_t)p.seq_bytes[i];
+          mbar_arrive_expect_tx(&bars.w_full[wr.idx], bytes);
+          bulk_copy_g2s(sW + (size_t)wr.idx * FM_W_SLOT_BYTES, p.wimg + p.seq_off[i], bytes, &bars.w_full[wr.idx]);
+        }
+        __syncwarp();
+        wr.advance();
+      }
+  } else if (warp == FM_MMA_WARP) {
+    const uint32_t idesc128 = umma_idesc_tf32(128, 128), idesc64 = umma_idesc_tf32(128, 64), idesc32 = umma_idesc_tf32(128, 32);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);   // K-major no-swizzle: SBO = 128 B between 8-row groups
+    const uint32_t sw = (smem_u32(sW) & 0x3FFFFu) >> 4;
+    const uint32_t w128_lo0 = sw | ((128u * 16u >> 4) << 16), w64_lo0 = sw | ((64u * 16u >> 4) << 16),
+                   w32_lo0 = sw | ((32u * 16u >> 4) << 16);
+    const uint32_t gh_lo0 = ((smem_u32(sGh) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
+    const uint32_t gl_lo0 = ((smem_u32(sGl) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
+    constexpr uint32_t W_SLOT = FM_W_SLOT_BYTES >> 4;
+    constexpr uint32_t W128_LO = (128u * 64u) >> 4, W128_KS = (2u * 128u * 16u) >> 4;
+    constexpr uint32_t W64_LO = (64u * 64u) >> 4, W64_KS = (2u * 64u * 16u) >> 4;
+    constexpr uint32_t W32_LO = (32u * 64u) >> 4, W32_KS = (2u * 32u * 16u) >> 4;
+    constexpr uint32_t G_PIECE = (128u * 16u) >> 4;
+    RingPos<FM_W_SLOTS> wr;
+    int u = 0;
+    for (int tl = 0; tl < my_tiles; ++tl) {
+      auto ss_dz = [&](int hf) {   // SS: DZ[hf].hi[g][f] = sum_o G[g][o] W2[o][f], f in the half, K = 48
+        if (hf == 0) { mbar_wait(&bars.g_ready, (uint32_t)(tl & 1)); tc_fence_after(); }
+        const uint32_t acc = tmem + FB_DZ + (uint32_t)hf * 128u;
+        for (int s = 0; s < 3; ++s) {
+          mbar_wait(&bars.w_full[wr.idx], wr.phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t wh = w64_lo0 + (uint32_t)wr.idx * W_SLOT;
+#pragma unroll
+            for (uint32_t ks = 0; ks < 2; ++ks) {
+              const uint32_t go = ((uint32_t)s * 4u + ks * 2u) * G_PIECE;
+              umma_tf32(acc, desc64(desc_hi, gl_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, (s | (int)ks) ? 1u : 0u);
+              umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + W64_LO + ks * W64_KS), idesc64, 1u);
+              umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, 1u);
+            }
+            umma_commit(&bars.w_free[wr.idx]);
+            if (s == 2) umma_commit(&bars.dzacc_full[hf]);
+          }
+          __syncwarp();
+          wr.advance();
+        }
+      };
+      for (int uu = 0; uu < nunits; ++uu, ++u) {
+        const int b = u & 1;
+        if (has_rgb && uu + 1 < nunits && ((uu + 1) >> 1) == na - 1) ss_dz((uu + 1) & 1);
+        mbar_wait(&bars.dz_ready[b], (uint32_t)((u >> 1) & 1));
+        tc_fence_after();
+        const uint32_t a_hi = tmem + FB_DZ + (uint32_t)b * 128u, a_lo = a_hi + 64u;
+        for (int s = 0; s < 4; ++s) {   // TS: DH[g][k] += sum_f DZ[g][f] W1[f][k], 64 f of this unit
+          mbar_wait(&bars.w_full[wr.idx], wr.phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t wh = w128_lo0 + (uint32_t)wr.idx * W_SLOT;
+#pragma unroll
+            for (uint32_t ks = 0; ks < 2; ++ks) {
+              const uint32_t col = (uint32_t)s * 16u + ks * 8u;
+              umma_tf32_ts(tmem + FB_DH, a_lo + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, (uu | s | (int)ks) ? 1u : 0u);
+              umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
+              umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, 1u);
+            }
+            umma_commit(&bars.w_free[wr.idx]);
+            if (s == 3) {
+              umma_commit(&bars.dz_free[b]);
+              if (uu == nunits - 1) umma_commit(&bars.dh_full);
+            }
+          }
+          __syncwarp();
+          wr.advance();
+        }
+      }
+      mbar_wait(&bars.dh_ready, (uint32_t)(tl & 1));
+      tc_fence_after();
+      for (int s = 0; s < 8; ++s) {     // TS: DE[g][j] = sum_k dh[g][k] W0e[k][j], N = 32
+        mbar_wait(&bars.w_full[wr.idx], wr.phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t wh = w32_lo0 + (uint32_t)wr.idx * W_SLOT;
+#pragma unroll
+          for (uint32_t ks = 0; ks < 2; ++ks) {
+            const uint32_t col = (uint32_t)s * 16u + ks * 8u;
+            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH_LO + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, (s | (int)ks) ? 1u : 0u);
+            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + W32_LO + ks * W32_KS), idesc32, 1u);
+            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, 1u);
+          }
+          umma_commit(&bars.w_free[wr.idx]);
+          if (s == 7) umma_commit(&bars.de_full);
+        }
+        __syncwarp();
+        wr.advance();
+      }
+    }
+  } else if (warp < FM_EPI_WARPS) {
+    const int q = warp & 3, ch = warp >> 2;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    int u = 0;
+    for (int tl = 0; tl < my_tiles; ++tl) {
+      const long tile = (long)blockIdx.x + (long)tl * gridDim.x;
+      const int gl = q * 32 + lane;
+      const long g = tile * FM_TG + gl;
+      const bool valid = g < (long)p.N;
+      // ---- upstream gradients of this Gaussian, scaled by the annealing coefficients
+      float4 G4[4];
+      float red[32];   // the 32 gradient columns whose sums (second-layer bias gradients) this warp owns
+#pragma unroll
+      for (int i = 0; i < 32; ++i) red[i] = 0.f;
+      float* gt = p.GT + tile * (FB_GT_ROWS * 128) + gl;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        float t[4] = {0.f, 0.f, 0.f, 0.f};
+        if (s < na && !(has_rgb && s == na - 1)) {
+          const int k = p.hdim[s];
+          if (valid) {
+            const float* a = p.d_out[s] ? p.d_out[s] + g * k : nullptr;
+            const float* bsub = (p.use_sub && p.d_sub[s]) ? p.d_sub[s] + g * k : nullptr;
+#pragma unroll
+            for (int o = 0; o < 4; ++o)
+              if (o < k) t[o] = ((a ? a[o] : 0.f) + (bsub ? bsub[o] : 0.f)) * p.coef[s];
+          }
+          if (ch == 0) {
+#pragma unroll
+            for (int o = 0; o < 4; ++o)
+              if (o < k) gt[(p.goff[s] + o) * 128] = t[o];
+          }
+        }
+        G4[s] = make_float4(t[0], t[1], t[2], t[3]);
+        if (ch == 0) { red[4 * s] = t[0]; red[4 * s + 1] = t[1]; red[4 * s + 2] = t[2]; red[4 * s + 3] = t[3]; }
+      }
+      if (has_rgb) {
+        // rgb rows: column-half 0 warps take o = 0..15, column-half 1 warps o = 16..47; staged as the K-major A operand
+        const int s = na - 1;
+        const float cf = p.coef[s];
+        const float4* a = (valid && p.d_out[s]) ? reinterpret_cast<const float4*>(p.d_out[s] + g * 48) : nullptr;
+        const float4* bsub = (valid && p.use_sub && p.d_sub[s]) ? reinterpret_cast<const float4*>(p.d_sub[s] + g * 48) : nullptr;
+        float4* gh = reinterpret_cast<float4*>(sGh) + gl;
+        float4* glo = reinterpret_cast<float4*>(sGl) + gl;
+        auto stage_piece = [&](int pc, float* r4) {
+          float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (a) x = a[pc];
+          if (bsub) { const float4 y = bsub[pc]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
+          x.x *= cf; x.y *= cf; x.z *= cf; x.w *= cf;
+          gh[pc * 128] = x;
+          glo[pc * 128] = split_lo(x);
+          float* gr = gt + (p.goff[s] + 4 * pc) * 128;
+          gr[0] = x.x; gr[128] = x.y; gr[256] = x.z; gr[384] = x.w;
+          r4[0] = x.x; r4[1] = x.y; r4[2] = x.z; r4[3] = x.w;
+        };
+        if (ch == 0) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) stage_piece(i, red + 16 + 4 * i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) stage_piece(4 + i, red + 4 * i);
+        }
+        fence_async_smem();
+        mbar_arrive(&bars.g_ready);
+      }
+      {
+        const float cs = warp_colsum32(red, lane);
+        // column-half 0: columns 0..15 are the small slots (4 each), 16..31 rgb outputs 0..15; column-half 1: rgb 16..47
+        int row = -1;
+        if (ch == 0) {
+          if (lane < 16) { const int s = lane >> 2, o = lane & 3; if (s < na && !(has_rgb && s == na - 1) && o < p.hdim[s]) row = p.goff[s] + o; }
+          else if (has_rgb) row = p.goff[na - 1] + lane - 16;
+        } else if (has_rgb) row = p.goff[na - 1] + 16 + lane;
+        if (row >= 0) atomicAdd(&s_db2[row], cs);
+      }
+      // ---- half heads
+#pragma unroll 1
+      for (int hs = 0; hs < na; ++hs) {
+        const bool is_rgb = has_rgb && hs == na - 1;
+        uint4 mw = make_uint4(0u, 0u, 0u, 0u);
+        if (valid) mw = *reinterpret_cast<const uint4*>(p.Mg + (g * na + hs) * 4);
+        float4 gs = G4[0];
+        if (hs == 1) gs = G4[1];
+        if (hs == 2) gs = G4[2];
+        if (hs == 3) gs = G4[3];
+#pragma unroll 1
+        for (int hf = 0; hf < 2; ++hf, ++u) {
+          const int b = u & 1;
+          const int col = hf * 64 + ch * 32;
+          const uint32_t word = hf == 0 ? (ch == 0 ? mw.x : mw.y) : (ch == 0 ? mw.z : mw.w);
+          mbar_wait(&bars.dz_free[b], (uint32_t)(((u >> 1) & 1) ^ 1));   // the UMMAs that read this buffer two units ago
+          tc_fence_after();
+          float v[32], lo[32];
+          if (!is_rgb) {
+            const float4* w2 = s_w2 + hs * 128 + col;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float4 w = w2[j];
+              v[j] = fmaf(gs.x, w.x, fmaf(gs.y, w.y, fmaf(gs.z, w.z, gs.w * w.w)));
+            }
+          } else {
+            mbar_wait(&bars.dzacc_full[b], (uint32_t)(tl & 1));
+            tc_fence_after();
+            tmem_ld32(lane_base + FB_DZ + (uint32_t)(b * 128 + ch * 32), v);
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
+            lo[j] = v[j] - trunc_tf32(v[j]);
+          }
+          tmem_st32(lane_base + FB_DZ + (uint32_t)(b * 128 + ch * 32), v);
+          tmem_st32(lane_base + FB_DZ + (uint32_t)(b * 128 + 64 + ch * 32), lo);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(&bars.dz_ready[b]);
+          if (p.store_dz) {
+            float* zp = p.dzT + ((tile * na + hs) * 128 + col) * 128 + gl;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) zp[j * 128] = v[j];
+          }
+          const float cs = warp_colsum32(v, lane);
+          atomicAdd(&s_db1[hs * 128 + col + lane], cs);
+        }
+      }
+      // ---- dh = (sum over heads) masked by the trunk ReLU -> dhT, bias gradient, A operand of dE
+      {
+        mbar_wait(&bars.dh_full, (uint32_t)(tl & 1));
+        tc_fence_after();
+        uint2 hw = make_uint2(0u, 0u);
+        if (valid) hw = *reinterpret_cast<const uint2*>(p.MgH + g * 4 + ch * 2);
+#pragma unroll 1
+        for (int blk = 0; blk < 2; ++blk) {
+          const int col = ch * 64 + blk * 32;
+          const uint32_t word = blk == 0 ? hw.x : hw.y;
+          float v[32], lo[32];
+          tmem_ld32(lane_base + FB_DH + (uint32_t)col, v);
+          float* hp = p.dhT + (tile * 128 + col) * 128 + gl;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
+            lo[j] = v[j] - trunc_tf32(v[j]);
+            hp[j * 128] = v[j];
+          }
+          tmem_st32(lane_base + FB_DH + (uint32_t)col, v);
+          tmem_st32(lane_base + FB_DH_LO + (uint32_t)col, lo);
+          const float cs = warp_colsum32(v, lane);
+          atomicAdd(&s_dc1[col + lane], cs);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&bars.dh_ready);
+      }
+      // ---- dE row of this Gaussian (the first 32 DZ[0] columns belong to the column-half 0 warps)
+      if (ch == 0) {
+        mbar_wait(&bars.de_full, (uint32_t)(tl & 1));
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(lane_base + FB_DZ, v);
+        if (valid) {
+          float4* de = reinterpret_cast<float4*>(p.d_emb + g * 32);
+#pragma unroll
+          for (int o = 0; o < 8; ++o) {
+            float4 x = make_float4(v[4 * o], v[4 * o + 1], v[4 * o + 2], v[4 * o + 3]);
+            if (p.accumulate_emb) { const float4 y = de[o]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
+            de[o] = x;
+          }
+        }
+        tc_fence_before();
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  // bias gradients: one atomic per column and CTA
+  for (int i = tid; i < 5 * 128; i += FM_THREADS) {
+    const int s = i >> 7;
+    if (s < na && p.db1[s] && s_db1[i] != 0.f) atomicAdd(p.db1[s] + (i & 127), s_db1[i]);
+  }
+  for (int i = tid; i < 128; i += FM_THREADS)
+    if (p.dc1 && s_dc1[i] != 0.f) atomicAdd(p.dc1 + i, s_dc1[i]);
+  for (int i = tid; i < 5 * 48; i += FM_THREADS) {
+    const int s = i / 48, o = i - s * 48;
+    if (s < na && o < p.hdim[s] && p.db2[s]) {
+      const float x = s_db2[p.goff[s] + o];
+      if (x != 0.f) atomicAdd(p.db2[s] + o, x);
+    }
+  }
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 

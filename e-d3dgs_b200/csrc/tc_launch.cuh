@@ -34,13 +34,10 @@ inline bool tc_rows_build(TcArgs& a) {
   return ns > 0;
 }
 
-inline int tc_sm_count() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-      sms = 148;
-  }
+inline int tc_sm_count() {   // of the current device (not cached: a process may drive several GPUs)
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+    sms = 148;
   return sms;
 }
 
@@ -62,12 +59,10 @@ inline tc_encode_tiled_fn tc_encode_tiled() {
 
 template <int EPI>
 inline cudaError_t tc_rows_run(const TcArgs& a, int grid, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
+  {  // a per-device attribute: set on every launch (a process-wide flag would miss the second GPU)
     const cudaError_t e =
         cudaFuncSetAttribute(tc_rows_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROWS_SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   tc_rows_kernel<EPI><<<grid, ROWS_THREADS, ROWS_SMEM_BYTES, stream>>>(a);
   return cudaGetLastError();
@@ -121,25 +116,39 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
         (g.ldp & 3) || (g.ldq & 3) || g.nseg < 0 || g.nseg > 2 || (reinterpret_cast<uintptr_t>(g.P) & 15) ||
         (reinterpret_cast<uintptr_t>(g.Q) & 15))
       return cudaErrorInvalidValue;
-    // tiles of 32 features x 16 Gaussians, 32-byte chunks swizzled inside 128-byte rows = the UMMA's MN-major
-    // layout for 32-bit elements (SWIZZLE_128B_BASE32B);
-    // columns >= cols and rows >= N are zero-filled by the unit
-    const cuuint32_t box[2] = {32, 16};
+    // row-major operand: tiles of 32 features x 16 Gaussians, 32-byte chunks swizzled inside 128-byte rows = the UMMA's
+    // MN-major layout for 32-bit elements (SWIZZLE_128B_BASE32B); columns >= cols and rows >= N are zero-filled by the unit.
+    // feature-major operand ([tile][rows][128 Gaussians]): one box of 16 Gaussians x 128 / 256 feature rows, SWIZZLE_64B
+    // = the K-major layout; feature rows >= cols are zero-filled.
+    const cuuint32_t estr3[3] = {1, 1, 1};
     const cuuint32_t estr[2] = {1, 1};
+    const cuuint64_t ntiles = (cuuint64_t)((a.N + 127) / 128);
     for (int side = 0; side < 2; ++side) {
-      const cuuint64_t dims[2] = {(cuuint64_t)(side ? g.qcols : g.pcols), (cuuint64_t)a.N};
-      const cuuint64_t strides[1] = {(cuuint64_t)(side ? g.ldq : g.ldp) * sizeof(float)};
-      const CUresult r = enc(side ? &a.qmap[i] : &a.pmap[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-                             const_cast<float*>(side ? g.Q : g.P), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      const bool km = side ? g.qk != 0 : g.pk != 0;
+      const int cols = side ? g.qcols : g.pcols;
+      CUtensorMap* map = side ? &a.qmap[i] : &a.pmap[i];
+      float* base = const_cast<float*>(side ? g.Q : g.P);
+      CUresult r;
+      if (km) {
+        const long rows_total = side ? g.qrow_total : g.prow_total;
+        const cuuint64_t dims[3] = {128, (cuuint64_t)cols, ntiles};
+        const cuuint64_t strides[2] = {128 * sizeof(float), (cuuint64_t)rows_total * 128 * sizeof(float)};
+        const cuuint32_t box[3] = {16, (cuuint32_t)(side && cols > 128 ? 256 : 128), 1};
+        r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr3, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      } else {
+        const cuuint32_t box[2] = {32, 16};
+        const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)a.N};
+        const cuuint64_t strides[1] = {(cuuint64_t)(side ? g.ldq : g.ldp) * sizeof(float)};
+        r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      }
       if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     }
   }
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
+  {  // a per-device attribute: set on every launch (a process-wide flag would miss the second GPU)
+    const cudaError_t e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   const int items = ((a.N + WG_SLICE - 1) / WG_SLICE) * a.ngroups;
   const int grid = items < tc_sm_count() ? items : tc_sm_count();

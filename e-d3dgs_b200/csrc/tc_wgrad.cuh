@@ -54,12 +54,15 @@ struct WgGroup {
   int pcols, qcols;
   int nseg;
   WgSegment seg[2];
+  // Feature-major operands (written by the stage-resident kernels, fused_mlp.cuh): P / Q point at row 0 of a
+  // [tile][rows_total][128 Gaussians] matrix; pk / qk select that layout per operand (K-major for the UMMA).
+  int pk, qk;
+  long prow_total, qrow_total;
 };
 struct WgArgs {
   WgGroup g[WG_MAX_GROUPS];
   int ngroups;
   int N;            // Gaussians
-  int dbg;          // 2 = single pass (hi*hi only)
   // tensor maps of P and Q of every group: dims {cols, N}, box {32, 16}, SWIZZLE_128B_ATOM_32B (tc_wgrad_launch)
   alignas(64) CUtensorMap pmap[WG_MAX_GROUPS];
   alignas(64) CUtensorMap qmap[WG_MAX_GROUPS];
@@ -71,9 +74,16 @@ struct WgBars {
   uint64_t acc_full[2], acc_free[2];
 };
 
-// UMMA instruction descriptor, kind::tf32, fp32 accumulate, both operands MN-major (bits 15 / 16).
-__device__ __forceinline__ uint32_t umma_idesc_tf32_mn(int M, int N) {
-  return umma_idesc_tf32(M, N) | (1u << 15) | (1u << 16);
+// UMMA instruction descriptor, kind::tf32, fp32 accumulate; bit 15 / 16: A / B operand MN-major.
+__device__ __forceinline__ uint32_t umma_idesc_tf32_mn(int M, int N, bool a_mn = true, bool b_mn = true) {
+  return umma_idesc_tf32(M, N) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u);
+}
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const void* tmap, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
 }
 
 __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_constant__ WgArgs p) {
@@ -162,9 +172,15 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
           mbar_arrive_expect_tx(bar, bytes);
           unsigned char* dst = sHi + (size_t)hr.idx * WG_SLAB_BYTES;
           const int row = (int)row0 + s * 16;
+          // feature-major operand: one box {16 Gaussians, 128 or 256 feature rows} of tile row / 128
+          if (p.g[group].pk) tma_load_3d(dst, &p.pmap[group], row & 127, 0, row >> 7, bar);
+          else {
 #pragma unroll
-          for (int b = 0; b < 4; ++b) tma_load_2d(dst + b * WG_BLOCK_BYTES, &p.pmap[group], 32 * b, row, bar);
-          for (int b = 0; b < nqb; ++b) tma_load_2d(dst + WG_P_BYTES + b * WG_BLOCK_BYTES, &p.qmap[group], 32 * b, row, bar);
+            for (int b = 0; b < 4; ++b) tma_load_2d(dst + b * WG_BLOCK_BYTES, &p.pmap[group], 32 * b, row, bar);
+          }
+          if (p.g[group].qk) tma_load_3d(dst + WG_P_BYTES, &p.qmap[group], row & 127, 0, row >> 7, bar);
+          else
+            for (int b = 0; b < nqb; ++b) tma_load_2d(dst + WG_P_BYTES + b * WG_BLOCK_BYTES, &p.qmap[group], 32 * b, row, bar);
         }
         __syncwarp();
         hr.advance();
@@ -182,14 +198,20 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
     const uint32_t hi0 = ((smem_u32(sHi) & 0x3FFFFu) >> 4) | lbo;
     const uint32_t lo0 = ((smem_u32(sLo) & 0x3FFFFu) >> 4) | lbo;
     constexpr uint32_t SLAB = WG_SLAB_BYTES >> 4, QOFF = WG_P_BYTES >> 4, KS = 1024u >> 4;
-    const bool single = (p.dbg & 2) != 0;
     RingPos<WG_HI_SLOTS> hr;
     RingPos<WG_LO_SLOTS> lr;
     for (int k = 0; k < my_items; ++k) {
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
-      const uint32_t idesc = umma_idesc_tf32_mn(128, p.g[group].qcols > 128 ? 256 : 128);
+      const bool pk = p.g[group].pk != 0, qk = p.g[group].qk != 0;
+      const uint32_t idesc = umma_idesc_tf32_mn(128, p.g[group].qcols > 128 ? 256 : 128, !pk, !qk);
+      // feature-major operand = K-major, SWIZZLE_64B rows of 16 Gaussians (as the activation slabs of tc_rows.cuh):
+      // SBO = 512 B between 8-row atoms, a k-step (8 Gaussians) advances the start by 32 B
+      const uint32_t kdesc_hi = (512u >> 4) | (1u << 14) | (4u << 29);
+      const uint32_t p_hi = pk ? kdesc_hi : desc_hi, q_hi = qk ? kdesc_hi : desc_hi;
+      const uint32_t p_fix = pk ? ((1u << 16) - lbo) : 0u, q_fix = qk ? ((1u << 16) - lbo) : 0u;   // LBO field
+      const uint32_t p_ks = pk ? (32u >> 4) : KS, q_ks = qk ? (32u >> 4) : KS;
       const int buf = k & 1;
       mbar_wait(&bars.acc_free[buf], (uint32_t)(((k >> 1) & 1) ^ 1));
       const uint32_t acc = tmem + (uint32_t)buf * 256u;
@@ -197,20 +219,15 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
         mbar_wait(&bars.x_full[lr.idx], lr.phase);        // lo written (and the stagers saw the hi slab land)
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t ph = hi0 + (uint32_t)hr.idx * SLAB, pl = lo0 + (uint32_t)lr.idx * SLAB;
-          const uint32_t qh = ph + QOFF, ql = pl + QOFF;
+          const uint32_t ph = hi0 + (uint32_t)hr.idx * SLAB + p_fix, pl = lo0 + (uint32_t)lr.idx * SLAB + p_fix;
+          const uint32_t qh = hi0 + (uint32_t)hr.idx * SLAB + QOFF + q_fix, ql = lo0 + (uint32_t)lr.idx * SLAB + QOFF + q_fix;
           const uint32_t first = s == 0 ? 0u : 1u;
-          if (single) {
-            umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, qh), idesc, first);
-            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, qh + KS), idesc, 1u);
-          } else {
-            umma_tf32(acc, desc64(desc_hi, pl), desc64(desc_hi, qh), idesc, first);  // small terms first
-            umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, ql), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph), desc64(desc_hi, qh), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, pl + KS), desc64(desc_hi, qh + KS), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, ql + KS), idesc, 1u);
-            umma_tf32(acc, desc64(desc_hi, ph + KS), desc64(desc_hi, qh + KS), idesc, 1u);
-          }
+          umma_tf32(acc, desc64(p_hi, pl), desc64(q_hi, qh), idesc, first);  // small terms first
+          umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, ql), idesc, 1u);
+          umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, qh), idesc, 1u);
+          umma_tf32(acc, desc64(p_hi, pl + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
+          umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, ql + q_ks), idesc, 1u);
+          umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
           umma_commit(&bars.lo_free[lr.idx]);
           umma_commit(&bars.hi_free[hr.idx]);
           if (s == nslab - 1) umma_commit(&bars.acc_full[buf]);
