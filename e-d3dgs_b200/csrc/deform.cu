@@ -632,6 +632,9 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   return ED3DGS_OK;
 }
 
+#ifdef ED3DGS_TRACE
+static long long* g_trace = nullptr;
+#endif
 // Backward of one stage on the stage-resident path: one chain kernel (dz, dh, dE, bias gradients, feature-major
 // gradient matrices) and three weight-gradient launches that contract those matrices over the Gaussians.
 static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
@@ -657,13 +660,16 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
     ++nimg;
     return at;
   };
-  uint32_t w1t[5][8], w2t[2][3], w0t[8];
+  uint32_t w1t[5][8], w2t[5][2][3], w0t[8];
   for (int i = 0; i < na; ++i)
     for (int sl = 0; sl < 8; ++sl) w1t[i][sl] = add_img(w->head_w1[act[i]], 128, 128, 128, sl * 16, 128);   // rows k, K = f
-  if (has_rgb)
+  for (int i = 0; i < na; ++i) {   // second-layer weights transposed: rows f (a half head), K = o
+    const int h = act[i], k = hHeadDim[h];
     for (int hf = 0; hf < 2; ++hf)
-      for (int sl = 0; sl < 3; ++sl) w2t[hf][sl] = add_img(w->head_w2[4] + hf * 64, 128, 64, 64, sl * 16, 48);  // rows f, K = o
+      for (int sl = 0; sl * 16 < k; ++sl) w2t[i][hf][sl] = add_img(w->head_w2[h] + hf * 64, 128, 64, 64, sl * 16, k);
+  }
   for (int sl = 0; sl < 8; ++sl) w0t[sl] = add_img(w->feat_w[0] + temb, ld0, gemb, 32, sl * 16, 128);           // rows j, K = k
+  if (nimg > FM_MAX_SLABS) { set_error("deform_backward: slab table overflow"); return ED3DGS_ERR_ARG; }
   pa.dst = reinterpret_cast<float4*>(wk.wimg_b);
   {
     ProfScope ps("fused_prepare", stream);
@@ -672,9 +678,13 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
   int nseq = 0;
   auto push = [&](uint32_t at, int NT) { ba.seq_off[nseq] = at; ba.seq_bytes[nseq] = (uint16_t)(NT * 128); ++nseq; };
   const int nunits = 2 * na;
+  auto push_w2t = [&](int unit) {
+    const int i = unit >> 1, k = hHeadDim[act[i]];
+    for (int sl = 0; sl * 16 < k; ++sl) push(w2t[i][unit & 1][sl], 64);
+  };
+  push_w2t(0);
   for (int uu = 0; uu < nunits; ++uu) {
-    if (has_rgb && uu + 1 < nunits && ((uu + 1) >> 1) == na - 1)
-      for (int sl = 0; sl < 3; ++sl) push(w2t[(uu + 1) & 1][sl], 64);
+    if (uu + 1 < nunits) push_w2t(uu + 1);
     for (int sl = 0; sl < 4; ++sl) push(w1t[uu >> 1][(uu & 1) * 4 + sl], 128);
   }
   for (int sl = 0; sl < 8; ++sl) push(w0t[sl], 32);
@@ -682,6 +692,9 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
   ba.wimg = reinterpret_cast<const float4*>(wk.wimg_b);
   ba.na = na; ba.has_rgb = has_rgb ? 1 : 0; ba.N = N;
   ba.use_sub = use_sub; ba.accumulate_emb = accumulate_emb; ba.store_dz = 1;
+#ifdef ED3DGS_TRACE
+  { static long long* tr = nullptr; if (!tr) { cudaMalloc(&tr, 8 * 8000 * 5); } cudaMemsetAsync(tr, 0, 8 * 8000 * 5, stream); ba.trace = tr; g_trace = tr; }
+#endif
   int goff = 0;
   for (int i = 0; i < na; ++i) {
     const int h = act[i];
@@ -699,7 +712,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
   const int sms = current_sm_count();
   {
     ProfScope ps("fused_bwd_kernel", stream);
-    fused_bwd_kernel<<<ntiles < sms ? ntiles : sms, FM_THREADS, FM_BWD_SMEM, stream>>>(ba);
+    fused_bwd_kernel<<<ntiles < sms ? ntiles : sms, FB_THREADS, FM_BWD_SMEM, stream>>>(ba);
   }
   TC_TRY(cudaGetLastError());
 
@@ -911,6 +924,15 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
   if (e != cudaSuccess) { set_error("deform_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
   return ED3DGS_OK;
 }
+
+#ifdef ED3DGS_TRACE
+int ed3dgs_trace_read(long long* host, int n) {
+  if (!g_trace) return -1;
+  cudaDeviceSynchronize();
+  cudaMemcpy(host, g_trace, (size_t)n * 8, cudaMemcpyDeviceToHost);
+  return 0;
+}
+#endif
 
 // Test hook (not in the public header): one GEMM through the tensor-core building block.
 int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, const float* A, long lda,

@@ -20,12 +20,13 @@
 namespace ed3dgs {
 
 constexpr int FM_TG = 128;                       // Gaussians per tile = UMMA M
-constexpr int FM_EPI_WARPS = 8;                  // warp w: TMEM lanes 32*(w&3).., column half w>>2
-constexpr int FM_MMA_WARP = 8;
-constexpr int FM_WLOAD_WARP = 9;
-constexpr int FM_ELOAD_WARP = 10;
-constexpr int FM_THREADS = 11 * 32;
+constexpr int FM_EPI_WARPS = 16;                 // warp w: TMEM lanes 32*(w&3).., column quarter w>>2
+constexpr int FM_MMA_WARP = 16;
+constexpr int FM_WLOAD_WARP = 17;
+constexpr int FM_ELOAD_WARP = 18;
+constexpr int FM_THREADS = 19 * 32;
 constexpr int FM_W_SLOTS = 8;
+constexpr int FMF_W_SLOTS = 7;                   // forward kernel: one slot less, the space holds the head-output partial sums
 constexpr int FM_W_SLOT_BYTES = 128 * 16 * 4 * 2;   // hi + lo of [128 rows x 16 k], K-major no-swizzle image
 constexpr int FM_E_SLAB_BYTES = 128 * 16 * 4;       // [128 Gaussians x 16 k], 64-byte rows, SWIZZLE_64B (TMA)
 constexpr int FM_E_BYTES = 2 * FM_E_SLAB_BYTES;     // K = 32
@@ -93,8 +94,29 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v) {
       "r"(__float_as_uint(v[31]))
       : "memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+      "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])),
+      "r"(__float_as_uint(v[7])), "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])),
+      "r"(__float_as_uint(v[11])), "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])),
+      "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+// lo part (x - trunc_tf32(x)) of 32 values to 32 TMEM columns, 16 at a time (keeps the register peak at 48)
+__device__ __forceinline__ void tmem_st_lo32(uint32_t taddr, const float* v) {
+  float lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) lo[j] = v[j] - __uint_as_float(__float_as_uint(v[j]) & 0xffffe000u);
+  tmem_st16(taddr, lo);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) lo[j] = v[16 + j] - __uint_as_float(__float_as_uint(v[16 + j]) & 0xffffe000u);
+  tmem_st16(taddr + 16u, lo);
+}
+__device__ __forceinline__ void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 
 // =============================================================================================================
@@ -122,14 +144,15 @@ struct FusedFwdArgs {
 };
 
 struct FwdBars {
-  uint64_t w_full[FM_W_SLOTS], w_free[FM_W_SLOTS];
+  uint64_t w_full[FMF_W_SLOTS], w_free[FMF_W_SLOTS];
+  uint64_t part[3][4];           // partial sums of a small head parked by the four column-quarter warps of a lane quarter
   uint64_t e_tma[2], e_full[2], e_free[2];
   uint64_t acc_full[2], acc_free[2];
   uint64_t h_ready, z4_ready, out_full;
 };
 
-constexpr size_t FM_FWD_SMEM = (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES + 4 * FM_E_BYTES + 5 * 128 * 16 +
-                               (128 + 5 * 128 + 5 * 48) * 4 + 2 * 128 * 16 * 4 + 1024;
+constexpr size_t FM_FWD_SMEM = (size_t)FMF_W_SLOTS * FM_W_SLOT_BYTES + 4 * FM_E_BYTES + 5 * 128 * 16 +
+                               (128 + 5 * 128 + 5 * 48) * 4 + 3 * 4 * 128 * 16 + 1024;
 
 __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_constant__ FusedFwdArgs p) {
   extern __shared__ __align__(128) unsigned char fm_smem_raw[];
@@ -138,17 +161,17 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   unsigned char* sW = fm_smem_raw + ((1024u - (smem_u32(fm_smem_raw) & 1023u)) & 1023u);
-  unsigned char* sEh = sW + (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES;
+  unsigned char* sEh = sW + (size_t)FMF_W_SLOTS * FM_W_SLOT_BYTES;
   unsigned char* sEl = sEh + 2 * FM_E_BYTES;
   float4* s_w2 = reinterpret_cast<float4*>(sEl + 2 * FM_E_BYTES);   // [slot][feature] -> (w2[0..3][feature])
   float* s_c1 = reinterpret_cast<float*>(s_w2 + 5 * 128);
   float* s_b1 = s_c1 + 128;                                         // [slot][128]
   float* s_b2 = s_b1 + 5 * 128;                                     // [slot][48]
-  float* s_part = s_b2 + 5 * 48;                                    // [2][128 rows][16]
+  float4* s_part = reinterpret_cast<float4*>(s_b2 + 5 * 48);        // [3][4 column quarters][128 rows]: small-head partial outputs
 
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
-    for (int i = 0; i < FM_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
+    for (int i = 0; i < FMF_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars.e_tma[i], 1); mbar_init(&bars.e_full[i], 32); mbar_init(&bars.e_free[i], 1);
       mbar_init(&bars.acc_full[i], 1); mbar_init(&bars.acc_free[i], FM_EPI_WARPS * 32);
@@ -156,6 +179,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
     mbar_init(&bars.h_ready, FM_EPI_WARPS * 32);
     mbar_init(&bars.z4_ready, FM_EPI_WARPS * 32);
     mbar_init(&bars.out_full, 1);
+    for (int i = 0; i < 12; ++i) mbar_init(&bars.part[i / 4][i & 3], 128);
     fence_mbar_init();
   }
   for (int i = tid; i < 5 * 128; i += FM_THREADS) {
@@ -209,7 +233,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
     }
   } else if (warp == FM_WLOAD_WARP) {
     // ------------------------------------------------------------------ weight slabs, in the order the MMA warp uses them
-    RingPos<FM_W_SLOTS> wr;
+    RingPos<FMF_W_SLOTS> wr;
     auto push = [&](int slab, uint32_t bytes) {
       mbar_wait(&bars.w_free[wr.idx], wr.phase ^ 1u);
       if (elect_one()) {
@@ -239,7 +263,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
     constexpr uint32_t W128_LO = (128u * 64u) >> 4, W128_KS = (2u * 128u * 16u) >> 4;
     constexpr uint32_t W48_LO = (48u * 64u) >> 4, W48_KS = (2u * 48u * 16u) >> 4;
     constexpr uint32_t E_SLAB = FM_E_SLAB_BYTES >> 4, E_KS = 32u >> 4;
-    RingPos<FM_W_SLOTS> wr;
+    RingPos<FMF_W_SLOTS> wr;
     int go = 0;
 
     auto layer0 = [&](int tl) {      // SS: ACC[g][f] = sum_k E[g][k] W0e[f][k], K = 32
@@ -326,56 +350,59 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 0..7)
-    const int q = warp & 3, ch = warp >> 2;
+    // ------------------------------------------------------------------ epilogue (warps 0..15)
+    // warp w: Gaussians (TMEM lanes) 32*(w&3).., features (columns) 32*(w>>2)..: one 32 x 32 block of every accumulator
+    const int q = warp & 3, cq = warp >> 2;
+    const int col = cq * 32;
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
-    int go = 0, npart = 0;
+    int go = 0, np = 0;
     for (int tl = 0; tl < my_tiles; ++tl) {
       const long tile = (long)blockIdx.x + (long)tl * gridDim.x;
       const int gl = q * 32 + lane;
       const long g = tile * FM_TG + gl;
       const bool valid = g < (long)p.N;
+      if (tl + 1 < my_tiles) {   // next tile's input rows: into L2 now
+        const long gn = g + (long)gridDim.x * FM_TG;
+        if (gn < (long)p.N) {
+          if (cq < na && !(has_rgb && cq == na - 1)) prefetch_l2(p.base[cq] + gn * p.hdim[cq]);
+          if (has_rgb && cq < 2) prefetch_l2(p.base[na - 1] + gn * 48 + cq * 32);
+        }
+      }
       // the previous tile's rgb output MMAs read H_lo and write H_hi: they must be done before H is rewritten
-      if (has_rgb && tl > 0 && ch == 1) { mbar_wait(&bars.out_full, (uint32_t)((tl - 1) & 1)); tc_fence_after(); }
+      if (has_rgb && tl > 0) { mbar_wait(&bars.out_full, (uint32_t)((tl - 1) & 1)); tc_fence_after(); }
       {  // ---- layer 0: h = relu(acc + c1) -> H_hi / H_lo (A operand of the five hidden layers), hT, trunk mask
         const int buf = go & 1;
         mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
         tc_fence_after();
-        uint32_t hw0 = 0, hw1 = 0;
-#pragma unroll 1
-        for (int blk = 0; blk < 2; ++blk) {
-          const int col = ch * 64 + blk * 32;
-          float v[32], lo[32];
-          tmem_ld32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);
-          const float4* c4 = reinterpret_cast<const float4*>(s_c1 + col);
-          float* hp = p.hT + (tile * 128 + col) * 128 + gl;
-          uint32_t word = 0;
+        float v[32];
+        tmem_ld32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);
+        const float4* c4 = reinterpret_cast<const float4*>(s_c1 + col);
+        float* hp = p.hT + (tile * 128 + col) * 128 + gl;
+        uint32_t word = 0;
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 c = c4[j4];
-            const float cc[4] = {c.x, c.y, c.z, c.w};
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 c = c4[j4];
+          const float cc[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int j = j4 * 4 + i;
-              const float h = fmaxf(v[j] + cc[i], 0.f);
-              v[j] = h;
-              lo[j] = h - trunc_tf32(h);
-              word |= (h > 0.f ? 1u : 0u) << j;
-              hp[j * 128] = h;
-            }
+          for (int i = 0; i < 4; ++i) {
+            const int j = j4 * 4 + i;
+            const float h = fmaxf(v[j] + cc[i], 0.f);
+            v[j] = h;
+            word |= (h > 0.f ? 1u : 0u) << j;
           }
-          tmem_st32(lane_base + FM_H_HI + (uint32_t)col, v);
-          tmem_st32(lane_base + FM_H_LO + (uint32_t)col, lo);
-          if (blk == 0) hw0 = word; else hw1 = word;
         }
+        tmem_st32(lane_base + FM_H_HI + (uint32_t)col, v);
+        tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);
         tmem_st_wait();
-        if (valid) *reinterpret_cast<uint2*>(p.MgH + g * 4 + ch * 2) = make_uint2(hw0, hw1);
         tc_fence_before();
         mbar_arrive(&bars.h_ready);
         mbar_arrive(&bars.acc_free[buf]);
         ++go;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) hp[j * 128] = v[j];   // off the critical path: the hidden-layer UMMAs are running
+        if (valid) p.MgH[g * 4 + cq] = word;
       }
-      // ---- hidden layer of every head: z = relu(acc + b1) -> zT, both mask layouts; the small heads' output layer
+      // ---- hidden layer of every head: z = relu(acc + b1) -> zT, ReLU mask; the small heads' output layer
       //      (k <= 4) is evaluated right here on the FP32 pipe, the rgb head's z goes back to TMEM for its UMMA
 #pragma unroll 1
       for (int hs = 0; hs < na; ++hs) {
@@ -383,51 +410,25 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
         const int buf = go & 1;
         mbar_wait(&bars.acc_full[buf], (uint32_t)((go >> 1) & 1));
         tc_fence_after();
-        uint32_t mw0 = 0, mw1 = 0;
-        float o4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-        for (int blk = 0; blk < 2; ++blk) {
-          const int col = ch * 64 + blk * 32;
-          float v[32];
-          tmem_ld32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);
-          const float4* b4 = reinterpret_cast<const float4*>(s_b1 + hs * 128 + col);
-          float* zp = p.zT + ((tile * na + hs) * 128 + col) * 128 + gl;
-          uint32_t word = 0;
+        float v[32];
+        tmem_ld32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);
+        const float4* b4 = reinterpret_cast<const float4*>(s_b1 + hs * 128 + col);
+        uint32_t word = 0;
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 c = b4[j4];
-            const float cc[4] = {c.x, c.y, c.z, c.w};
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 c = b4[j4];
+          const float cc[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int j = j4 * 4 + i;
-              const float z = fmaxf(v[j] + cc[i], 0.f);
-              v[j] = z;
-              const bool pos = z > 0.f;
-              word |= (pos ? 1u : 0u) << j;
-              zp[j * 128] = z;
-            }
-          }
-          if (blk == 0) mw0 = word; else mw1 = word;
-          if (!is_rgb) {
-            const float4* w2 = s_w2 + hs * 128 + col;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float4 w = w2[j];
-              o4[0] = fmaf(v[j], w.x, o4[0]);
-              o4[1] = fmaf(v[j], w.y, o4[1]);
-              o4[2] = fmaf(v[j], w.z, o4[2]);
-              o4[3] = fmaf(v[j], w.w, o4[3]);
-            }
-          } else {
-            float lo[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) lo[j] = v[j] - trunc_tf32(v[j]);
-            tmem_st32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);   // Z4_hi in place
-            tmem_st32(lane_base + FM_H_LO + (uint32_t)col, lo);               // the trunk operand is dead by now
+          for (int i = 0; i < 4; ++i) {
+            const int j = j4 * 4 + i;
+            const float z = fmaxf(v[j] + cc[i], 0.f);
+            v[j] = z;
+            word |= (z > 0.f ? 1u : 0u) << j;
           }
         }
-        if (valid) *reinterpret_cast<uint2*>(p.Mg + (g * na + hs) * 4 + ch * 2) = make_uint2(mw0, mw1);
         if (is_rgb) {
+          tmem_st32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);   // Z4_hi in place
+          tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);             // the trunk operand is dead by now
           tmem_st_wait();
           tc_fence_before();
           mbar_arrive(&bars.z4_ready);
@@ -435,41 +436,82 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
         tc_fence_before();
         mbar_arrive(&bars.acc_free[buf]);
         ++go;
+        float* zp = p.zT + ((tile * na + hs) * 128 + col) * 128 + gl;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) zp[j * 128] = v[j];
+        if (valid) p.Mg[(g * na + hs) * 4 + cq] = word;
         if (!is_rgb) {
-          // x = base + (delta + b2) * coef: the column-half 0 warps park their partial sums, the column-half 1 warps finish
-          float4* part = reinterpret_cast<float4*>(s_part) + (size_t)(npart & 1) * 128 + gl;
-          ++npart;
-          if (ch == 0) *part = make_float4(o4[0], o4[1], o4[2], o4[3]);
-          epi_bar_sync();
-          if (ch == 1 && valid) {
-            const float4 o2 = *part;
-            const float t[4] = {o4[0] + o2.x, o4[1] + o2.y, o4[2] + o2.z, o4[3] + o2.w};
-            const int k = p.hdim[hs];
-            const float cf = p.coef[hs];
+          const int k = p.hdim[hs];
+          const bool fin = cq == (hs & 3);      // this warp finishes the head: its base row is requested before the FMAs
+          float bsv[4] = {0.f, 0.f, 0.f, 0.f};
+          if (fin && valid) {
             const float* bs = p.base[hs] + g * k;
-            float* ds = p.dst[hs] + g * k;
 #pragma unroll
             for (int o = 0; o < 4; ++o)
-              if (o < k) ds[o] = bs[o] + (t[o] + s_b2[hs * 48 + o]) * cf;
+              if (o < k) bsv[o] = bs[o];
+          }
+          const float4* w2 = s_w2 + hs * 128 + col;
+          float o4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float4 w = w2[j];
+            o4[0] = fmaf(v[j], w.x, o4[0]);
+            o4[1] = fmaf(v[j], w.y, o4[1]);
+            o4[2] = fmaf(v[j], w.z, o4[2]);
+            o4[3] = fmaf(v[j], w.w, o4[3]);
+          }
+          // the four column quarters of a Gaussian meet in shared memory; the quarter (hs & 3) warp finishes the head:
+          // x = base + (delta + b2) * coef. Three buffers: a buffer is rewritten three heads later, by which time its
+          // reader has gone through two more accumulator hand-overs that every warp takes part in.
+          const int pb = np % 3;
+          const uint32_t pph = (uint32_t)((np / 3) & 1);
+          ++np;
+          s_part[(pb * 4 + cq) * 128 + gl] = make_float4(o4[0], o4[1], o4[2], o4[3]);
+          mbar_arrive(&bars.part[pb][q]);
+          if (fin) {
+            mbar_wait(&bars.part[pb][q], pph);
+            float t[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const float4 o2 = s_part[(pb * 4 + c) * 128 + gl];
+              t[0] += o2.x; t[1] += o2.y; t[2] += o2.z; t[3] += o2.w;
+            }
+            if (valid) {
+              const float cf = p.coef[hs];
+              float* ds = p.dst[hs] + g * k;
+#pragma unroll
+              for (int o = 0; o < 4; ++o)
+                if (o < k) ds[o] = bsv[o] + (t[o] + s_b2[hs * 48 + o]) * cf;
+            }
           }
         }
       }
-      if (has_rgb && ch == 0) {
-        // the rgb accumulator sits in the columns these warps rewrite in the next tile's layer-0 epilogue
+      if (has_rgb && cq < 2) {
+        // rgb accumulator: columns [0,32) by the quarter-0 warps, [32,48) by the quarter-1 warps -- the warps that
+        // rewrite those H_hi columns in the next tile's layer-0 epilogue
         const int s = na - 1;
+        float4 bsr[8];                     // the base row is requested before the wait for the output UMMAs
+#pragma unroll
+        for (int o = 0; o < 8; ++o) bsr[o] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) {
+          const float4* bs = reinterpret_cast<const float4*>(p.base[s] + g * 48 + cq * 32);
+#pragma unroll
+          for (int o = 0; o < 8; ++o)
+            if (cq == 0 || o < 4) bsr[o] = bs[o];
+        }
         mbar_wait(&bars.out_full, (uint32_t)(tl & 1));
         tc_fence_after();
-        float v[48];
-        tmem_ld32(lane_base + FM_H_HI, v);
-        tmem_ld16(lane_base + FM_H_HI + 32u, v + 32);
+        float v[32];
+        if (cq == 0) tmem_ld32(lane_base + FM_H_HI, v);
+        else tmem_ld16(lane_base + FM_H_HI + 32u, v);
         if (valid) {
-          const float4* bs = reinterpret_cast<const float4*>(p.base[s] + g * 48);
-          float4* ds = reinterpret_cast<float4*>(p.dst[s] + g * 48);
+          float4* ds = reinterpret_cast<float4*>(p.dst[s] + g * 48 + cq * 32);
           const float cf = p.coef[s];
-          const float4* b2 = reinterpret_cast<const float4*>(s_b2 + s * 48);
+          const float4* b2 = reinterpret_cast<const float4*>(s_b2 + s * 48 + cq * 32);
 #pragma unroll
-          for (int o = 0; o < 12; ++o) {
-            float4 b = bs[o];
+          for (int o = 0; o < 8; ++o) {
+            if (cq == 1 && o >= 4) break;
+            float4 b = bsr[o];
             const float4 c = b2[o];
             b.x += (v[4 * o + 0] + c.x) * cf;
             b.y += (v[4 * o + 1] + c.y) * cf;
@@ -503,6 +545,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
 constexpr uint32_t FB_DH = 0, FB_DZ = 128, FB_DH_LO = 384;
 constexpr int FB_G_BYTES = 12 * 128 * 16;   // rgb upstream gradients [128 Gaussians][48], K-major no-swizzle image
 constexpr int FB_GT_ROWS = 64;              // rows of a GT tile (59 used)
+constexpr int FB_THREADS = 18 * 32;         // 16 epilogue warps + MMA + weight loader (register allocation rounds to 20 warps: 96 per thread)
 
 struct FusedBwdArgs {
   const float4* wimg;
@@ -511,6 +554,7 @@ struct FusedBwdArgs {
   int nseq;
   int na, has_rgb, N;
   int use_sub, accumulate_emb, store_dz;
+  long long* trace;          // ED3DGS_TRACE builds: (event, clock) pairs of block 0
   const float* w2[5];        // by slot, [k][128]
   int hdim[5];
   int goff[5];               // first row of the slot in a GT tile
@@ -531,12 +575,19 @@ struct FusedBwdArgs {
 struct BwdBars {
   uint64_t w_full[FM_W_SLOTS], w_free[FM_W_SLOTS];
   uint64_t g_ready;
-  uint64_t dzacc_full[2], dz_ready[2], dz_free[2];
+  uint64_t dzacc_full[2], dz_ready[2];
   uint64_t dh_full, dh_ready, de_full;
 };
 
-constexpr size_t FM_BWD_SMEM = (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES + 2 * FB_G_BYTES + 5 * 128 * 16 +
-                               (5 * 128 + 128 + 64) * 4 + 1024;
+constexpr int FB_GS_BYTES = 8 * 128 * 16;   // small-head upstream gradients [128 Gaussians][4 slots x 8 k], K-major image
+constexpr size_t FM_BWD_SMEM = (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES + 2 * FB_G_BYTES + 2 * FB_GS_BYTES +
+                               4 * (5 * 128 + 128 + 64) * 4 + 1024;
+
+#ifdef ED3DGS_TRACE
+#define FM_TRACE(ev) do { if (blockIdx.x == 0 && lane == 0 && p.trace && tcount < 4000) { p.trace[tbase + 2 * tcount] = (ev); p.trace[tbase + 2 * tcount + 1] = clock64(); ++tcount; } } while (0)
+#else
+#define FM_TRACE(ev) do {} while (0)
+#endif
 
 // Column sums of a 32 x 32 block held one row per lane: lane l returns sum over lanes of v[l]. 31 shuffles.
 __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
@@ -553,44 +604,35 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-__global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_constant__ FusedBwdArgs p) {
+__global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_constant__ FusedBwdArgs p) {
   extern __shared__ __align__(128) unsigned char fm_smem_raw[];
   __shared__ BwdBars bars;
   __shared__ uint32_t s_tmem;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   unsigned char* sW = fm_smem_raw + ((1024u - (smem_u32(fm_smem_raw) & 1023u)) & 1023u);
-  unsigned char* sGh = sW + (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES;
+  unsigned char* sGh = sW + (size_t)FM_W_SLOTS * FM_W_SLOT_BYTES;   // rgb gradients, hi / lo
   unsigned char* sGl = sGh + FB_G_BYTES;
-  float4* s_w2 = reinterpret_cast<float4*>(sGl + FB_G_BYTES);
-  float* s_db1 = reinterpret_cast<float*>(s_w2 + 5 * 128);   // [slot][128]
-  float* s_dc1 = s_db1 + 5 * 128;                            // [128]
-  float* s_db2 = s_dc1 + 128;                                // [64] rows of GT
+  unsigned char* sSh = sGl + FB_G_BYTES;                            // small-head gradients, hi / lo
+  unsigned char* sSl = sSh + FB_GS_BYTES;
+  // bias-gradient partial sums, one private copy per lane quarter (a warp only ever touches its own addresses:
+  // shared-memory float atomics are a compare-and-swap loop on this architecture)
+  float* s_db1 = reinterpret_cast<float*>(sSl + FB_GS_BYTES);      // [4][slot][128]
+  float* s_dc1 = s_db1 + 4 * 5 * 128;                              // [4][128]
+  float* s_db2 = s_dc1 + 4 * 128;                                  // [4][64] rows of GT
 
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
     for (int i = 0; i < FM_W_SLOTS; ++i) { mbar_init(&bars.w_full[i], 1); mbar_init(&bars.w_free[i], 1); }
     mbar_init(&bars.g_ready, FM_EPI_WARPS * 32);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&bars.dzacc_full[i], 1); mbar_init(&bars.dz_ready[i], FM_EPI_WARPS * 32); mbar_init(&bars.dz_free[i], 1);
-    }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars.dzacc_full[i], 1); mbar_init(&bars.dz_ready[i], FM_EPI_WARPS / 2 * 32); }
     mbar_init(&bars.dh_full, 1); mbar_init(&bars.dh_ready, FM_EPI_WARPS * 32); mbar_init(&bars.de_full, 1);
     fence_mbar_init();
   }
-  for (int i = tid; i < 5 * 128; i += FM_THREADS) {
-    const int s = i >> 7, f = i & 127;
-    float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (s < p.na && !(p.has_rgb && s == p.na - 1)) {
-      const int k = p.hdim[s];
-      w.x = p.w2[s][f];
-      if (k > 1) w.y = p.w2[s][128 + f];
-      if (k > 2) w.z = p.w2[s][256 + f];
-      if (k > 3) w.w = p.w2[s][384 + f];
-    }
-    s_w2[i] = w;
-    s_db1[i] = 0.f;
-  }
-  for (int i = tid; i < 128 + 64; i += FM_THREADS) s_dc1[i] = 0.f;   // s_dc1 and s_db2 are adjacent
+  // the padding k-pieces of the small-gradient image stay zero for the whole kernel
+  for (int i = tid; i < 2 * FB_GS_BYTES / 16; i += FB_THREADS) reinterpret_cast<float4*>(sSh)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < 4 * (5 * 128 + 128 + 64); i += FB_THREADS) s_db1[i] = 0.f;   // the three arrays are adjacent
+  fence_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -621,8 +663,9 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_c
     const uint32_t sw = (smem_u32(sW) & 0x3FFFFu) >> 4;
     const uint32_t w128_lo0 = sw | ((128u * 16u >> 4) << 16), w64_lo0 = sw | ((64u * 16u >> 4) << 16),
                    w32_lo0 = sw | ((32u * 16u >> 4) << 16);
-    const uint32_t gh_lo0 = ((smem_u32(sGh) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
-    const uint32_t gl_lo0 = ((smem_u32(sGl) & 0x3FFFFu) >> 4) | ((128u * 16u >> 4) << 16);
+    const uint32_t lbo128 = (128u * 16u >> 4) << 16;
+    const uint32_t gh_lo0 = ((smem_u32(sGh) & 0x3FFFFu) >> 4) | lbo128, gl_lo0 = ((smem_u32(sGl) & 0x3FFFFu) >> 4) | lbo128;
+    const uint32_t sh_lo0 = ((smem_u32(sSh) & 0x3FFFFu) >> 4) | lbo128, sl_lo0 = ((smem_u32(sSl) & 0x3FFFFu) >> 4) | lbo128;
     constexpr uint32_t W_SLOT = FM_W_SLOT_BYTES >> 4;
     constexpr uint32_t W128_LO = (128u * 64u) >> 4, W128_KS = (2u * 128u * 16u) >> 4;
     constexpr uint32_t W64_LO = (64u * 64u) >> 4, W64_KS = (2u * 64u * 16u) >> 4;
@@ -630,34 +673,52 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_c
     constexpr uint32_t G_PIECE = (128u * 16u) >> 4;
     RingPos<FM_W_SLOTS> wr;
     int u = 0;
+    int tcount = 0; const int tbase = 0; (void)tcount; (void)tbase;
     for (int tl = 0; tl < my_tiles; ++tl) {
-      auto ss_dz = [&](int hf) {   // SS: DZ[hf].hi[g][f] = sum_o G[g][o] W2[o][f], f in the half, K = 48
-        if (hf == 0) { mbar_wait(&bars.g_ready, (uint32_t)(tl & 1)); tc_fence_after(); }
+      FM_TRACE(100 + tl);
+      // SS: DZ[hf].hi[g][f] = sum_o G[g][o] W2[o][f] for the 64 features of a half head; K = 8 (small heads, one slab of
+      // which one k-step is used) or 48 (rgb, three slabs)
+      auto ss_dz = [&](int unit) {
+        const int hs = unit >> 1, hf = unit & 1;
+        const bool is_rgb = has_rgb && hs == na - 1;
         const uint32_t acc = tmem + FB_DZ + (uint32_t)hf * 128u;
-        for (int s = 0; s < 3; ++s) {
+        const int nsl = is_rgb ? 3 : 1;
+        for (int s = 0; s < nsl; ++s) {
           mbar_wait(&bars.w_full[wr.idx], wr.phase);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t wh = w64_lo0 + (uint32_t)wr.idx * W_SLOT;
+            if (is_rgb) {
 #pragma unroll
-            for (uint32_t ks = 0; ks < 2; ++ks) {
-              const uint32_t go = ((uint32_t)s * 4u + ks * 2u) * G_PIECE;
-              umma_tf32(acc, desc64(desc_hi, gl_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, (s | (int)ks) ? 1u : 0u);
-              umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + W64_LO + ks * W64_KS), idesc64, 1u);
-              umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, 1u);
+              for (uint32_t ks = 0; ks < 2; ++ks) {
+                const uint32_t go = ((uint32_t)s * 4u + ks * 2u) * G_PIECE;
+                umma_tf32(acc, desc64(desc_hi, gl_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, (s | (int)ks) ? 1u : 0u);
+                umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + W64_LO + ks * W64_KS), idesc64, 1u);
+                umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, 1u);
+              }
+            } else {
+              const uint32_t go = (uint32_t)(2 * hs) * G_PIECE;
+              umma_tf32(acc, desc64(desc_hi, sl_lo0 + go), desc64(desc_hi, wh), idesc64, 0u);
+              umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh + W64_LO), idesc64, 1u);
+              umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh), idesc64, 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
-            if (s == 2) umma_commit(&bars.dzacc_full[hf]);
+            if (s == nsl - 1) umma_commit(&bars.dzacc_full[hf]);
           }
           __syncwarp();
           wr.advance();
         }
       };
+      mbar_wait(&bars.g_ready, (uint32_t)(tl & 1));
+      tc_fence_after();
+      ss_dz(0);
       for (int uu = 0; uu < nunits; ++uu, ++u) {
         const int b = u & 1;
-        if (has_rgb && uu + 1 < nunits && ((uu + 1) >> 1) == na - 1) ss_dz((uu + 1) & 1);
+        if (uu + 1 < nunits) ss_dz(uu + 1);   // its buffer was last read by the UMMAs of unit uu - 1, already in the queue
+        FM_TRACE(1);
         mbar_wait(&bars.dz_ready[b], (uint32_t)((u >> 1) & 1));
         tc_fence_after();
+        FM_TRACE(2);
         const uint32_t a_hi = tmem + FB_DZ + (uint32_t)b * 128u, a_lo = a_hi + 64u;
         for (int s = 0; s < 4; ++s) {   // TS: DH[g][k] += sum_f DZ[g][f] W1[f][k], 64 f of this unit
           mbar_wait(&bars.w_full[wr.idx], wr.phase);
@@ -672,17 +733,16 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_c
               umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
-            if (s == 3) {
-              umma_commit(&bars.dz_free[b]);
-              if (uu == nunits - 1) umma_commit(&bars.dh_full);
-            }
+            if (s == 3 && uu == nunits - 1) umma_commit(&bars.dh_full);
           }
           __syncwarp();
           wr.advance();
         }
       }
+      FM_TRACE(3);
       mbar_wait(&bars.dh_ready, (uint32_t)(tl & 1));
       tc_fence_after();
+      FM_TRACE(4);
       for (int s = 0; s < 8; ++s) {     // TS: DE[g][j] = sum_k dh[g][k] W0e[k][j], N = 32
         mbar_wait(&bars.w_full[wr.idx], wr.phase);
         tc_fence_after();
@@ -703,171 +763,192 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_c
       }
     }
   } else if (warp < FM_EPI_WARPS) {
-    const int q = warp & 3, ch = warp >> 2;
+    // warp w: Gaussians 32*(w&3).., column quarter cq = w>>2. A head's features cq*32.. are this warp's; the half
+    // head hf = cq>>1 (buffer DZ[hf]) is its unit, so the two warp groups alternate units.
+    const int q = warp & 3, cq = warp >> 2, hf = cq >> 1, ch = cq & 1;
+    const int col = cq * 32;
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
-    int u = 0;
+    const uint32_t dz_hi = lane_base + FB_DZ + (uint32_t)(hf * 128 + ch * 32), dz_lo = dz_hi + 64u;
+    int n = 0;   // units this group has produced
+    // Per-tile inputs of this thread (ReLU mask words, upstream gradient rows). They are requested one tile ahead, right
+    // after the trunk-gradient hand-over of the previous tile, so that their latency hides behind that tile's stores
+    // (a trace showed the tensor pipe idle a third of the time behind these loads when they were issued at the tile top).
+    uint32_t mword[5] = {0u, 0u, 0u, 0u, 0u};
+    uint32_t hword = 0u;
+    float tsm[4] = {0.f, 0.f, 0.f, 0.f};                 // small slot cq of this Gaussian (this warp stages it)
+    float4 xr[3];                                       // rgb outputs 12*cq .. 12*cq+11
+    const bool my_small = cq < na && !(has_rgb && cq == na - 1);
+    auto request_tile = [&](int tl) {
+      const long g = ((long)blockIdx.x + (long)tl * gridDim.x) * FM_TG + q * 32 + lane;
+      const bool valid = g < (long)p.N;
+#pragma unroll
+      for (int s = 0; s < 5; ++s) mword[s] = 0u;
+      hword = 0u;
+#pragma unroll
+      for (int o = 0; o < 4; ++o) tsm[o] = 0.f;
+      if (valid) {
+#pragma unroll
+        for (int s = 0; s < 5; ++s)
+          if (s < na) mword[s] = p.Mg[(g * na + s) * 4 + cq];
+        hword = p.MgH[g * 4 + cq];
+      }
+      if (my_small && valid) {
+        const int k = p.hdim[cq];
+        const float* a = p.d_out[cq] ? p.d_out[cq] + g * k : nullptr;
+        const float* bsub = (p.use_sub && p.d_sub[cq]) ? p.d_sub[cq] + g * k : nullptr;
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+          if (o < k) tsm[o] = (a ? a[o] : 0.f) + (bsub ? bsub[o] : 0.f);
+      }
+#pragma unroll
+      for (int i = 0; i < 3; ++i) xr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (has_rgb && valid) {
+        const int s = na - 1;
+        if (p.d_out[s]) {
+          const float4* a = reinterpret_cast<const float4*>(p.d_out[s] + g * 48) + cq * 3;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) xr[i] = a[i];
+        }
+        if (p.use_sub && p.d_sub[s]) {
+          const float4* bsub = reinterpret_cast<const float4*>(p.d_sub[s] + g * 48) + cq * 3;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) { const float4 y = bsub[i]; xr[i].x += y.x; xr[i].y += y.y; xr[i].z += y.z; xr[i].w += y.w; }
+        }
+      }
+    };
+    if (my_tiles > 0) request_tile(0);
+    int tcount = 0; const int tbase = 8000 * (1 + (warp >> 2)); (void)tcount; (void)tbase;
     for (int tl = 0; tl < my_tiles; ++tl) {
+      if (q == 0) FM_TRACE(100 + tl);
       const long tile = (long)blockIdx.x + (long)tl * gridDim.x;
       const int gl = q * 32 + lane;
       const long g = tile * FM_TG + gl;
       const bool valid = g < (long)p.N;
-      // ---- upstream gradients of this Gaussian, scaled by the annealing coefficients
-      float4 G4[4];
-      float red[32];   // the 32 gradient columns whose sums (second-layer bias gradients) this warp owns
+      // ---- upstream gradients scaled by the annealing coefficients: GT rows, bias-gradient sums, and the K-major A
+      //      operands of the dz UMMAs (column quarter cq stages small slot cq and rgb outputs 12*cq .. 12*cq+11)
+      if (q == 0) FM_TRACE(20);
+      float red[32];   // the gradient columns whose sums (second-layer bias gradients) this warp owns
 #pragma unroll
       for (int i = 0; i < 32; ++i) red[i] = 0.f;
       float* gt = p.GT + tile * (FB_GT_ROWS * 128) + gl;
+      if (my_small) {
+        const float cf = p.coef[cq];
+        const int k = p.hdim[cq];
 #pragma unroll
-      for (int s = 0; s < 4; ++s) {
-        float t[4] = {0.f, 0.f, 0.f, 0.f};
-        if (s < na && !(has_rgb && s == na - 1)) {
-          const int k = p.hdim[s];
-          if (valid) {
-            const float* a = p.d_out[s] ? p.d_out[s] + g * k : nullptr;
-            const float* bsub = (p.use_sub && p.d_sub[s]) ? p.d_sub[s] + g * k : nullptr;
-#pragma unroll
-            for (int o = 0; o < 4; ++o)
-              if (o < k) t[o] = ((a ? a[o] : 0.f) + (bsub ? bsub[o] : 0.f)) * p.coef[s];
-          }
-          if (ch == 0) {
-#pragma unroll
-            for (int o = 0; o < 4; ++o)
-              if (o < k) gt[(p.goff[s] + o) * 128] = t[o];
-          }
-        }
-        G4[s] = make_float4(t[0], t[1], t[2], t[3]);
-        if (ch == 0) { red[4 * s] = t[0]; red[4 * s + 1] = t[1]; red[4 * s + 2] = t[2]; red[4 * s + 3] = t[3]; }
+        for (int o = 0; o < 4; ++o) tsm[o] *= cf;
+        float* gr = gt + p.goff[cq] * 128;
+        gr[0] = tsm[0];
+        if (k > 1) gr[128] = tsm[1];
+        if (k > 2) gr[256] = tsm[2];
+        if (k > 3) gr[384] = tsm[3];
+        red[0] = tsm[0]; red[1] = tsm[1]; red[2] = tsm[2]; red[3] = tsm[3];
+        const float4 x = make_float4(tsm[0], tsm[1], tsm[2], tsm[3]);
+        reinterpret_cast<float4*>(sSh)[(2 * cq) * 128 + gl] = x;
+        reinterpret_cast<float4*>(sSl)[(2 * cq) * 128 + gl] = split_lo(x);
       }
       if (has_rgb) {
-        // rgb rows: column-half 0 warps take o = 0..15, column-half 1 warps o = 16..47; staged as the K-major A operand
         const int s = na - 1;
         const float cf = p.coef[s];
-        const float4* a = (valid && p.d_out[s]) ? reinterpret_cast<const float4*>(p.d_out[s] + g * 48) : nullptr;
-        const float4* bsub = (valid && p.use_sub && p.d_sub[s]) ? reinterpret_cast<const float4*>(p.d_sub[s] + g * 48) : nullptr;
         float4* gh = reinterpret_cast<float4*>(sGh) + gl;
         float4* glo = reinterpret_cast<float4*>(sGl) + gl;
-        auto stage_piece = [&](int pc, float* r4) {
-          float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (a) x = a[pc];
-          if (bsub) { const float4 y = bsub[pc]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const int pc = cq * 3 + i;
+          float4 x = xr[i];
           x.x *= cf; x.y *= cf; x.z *= cf; x.w *= cf;
           gh[pc * 128] = x;
           glo[pc * 128] = split_lo(x);
           float* gr = gt + (p.goff[s] + 4 * pc) * 128;
           gr[0] = x.x; gr[128] = x.y; gr[256] = x.z; gr[384] = x.w;
-          r4[0] = x.x; r4[1] = x.y; r4[2] = x.z; r4[3] = x.w;
-        };
-        if (ch == 0) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) stage_piece(i, red + 16 + 4 * i);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) stage_piece(4 + i, red + 4 * i);
+          red[16 + 4 * i] = x.x; red[17 + 4 * i] = x.y; red[18 + 4 * i] = x.z; red[19 + 4 * i] = x.w;
         }
-        fence_async_smem();
-        mbar_arrive(&bars.g_ready);
       }
+      if (q == 0) FM_TRACE(21);
+      fence_async_smem();
+      mbar_arrive(&bars.g_ready);
+      if (q == 0) FM_TRACE(22);
       {
         const float cs = warp_colsum32(red, lane);
-        // column-half 0: columns 0..15 are the small slots (4 each), 16..31 rgb outputs 0..15; column-half 1: rgb 16..47
+        // columns 0..3: small slot cq; 16..27: rgb outputs 12*cq + (lane - 16)
         int row = -1;
-        if (ch == 0) {
-          if (lane < 16) { const int s = lane >> 2, o = lane & 3; if (s < na && !(has_rgb && s == na - 1) && o < p.hdim[s]) row = p.goff[s] + o; }
-          else if (has_rgb) row = p.goff[na - 1] + lane - 16;
-        } else if (has_rgb) row = p.goff[na - 1] + 16 + lane;
-        if (row >= 0) atomicAdd(&s_db2[row], cs);
+        if (lane < 4) { if (my_small && lane < p.hdim[cq]) row = p.goff[cq] + lane; }
+        else if (has_rgb && lane >= 16 && lane < 28) row = p.goff[na - 1] + 12 * cq + lane - 16;
+        if (row >= 0) s_db2[q * 64 + row] += cs;
       }
-      // ---- half heads
+      if (q == 0) FM_TRACE(23);
+      // ---- this group's half of every head: accumulator -> ReLU mask -> hi / lo A operand of dh += dz W1
 #pragma unroll 1
-      for (int hs = 0; hs < na; ++hs) {
-        const bool is_rgb = has_rgb && hs == na - 1;
-        uint4 mw = make_uint4(0u, 0u, 0u, 0u);
-        if (valid) mw = *reinterpret_cast<const uint4*>(p.Mg + (g * na + hs) * 4);
-        float4 gs = G4[0];
-        if (hs == 1) gs = G4[1];
-        if (hs == 2) gs = G4[2];
-        if (hs == 3) gs = G4[3];
-#pragma unroll 1
-        for (int hf = 0; hf < 2; ++hf, ++u) {
-          const int b = u & 1;
-          const int col = hf * 64 + ch * 32;
-          const uint32_t word = hf == 0 ? (ch == 0 ? mw.x : mw.y) : (ch == 0 ? mw.z : mw.w);
-          mbar_wait(&bars.dz_free[b], (uint32_t)(((u >> 1) & 1) ^ 1));   // the UMMAs that read this buffer two units ago
-          tc_fence_after();
-          float v[32], lo[32];
-          if (!is_rgb) {
-            const float4* w2 = s_w2 + hs * 128 + col;
+      for (int hs = 0; hs < na; ++hs, ++n) {
+        uint32_t word = mword[0];
+        if (hs == 1) word = mword[1];
+        if (hs == 2) word = mword[2];
+        if (hs == 3) word = mword[3];
+        if (hs == 4) word = mword[4];
+        if (q == 0) FM_TRACE(10);
+        mbar_wait(&bars.dzacc_full[hf], (uint32_t)(n & 1));
+        tc_fence_after();
+        if (q == 0) FM_TRACE(11);
+        float v[32];
+        tmem_ld32(dz_hi, v);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float4 w = w2[j];
-              v[j] = fmaf(gs.x, w.x, fmaf(gs.y, w.y, fmaf(gs.z, w.z, gs.w * w.w)));
-            }
-          } else {
-            mbar_wait(&bars.dzacc_full[b], (uint32_t)(tl & 1));
-            tc_fence_after();
-            tmem_ld32(lane_base + FB_DZ + (uint32_t)(b * 128 + ch * 32), v);
-          }
+        for (int j = 0; j < 32; ++j) v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
+        tmem_st32(dz_hi, v);
+        tmem_st_lo32(dz_lo, v);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&bars.dz_ready[hf]);
+        if (q == 0) FM_TRACE(12);
+        if (p.store_dz) {
+          float* zp = p.dzT + ((tile * na + hs) * 128 + col) * 128 + gl;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
-            lo[j] = v[j] - trunc_tf32(v[j]);
-          }
-          tmem_st32(lane_base + FB_DZ + (uint32_t)(b * 128 + ch * 32), v);
-          tmem_st32(lane_base + FB_DZ + (uint32_t)(b * 128 + 64 + ch * 32), lo);
-          tmem_st_wait();
-          tc_fence_before();
-          mbar_arrive(&bars.dz_ready[b]);
-          if (p.store_dz) {
-            float* zp = p.dzT + ((tile * na + hs) * 128 + col) * 128 + gl;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) zp[j * 128] = v[j];
-          }
-          const float cs = warp_colsum32(v, lane);
-          atomicAdd(&s_db1[hs * 128 + col + lane], cs);
+          for (int j = 0; j < 32; ++j) zp[j * 128] = v[j];
         }
+        const float cs = warp_colsum32(v, lane);
+        s_db1[q * 640 + hs * 128 + col + lane] += cs;
       }
       // ---- dh = (sum over heads) masked by the trunk ReLU -> dhT, bias gradient, A operand of dE
       {
+        if (q == 0) FM_TRACE(13);
         mbar_wait(&bars.dh_full, (uint32_t)(tl & 1));
         tc_fence_after();
-        uint2 hw = make_uint2(0u, 0u);
-        if (valid) hw = *reinterpret_cast<const uint2*>(p.MgH + g * 4 + ch * 2);
-#pragma unroll 1
-        for (int blk = 0; blk < 2; ++blk) {
-          const int col = ch * 64 + blk * 32;
-          const uint32_t word = blk == 0 ? hw.x : hw.y;
-          float v[32], lo[32];
-          tmem_ld32(lane_base + FB_DH + (uint32_t)col, v);
-          float* hp = p.dhT + (tile * 128 + col) * 128 + gl;
+        if (q == 0) FM_TRACE(14);
+        float v[32];
+        tmem_ld32(lane_base + FB_DH + (uint32_t)col, v);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
-            lo[j] = v[j] - trunc_tf32(v[j]);
-            hp[j * 128] = v[j];
-          }
-          tmem_st32(lane_base + FB_DH + (uint32_t)col, v);
-          tmem_st32(lane_base + FB_DH_LO + (uint32_t)col, lo);
-          const float cs = warp_colsum32(v, lane);
-          atomicAdd(&s_dc1[col + lane], cs);
-        }
+        for (int j = 0; j < 32; ++j) v[j] = ((hword >> j) & 1u) ? v[j] : 0.f;
+        tmem_st32(lane_base + FB_DH + (uint32_t)col, v);
+        tmem_st_lo32(lane_base + FB_DH_LO + (uint32_t)col, v);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&bars.dh_ready);
+        if (q == 0) FM_TRACE(15);
+        if (tl + 1 < my_tiles) request_tile(tl + 1);   // latency hides behind the stores and the column sums below
+        float* hp = p.dhT + (tile * 128 + col) * 128 + gl;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) hp[j * 128] = v[j];
+        if (q == 0) FM_TRACE(16);
+        const float cs = warp_colsum32(v, lane);
+        s_dc1[q * 128 + col + lane] += cs;
+        if (q == 0) FM_TRACE(17);
       }
-      // ---- dE row of this Gaussian (the first 32 DZ[0] columns belong to the column-half 0 warps)
-      if (ch == 0) {
+      // ---- dE row of this Gaussian (the first 32 DZ[0] columns are the quarter-0 warps' own)
+      if (cq == 0) {
+        float4* de = reinterpret_cast<float4*>(p.d_emb + g * 32);
+        float4 old[8];
+#pragma unroll
+        for (int o = 0; o < 8; ++o) old[o] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && p.accumulate_emb) {
+#pragma unroll
+          for (int o = 0; o < 8; ++o) old[o] = de[o];
+        }
         mbar_wait(&bars.de_full, (uint32_t)(tl & 1));
         tc_fence_after();
         float v[32];
         tmem_ld32(lane_base + FB_DZ, v);
         if (valid) {
-          float4* de = reinterpret_cast<float4*>(p.d_emb + g * 32);
 #pragma unroll
-          for (int o = 0; o < 8; ++o) {
-            float4 x = make_float4(v[4 * o], v[4 * o + 1], v[4 * o + 2], v[4 * o + 3]);
-            if (p.accumulate_emb) { const float4 y = de[o]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
-            de[o] = x;
-          }
+          for (int o = 0; o < 8; ++o)
+            de[o] = make_float4(old[o].x + v[4 * o], old[o].y + v[4 * o + 1], old[o].z + v[4 * o + 2], old[o].w + v[4 * o + 3]);
         }
         tc_fence_before();
       }
@@ -877,16 +958,18 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_bwd_kernel(const __grid_c
   tc_fence_before();
   __syncthreads();
   // bias gradients: one atomic per column and CTA
-  for (int i = tid; i < 5 * 128; i += FM_THREADS) {
+  for (int i = tid; i < 5 * 128; i += FB_THREADS) {
     const int s = i >> 7;
-    if (s < na && p.db1[s] && s_db1[i] != 0.f) atomicAdd(p.db1[s] + (i & 127), s_db1[i]);
+    const float x = s_db1[i] + s_db1[640 + i] + s_db1[1280 + i] + s_db1[1920 + i];
+    if (s < na && p.db1[s] && x != 0.f) atomicAdd(p.db1[s] + (i & 127), x);
   }
-  for (int i = tid; i < 128; i += FM_THREADS)
-    if (p.dc1 && s_dc1[i] != 0.f) atomicAdd(p.dc1 + i, s_dc1[i]);
-  for (int i = tid; i < 5 * 48; i += FM_THREADS) {
+  for (int i = tid; i < 128; i += FB_THREADS)
+    if (p.dc1) atomicAdd(p.dc1 + i, s_dc1[i] + s_dc1[128 + i] + s_dc1[256 + i] + s_dc1[384 + i]);
+  for (int i = tid; i < 5 * 48; i += FB_THREADS) {
     const int s = i / 48, o = i - s * 48;
     if (s < na && o < p.hdim[s] && p.db2[s]) {
-      const float x = s_db2[p.goff[s] + o];
+      const int r = p.goff[s] + o;
+      const float x = s_db2[r] + s_db2[64 + r] + s_db2[128 + r] + s_db2[192 + r];
       if (x != 0.f) atomicAdd(p.db2[s] + o, x);
     }
   }
