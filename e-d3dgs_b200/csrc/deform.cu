@@ -717,49 +717,41 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
   TC_TRY(cudaGetLastError());
 
   if (g) {
-    {  // dW2_h[o][f] += sum_n GT[o][n] zT_h[f][n]: all gradient rows on the M side, two heads' activations on the N side
-      WgArgs a{};
-      a.N = N;
-      for (int i0 = 0; i0 < na; i0 += 2) {
-        WgGroup& gr = a.g[a.ngroups];
-        gr.P = wk.GT; gr.pk = 1; gr.prow_total = FB_GT_ROWS; gr.pcols = FB_GT_ROWS;
-        gr.Q = wk.zT[s] + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
-        for (int i = i0; i < i0 + 2 && i < na; ++i) {
-          const int h = act[i];
-          if (!g->head_w2[h]) continue;
-          gr.seg[gr.nseg++] = WgSegment{g->head_w2[h], 1, 128, (i - i0) * 128, 128, ba.goff[i], hHeadDim[h]};
-        }
-        if (gr.nseg > 0) ++a.ngroups;
-        else gr = WgGroup{};
+    // every weight gradient of the stage in one launch; the groups of a slice of Gaussians are adjacent work items, so
+    // hT / dzT / zT / GT are shared through L2
+    WgArgs a{};
+    a.N = N;
+    for (int i0 = 0; i0 < na; i0 += 2) {   // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n], two heads side by side (N = 256)
+      WgGroup& gr = a.g[a.ngroups];
+      gr = WgGroup{};
+      gr.P = wk.hT[s]; gr.pk = 1; gr.prow_total = 128; gr.pcols = 128;
+      gr.Q = wk.dzT + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
+      for (int i = i0; i < i0 + 2 && i < na; ++i) {
+        const int h = act[i];
+        if (!g->head_w1[h]) continue;
+        gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], 128, 1, (i - i0) * 128, 128, 0, 128};
       }
-      TC_TRY(tc_wgrad_launch(a, stream));
+      if (gr.nseg > 0) ++a.ngroups;
     }
-    {  // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n]
-      WgArgs a{};
-      a.N = N;
-      for (int i0 = 0; i0 < na; i0 += 2) {
-        WgGroup& gr = a.g[a.ngroups];
-        gr.P = wk.hT[s]; gr.pk = 1; gr.prow_total = 128; gr.pcols = 128;
-        gr.Q = wk.dzT + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
-        for (int i = i0; i < i0 + 2 && i < na; ++i) {
-          const int h = act[i];
-          if (!g->head_w1[h]) continue;
-          gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], 128, 1, (i - i0) * 128, 128, 0, 128};
-        }
-        if (gr.nseg > 0) ++a.ngroups;
-        else gr = WgGroup{};
-      }
-      TC_TRY(tc_wgrad_launch(a, stream));
+    for (int i = 0; i < na; ++i) {   // dW2_h[o][f] += sum_n zT_h[f][n] GT[goff_h + o][n]: 16 (48 for rgb) gradient rows on the N side
+      const int h = act[i];
+      if (!g->head_w2[h]) continue;
+      WgGroup& gr = a.g[a.ngroups++];
+      gr = WgGroup{};
+      gr.P = wk.zT[s] + (size_t)i * 128 * 128; gr.pk = 1; gr.prow_total = (long)na * 128; gr.pcols = 128;
+      gr.Q = wk.GT + (size_t)ba.goff[i] * 128; gr.qk = 1; gr.qrow_total = FB_GT_ROWS; gr.qcols = (hHeadDim[h] + 15) / 16 * 16;
+      gr.nseg = 1;
+      gr.seg[0] = WgSegment{g->head_w2[h], 128, 1, 0, hHeadDim[h], 0, 128};
     }
     if (g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dhT[o][n] emb[n][i]
-      WgArgs a{};
-      a.N = N; a.ngroups = 1;
-      a.g[0].P = emb; a.g[0].ldp = gemb; a.g[0].pcols = gemb;
-      a.g[0].Q = wk.dhT; a.g[0].qk = 1; a.g[0].qrow_total = 128; a.g[0].qcols = 128;
-      a.g[0].nseg = 1;
-      a.g[0].seg[0] = WgSegment{g->feat_w[0] + temb, ld0, 1, 0, 128, 0, gemb};
-      TC_TRY(tc_wgrad_launch(a, stream));
+      WgGroup& gr = a.g[a.ngroups++];
+      gr = WgGroup{};
+      gr.P = emb; gr.ldp = gemb; gr.pcols = gemb;
+      gr.Q = wk.dhT; gr.qk = 1; gr.qrow_total = 128; gr.qcols = 128;
+      gr.nseg = 1;
+      gr.seg[0] = WgSegment{g->feat_w[0] + temb, ld0, 1, 0, 128, 0, gemb};
     }
+    TC_TRY(tc_wgrad_launch(a, stream));
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, 128, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);

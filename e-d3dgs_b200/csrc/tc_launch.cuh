@@ -111,7 +111,8 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
   tc_encode_tiled_fn enc = tc_encode_tiled();
   if (!enc) return cudaErrorNotSupported;
   for (int i = 0; i < a.ngroups; ++i) {
-    const WgGroup& g = a.g[i];
+    WgGroup& g = a.g[i];
+    g.qbox = g.qk ? (g.qcols > 128 ? 256 : (g.qcols + 15) / 16 * 16) : 0;
     if (g.pcols <= 0 || g.pcols > 128 || (g.pcols & 3) || g.qcols <= 0 || g.qcols > 256 || (g.qcols & 3) ||
         (g.ldp & 3) || (g.ldq & 3) || g.nseg < 0 || g.nseg > 2 || (reinterpret_cast<uintptr_t>(g.P) & 15) ||
         (reinterpret_cast<uintptr_t>(g.Q) & 15))
@@ -133,7 +134,7 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
         const long rows_total = side ? g.qrow_total : g.prow_total;
         const cuuint64_t dims[3] = {128, (cuuint64_t)cols, ntiles};
         const cuuint64_t strides[2] = {128 * sizeof(float), (cuuint64_t)rows_total * 128 * sizeof(float)};
-        const cuuint32_t box[3] = {16, (cuuint32_t)(side && cols > 128 ? 256 : 128), 1};
+        const cuuint32_t box[3] = {16, (cuuint32_t)(side ? g.qbox : 128), 1};
         r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr3, CU_TENSOR_MAP_INTERLEAVE_NONE,
                 CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       } else {

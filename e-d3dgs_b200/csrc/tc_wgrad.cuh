@@ -25,7 +25,7 @@
 namespace ed3dgs {
 
 constexpr int WG_SLICE = 2048;                    // Gaussians per work item (tensor-core accumulation chain)
-constexpr int WG_MAX_GROUPS = 3;
+constexpr int WG_MAX_GROUPS = 9;                  // one stage's dW1 pairs, dW2 heads and dW0 in a single launch
 constexpr int WG_EPI_WARPS = 8;                   // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int WG_MMA_WARP = 8;
 constexpr int WG_LOAD_WARP = 9;
@@ -56,9 +56,15 @@ struct WgGroup {
   WgSegment seg[2];
   // Feature-major operands (written by the stage-resident kernels, fused_mlp.cuh): P / Q point at row 0 of a
   // [tile][rows_total][128 Gaussians] matrix; pk / qk select that layout per operand (K-major for the UMMA).
-  int pk, qk;
+  // A feature-major Q of qcols <= 128 rows is loaded and multiplied at its own width (qbox = qcols rounded up to 16, set
+  // by tc_wgrad_launch): the second-layer weight gradients have 16 or 48 columns, not 128.
+  int pk, qk, qbox;
   long prow_total, qrow_total;
 };
+__device__ __forceinline__ int wg_q_bytes(const WgGroup& g) {
+  return g.qk ? g.qbox * 64 : (g.qcols > 128 ? 8 : 4) * WG_BLOCK_BYTES;
+}
+__device__ __forceinline__ int wg_mma_n(const WgGroup& g) { return g.qk ? g.qbox : (g.qcols > 128 ? 256 : 128); }
 struct WgArgs {
   WgGroup g[WG_MAX_GROUPS];
   int ngroups;
@@ -133,7 +139,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
-      const int nchunks = (WG_P_BYTES + (p.g[group].qcols > 128 ? 8 : 4) * WG_BLOCK_BYTES) / 16;
+      const int nchunks = (WG_P_BYTES + wg_q_bytes(p.g[group])) / 16;
       for (int s = 0; s < nslab; ++s) {
         mbar_wait(&bars.hi_full[hr.idx], hr.phase);       // TMA bytes of this slab have landed
         const float4* src = reinterpret_cast<const float4*>(sHi + (size_t)hr.idx * WG_SLAB_BYTES);
@@ -164,7 +170,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
       long row0;
       item_setup(k, group, row0, nslab);
       const int nqb = p.g[group].qcols > 128 ? 8 : 4;
-      const uint32_t bytes = (uint32_t)(WG_P_BYTES + nqb * WG_BLOCK_BYTES);
+      const uint32_t bytes = (uint32_t)(WG_P_BYTES + wg_q_bytes(p.g[group]));
       for (int s = 0; s < nslab; ++s) {
         mbar_wait(&bars.hi_free[hr.idx], hr.phase ^ 1u);
         if (elect_one()) {
@@ -205,7 +211,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
       long row0;
       item_setup(k, group, row0, nslab);
       const bool pk = p.g[group].pk != 0, qk = p.g[group].qk != 0;
-      const uint32_t idesc = umma_idesc_tf32_mn(128, p.g[group].qcols > 128 ? 256 : 128, !pk, !qk);
+      const uint32_t idesc = umma_idesc_tf32_mn(128, wg_mma_n(p.g[group]), !pk, !qk);
       // feature-major operand = K-major, SWIZZLE_64B rows of 16 Gaussians (as the activation slabs of tc_rows.cuh):
       // SBO = 512 B between 8-row atoms, a k-step (8 Gaussians) advances the start by 32 B
       const uint32_t kdesc_hi = (512u >> 4) | (1u << 14) | (4u << 29);
