@@ -947,7 +947,10 @@ int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, c
   a.lda = lda; a.ldb = ldb;
   a.M = M; a.K = K; a.NT = NT; a.k_per_cta = k_per_cta > 0 ? k_per_cta : K;
   a.epilogue = epilogue; a.relu = 0; a.accumulate = 0; a.ones_col = ones_col; a.dbg = dbg;
-  static float* scratch = nullptr;
+  static float* scratch_of[64] = {};   // test entry: one scratch per device, never freed
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("tc_gemm: no current device"); return ED3DGS_ERR_CUDA; }
+  float*& scratch = scratch_of[dev];
   if (!scratch && cudaMalloc(&scratch, tc_prep_scratch_floats() * sizeof(float)) != cudaSuccess) {
     set_error("tc_gemm test scratch allocation failed");
     return ED3DGS_ERR_CUDA;

@@ -370,6 +370,7 @@ int knn_exact(int P, int K, const float* points, double* sq_dists, int* indices,
   knn_bounds<<<min((P + 255) / 256, 1184), 256, 0, stream>>>(P, points, w.bounds);
   knn_morton<<<(P + 255) / 256, 256, 0, stream>>>(P, points, w.bounds, w.bin.keys[2], w.bin.vals[2]);
   const int sel = radix_sort_pairs(w.bin, (uint32_t)P, 30, stream);
+  if (sel < 0) { set_error("radix_sort_pairs: %s", cudaGetErrorString(cudaGetLastError())); return ED3DGS_ERR_CUDA; }
   const int nboxes = (P + KNN_BOX - 1) / KNN_BOX;
   knn_gather_boxes<<<nboxes, KNN_BOX, 0, stream>>>(P, points, w.bin.vals[sel], w.sorted_pts, w.box_min, w.box_max);
   knn_box_bounds256<<<nb256, KNN2_BOX, 0, stream>>>(P, w.sorted_pts, bmin, bmax);
@@ -393,6 +394,7 @@ int dist_cuda2(int P, const float* points, float* mean_dists, void* workspace, s
   knn_bounds<<<min((P + 255) / 256, 1184), 256, 0, stream>>>(P, points, w.bounds);
   knn_morton<<<(P + 255) / 256, 256, 0, stream>>>(P, points, w.bounds, w.bin.keys[2], w.bin.vals[2]);
   const int sel = radix_sort_pairs(w.bin, (uint32_t)P, 30, stream);
+  if (sel < 0) { set_error("radix_sort_pairs: %s", cudaGetErrorString(cudaGetLastError())); return ED3DGS_ERR_CUDA; }
   const int nboxes = (P + KNN_BOX - 1) / KNN_BOX;
   knn_gather_boxes<<<nboxes, KNN_BOX, 0, stream>>>(P, points, w.bin.vals[sel], w.sorted_pts, w.box_min, w.box_max);
   knn_mean_dist<<<(P + KNN_THREADS - 1) / KNN_THREADS, KNN_THREADS, 0, stream>>>(P, w.sorted_pts, w.box_min,

@@ -244,15 +244,13 @@ radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__
   }
 }
 
-// Sorts pairs; returns the index (0/1) of the ping-pong half that holds the result.
+// Sorts pairs; returns the index (0/1) of the ping-pong half that holds the result, -1 on a CUDA error.
 int radix_sort_pairs(BinningState& b, uint32_t n, int end_bit, cudaStream_t stream) {
   if (n == 0) return 0;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)sizeof(ScatterSmem));
-    attr_set = true;
-  }
+  // a per-device attribute, set on every call (cheap; a process-wide flag would miss the second GPU of the process)
+  if (cudaFuncSetAttribute(radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScatterSmem)) !=
+      cudaSuccess)
+    return -1;
   const uint32_t nblocks = (uint32_t)sort_blocks(n);
   int cur = 2, dst = 0;  // first pass reads the (preserved) emission buffers
   for (int shift = 0; shift < end_bit; shift += 8) {

@@ -897,11 +897,10 @@ template <bool COORD, bool DEPTH>
 static int launch_blend_bwd(dim3 grid, cudaStream_t stream, const RasterBwdArgs& a, const GeomState& geom,
                             const ImageState& img, const uint32_t* plist, float fx, float fy) {
   using Cfg = BwdCfg<COORD, DEPTH>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(blend_bwd<COORD, DEPTH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem);
-    attr_set = true;
-  }
+  // per-device attribute: set on every launch
+  if (cudaFuncSetAttribute(blend_bwd<COORD, DEPTH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem) !=
+      cudaSuccess)
+    return 1;
   blend_bwd<COORD, DEPTH><<<grid, BWD_THREADS, Cfg::smem, stream>>>(
       img.ranges, plist, a.width, a.height, a.background, geom.rec, geom.rec_coord, a.alphas, img.accum_coord,
       img.accum_depth, img.normal_length, img.n_contrib, a.dL_dpix, a.dL_dpix_coord, a.dL_dpix_mcoord,
@@ -945,10 +944,12 @@ int raster_backward(const RasterBwdArgs& a, cudaStream_t stream) {
     ProfScope ps("blend_bwd", stream);
     const dim3 grid(gx, gy, 1);
     const uint32_t* plist = bin.vals[sel];
-    if (coord && depth) launch_blend_bwd<true, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);
-    else if (coord) launch_blend_bwd<true, false>(grid, stream, a, geom, img, plist, focal_x, focal_y);
-    else if (depth) launch_blend_bwd<false, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);
-    else launch_blend_bwd<false, false>(grid, stream, a, geom, img, plist, focal_x, focal_y);
+    int bad;
+    if (coord && depth) bad = launch_blend_bwd<true, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);
+    else if (coord) bad = launch_blend_bwd<true, false>(grid, stream, a, geom, img, plist, focal_x, focal_y);
+    else if (depth) bad = launch_blend_bwd<false, true>(grid, stream, a, geom, img, plist, focal_x, focal_y);
+    else bad = launch_blend_bwd<false, false>(grid, stream, a, geom, img, plist, focal_x, focal_y);
+    if (bad) { set_error("blend_bwd: %s", cudaGetErrorString(cudaGetLastError())); return ED3DGS_ERR_CUDA; }
   }
   if (a.debug) {
     err = cudaStreamSynchronize(stream);

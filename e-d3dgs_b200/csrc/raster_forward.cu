@@ -575,22 +575,21 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
 }
 
 template <bool COORD, bool DEPTH>
-static void launch_render_fwd(dim3 grid, cudaStream_t stream, const ImageState& img, const uint32_t* point_list,
+static cudaError_t launch_render_fwd(dim3 grid, cudaStream_t stream, const ImageState& img, const uint32_t* point_list,
                               int W, int H, const GeomState& geom, float fx, float fy, const float* bg,
                               float* out_color, float* out_coord, float* out_mcoord, float* out_depth,
                               float* out_mdepth, float* out_alpha, float* out_tongue, float* out_normal) {
   constexpr int NQ = (COORD || DEPTH) ? 4 : 3;
   constexpr int NQC = COORD ? REC_COORD_QUADS : 0;
   const size_t smem = 2 * (NQ + NQC) * RENDER_BATCH * sizeof(float4);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(render_fwd<COORD, DEPTH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+  // per-device attribute: set on every launch
+  const cudaError_t e = cudaFuncSetAttribute(render_fwd<COORD, DEPTH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
   render_fwd<COORD, DEPTH><<<grid, RENDER_THREADS, smem, stream>>>(
       img.ranges, point_list, W, H, geom.rec, geom.rec_coord, fx, fy, bg, out_color, out_coord, out_mcoord,
       out_depth, out_mdepth, out_alpha, out_tongue, out_normal, img.n_contrib, img.accum_depth,
       img.normal_length, img.accum_coord);
+  return cudaGetLastError();
 }
 
 // Next-highest bit of the MSB of n, i.e. bits needed for tile ids (rasterizer_impl.cu:35-50).
@@ -670,6 +669,7 @@ int raster_front(const RasterFwdArgs& a, float4* inte_rec, FrontEnd& fe, cudaStr
     ProfScope ps("radix_sort_pairs", stream);
     sel = radix_sort_pairs(bin, R, 32 + bit, stream);
     }
+    if (sel < 0) { set_error("radix_sort_pairs: %s", cudaGetErrorString(cudaGetLastError())); return ED3DGS_ERR_CUDA; }
     ED_DEBUG_SYNC("radix_sort");
   }
   fe.sel = sel;
@@ -705,16 +705,17 @@ int raster_forward(const RasterFwdArgs& a, cudaStream_t stream) {
   launch_render_fwd<C_, D_>(grid, stream, img, plist, W, H, geom, focal_x, focal_y, a.background,        \
                             a.out_color, a.out_coord, a.out_mcoord, a.out_depth, a.out_mdepth, a.out_alpha, \
                             a.out_tongue, a.out_normal)
+  cudaError_t render_err;
   {
   ProfScope ps("render_fwd", stream);
-  if (coord && depth) ED_RENDER(true, true);
-  else if (coord) ED_RENDER(true, false);
-  else if (depth) ED_RENDER(false, true);
-  else ED_RENDER(false, false);
+  if (coord && depth) render_err = ED_RENDER(true, true);
+  else if (coord) render_err = ED_RENDER(true, false);
+  else if (depth) render_err = ED_RENDER(false, true);
+  else render_err = ED_RENDER(false, false);
   }
 #undef ED_RENDER
+  ED_CHECK(render_err);
   ED_DEBUG_SYNC("render");
-  ED_CHECK(cudaGetLastError());
   return ED3DGS_OK;
 }
 

@@ -31,6 +31,7 @@ class _SsimL1(torch.autograd.Function):
                                                         maps.data_ptr(), _lib.stream_handle()))
         ctx.save_for_backward(x, y, maps)
         ctx.shape = img.shape
+        ctx.set_materialize_grads(False)   # an unused output arrives as None: one backward kernel, not two and an add
         out = (sums / x.numel()).float()
         return out[0], out[1]
 
@@ -41,6 +42,8 @@ class _SsimL1(torch.autograd.Function):
         B = x.numel() // (C * H * W)
         n = float(x.numel())
         # the two upstream scalars enter as device-side coefficients: d_img = g_l1/n * sign + g_ssim/n * dssim
+        if g_l1 is None and g_ssim is None:
+            return None, None
         d = torch.empty_like(x)
         d2 = None
         with torch.cuda.device(x.device):
@@ -83,7 +86,9 @@ class _PhotometricLoss(torch.autograd.Function):
         ctx.save_for_backward(x, y, maps)
         ctx.shape, ctx.lam = img.shape, float(lambda_dssim)
         m = (sums / x.numel()).float()
-        return m[0] + ctx.lam * (1 - m[1]) / 2, m[0], m[1]
+        l1, s = m[0].clone(), m[1].clone()
+        ctx.mark_non_differentiable(l1, s)   # reported values; build a loss from them and autograd says so loudly
+        return m[0] + ctx.lam * (1 - m[1]) / 2, l1, s
 
     @staticmethod
     def backward(ctx, g, _g_l1, _g_ssim):
@@ -165,20 +170,47 @@ def depth_normal_loss(view, rendered_expected_depth, rendered_median_depth, rend
                                   1.0 - depth_ratio, depth_ratio)
 
 
-@torch.no_grad()
+class _DepthDoubleToNormal(torch.autograd.Function):
+    """[2,3,H,W] normals of two depth maps, differentiable in both (the stencil of ed3dgs_depth_normal_backward with
+    the incoming gradient plane in the place of the rendered normal and coefficient -H*W, i.e. dL/dn = grad)."""
+
+    @staticmethod
+    def forward(ctx, depth1, depth2, fx, fy):
+        _check(depth1)
+        d1 = depth1.detach().contiguous().float()
+        d2 = depth2.detach().contiguous().float()
+        H, W = d1.shape[-2], d1.shape[-1]
+        out = torch.empty((2, 3, H, W), dtype=torch.float32, device=d1.device)
+        dummy_n = torch.zeros((3, H, W), dtype=torch.float32, device=d1.device)
+        sums = torch.empty(2, dtype=torch.float64, device=d1.device)
+        with torch.cuda.device(d1.device):
+            _lib.check(_lib.lib().ed3dgs_depth_normal_forward(H, W, float(fx), float(fy), d1.data_ptr(), d2.data_ptr(),
+                                                             dummy_n.data_ptr(), out.data_ptr(), sums.data_ptr(),
+                                                             _lib.stream_handle()))
+        ctx.save_for_backward(d1, d2)
+        ctx.cfg = (float(fx), float(fy), depth1.shape, depth2.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        d1, d2 = ctx.saved_tensors
+        fx, fy, s1, s2 = ctx.cfg
+        H, W = d1.shape[-2], d1.shape[-1]
+        g = g.contiguous().float()
+        g1, g2 = torch.empty_like(d1), torch.empty_like(d2)
+        hw = float(H * W)
+        with torch.cuda.device(d1.device):
+            lib = _lib.lib()
+            _lib.check(lib.ed3dgs_depth_normal_backward(H, W, fx, fy, d1.data_ptr(), d2.data_ptr(), g[0].data_ptr(), None,
+                                                       -hw, 0.0, g1.data_ptr(), None, None, _lib.stream_handle()))
+            _lib.check(lib.ed3dgs_depth_normal_backward(H, W, fx, fy, d1.data_ptr(), d2.data_ptr(), g[1].data_ptr(), None,
+                                                       0.0, -hw, None, g2.data_ptr(), None, _lib.stream_handle()))
+        return g1.view(s1), g2.view(s2), None, None
+
+
 def depth_double_to_normal(view, depth1, depth2):
-    """utils/graphics_utils.py:264-267: [2,3,H,W] normals from two depth maps (no gradient on this entry point; the
-    differentiable use is depth_normal_loss)."""
-    _check(depth1)
-    d1 = depth1.detach().contiguous().float()
-    d2 = depth2.detach().contiguous().float()
-    H, W = d1.shape[-2], d1.shape[-1]
+    """utils/graphics_utils.py:264-267: [2,3,H,W] normals from two depth maps, differentiable in both like the
+    reference's (train.py:253-266 back-propagates through it). depth_normal_loss is the fused form of the whole
+    regulariser and the cheaper call."""
     fx, fy = _focals(view)
-    out = torch.empty((2, 3, H, W), dtype=torch.float32, device=d1.device)
-    dummy_n = torch.zeros((3, H, W), dtype=torch.float32, device=d1.device)
-    sums = torch.empty(2, dtype=torch.float64, device=d1.device)
-    with torch.cuda.device(d1.device):
-        _lib.check(_lib.lib().ed3dgs_depth_normal_forward(H, W, float(fx), float(fy), d1.data_ptr(), d2.data_ptr(),
-                                                         dummy_n.data_ptr(), out.data_ptr(), sums.data_ptr(),
-                                                         _lib.stream_handle()))
-    return out
+    return _DepthDoubleToNormal.apply(depth1, depth2, fx, fy)

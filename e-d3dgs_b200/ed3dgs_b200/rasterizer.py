@@ -5,6 +5,7 @@ same ``GaussianRasterizationSettings`` fields, same ``GaussianRasterizer.forward
 libed3dgs_b200.so through its C ABI. PyTorch only owns memory, streams and autograd here.
 """
 import ctypes
+from types import SimpleNamespace
 from typing import NamedTuple
 
 import torch
@@ -13,11 +14,33 @@ import torch.nn as nn
 from . import _lib
 
 
-def _scalar(v, kind):
-    """Settings scalars may be python numbers or 0-dim (CUDA) tensors (gaussian_renderer/__init__.py:29-37)."""
-    if isinstance(v, torch.Tensor):
-        v = v.item()
-    return kind(v)
+_HOST_FIELDS = (("image_height", int), ("image_width", int), ("tanfovx", float), ("tanfovy", float),
+                ("kernel_size", float), ("scale_modifier", float), ("sh_degree", int))
+
+
+def host_scalars(rs):
+    """The seven settings scalars as python numbers. The reference's render() passes them as 0-dim CUDA tensors
+    (gaussian_renderer/__init__.py:29-37) and its extension reads each one back on its own; here all device-resident
+    ones come back in ONE transfer, once per settings object (forward, backward, integrate and markVisible share the
+    cached tuple). Python numbers (what ed3dgs_b200.renderer passes) cost nothing."""
+    cache = getattr(rs, "__dict__", None)
+    if cache is not None and "_host" in cache:
+        return cache["_host"]
+    vals = [getattr(rs, name) for name, _ in _HOST_FIELDS]
+    dev = [i for i, v in enumerate(vals) if isinstance(v, torch.Tensor) and v.is_cuda]
+    if dev:
+        got = torch.stack([vals[i].detach().reshape(()).double() for i in dev]).cpu().tolist()
+        for i, g in zip(dev, got):
+            vals[i] = g
+    out = {}
+    for (name, kind), v in zip(_HOST_FIELDS, vals):
+        if isinstance(v, torch.Tensor):
+            v = v.item()
+        out[name] = kind(v)
+    host = SimpleNamespace(**out)
+    if cache is not None:
+        cache["_host"] = host
+    return host
 
 
 def cpu_deep_copy_tuple(input_tuple):
@@ -274,10 +297,11 @@ class _RasterizeGaussians(torch.autograd.Function):
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, tongue_class, scales, rotations,
                 cov3Ds_precomp, raster_settings):
         rs = raster_settings
+        hs = host_scalars(rs)
         args = (rs.bg, means3D, colors_precomp, opacities, tongue_class, scales, rotations,
-                _scalar(rs.scale_modifier, float), cov3Ds_precomp, rs.viewmatrix, rs.projmatrix,
-                _scalar(rs.tanfovx, float), _scalar(rs.tanfovy, float), _scalar(rs.kernel_size, float),
-                _scalar(rs.image_height, int), _scalar(rs.image_width, int), sh, _scalar(rs.sh_degree, int),
+                hs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix,
+                hs.tanfovx, hs.tanfovy, hs.kernel_size,
+                hs.image_height, hs.image_width, sh, hs.sh_degree,
                 rs.campos, bool(rs.prefiltered), bool(rs.require_coord), bool(rs.require_depth), bool(rs.debug))
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
@@ -325,7 +349,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                 grad_rotations, grad_cov3Ds_precomp, None)
 
 
-class GaussianRasterizationSettings(NamedTuple):
+class _SettingsFields(NamedTuple):
     image_height: int
     image_width: int
     tanfovx: float
@@ -341,6 +365,11 @@ class GaussianRasterizationSettings(NamedTuple):
     require_depth: bool
     require_coord: bool
     debug: bool
+
+
+class GaussianRasterizationSettings(_SettingsFields):
+    """The reference's NamedTuple (__init__.py:176-191), same fields in the same order. The subclass only adds an
+    instance dict so host_scalars() can cache the python-number view of the scalar fields on the object."""
 
 
 class GaussianRasterizer(nn.Module):
@@ -388,10 +417,11 @@ class GaussianRasterizer(nn.Module):
         rotations = empty if rotations is None else rotations
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
         view2gaussian_precomp = empty if view2gaussian_precomp is None else view2gaussian_precomp
+        hs = host_scalars(rs)
         args = (rs.bg, points3D, means3D, colors_precomp, opacities, scales, rotations,
-                _scalar(rs.scale_modifier, float), cov3D_precomp, view2gaussian_precomp, rs.viewmatrix,
-                rs.projmatrix, _scalar(rs.tanfovx, float), _scalar(rs.tanfovy, float), 0.0, None,
-                _scalar(rs.image_height, int), _scalar(rs.image_width, int), shs, _scalar(rs.sh_degree, int),
+                hs.scale_modifier, cov3D_precomp, view2gaussian_precomp, rs.viewmatrix,
+                rs.projmatrix, hs.tanfovx, hs.tanfovy, 0.0, None,
+                hs.image_height, hs.image_width, shs, hs.sh_degree,
                 rs.campos, bool(rs.prefiltered), bool(rs.debug))
         with torch.no_grad():
             if rs.debug:

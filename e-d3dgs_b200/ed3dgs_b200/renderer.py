@@ -65,6 +65,21 @@ class GaussianScene(nn.Module):
     def get_embedding(self):
         return self._embedding
 
+    @property
+    def get_scaling(self):
+        return self.scaling_activation(self._scaling)
+
+    def get_covariance(self, scaling_modifier=1):
+        """gaussian_model.py:31-35,143-144: the six upper-triangle entries of (R S)(R S)^T."""
+        q = self._rotation / self._rotation.norm(dim=1, keepdim=True)
+        r, x, y, z = q.unbind(1)
+        R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                         2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                         2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).view(-1, 3, 3)
+        L = R @ torch.diag_embed(scaling_modifier * self.get_scaling)
+        c = L @ L.transpose(1, 2)
+        return torch.stack([c[:, 0, 0], c[:, 0, 1], c[:, 0, 2], c[:, 1, 1], c[:, 1, 2], c[:, 2, 2]], -1)
+
     @torch.no_grad()
     def compute_3D_filter(self, cameras):
         """gaussian_model.py:538-592"""
@@ -112,8 +127,16 @@ def render(viewpoint_camera, pc, pipe, bg_color, kernel_size, scaling_modifier=1
     means2D = screenspace_points
     opacity = pc._opacity
     shs = pc.get_features
-    scales = pc._scaling
-    rotations = pc._rotation
+    scales = None
+    rotations = None
+    cov3D_precomp = None
+    if getattr(pipe, "compute_cov3D_python", False):
+        # as in the reference (:66-67) the deformation below then receives scales = rotations = None and raises
+        # TypeError on scales[:, :3] (deformation.py:107): the flag cannot be combined with the deformation network
+        cov3D_precomp = pc.get_covariance(scaling_modifier)
+    else:
+        scales = pc._scaling
+        rotations = pc._rotation
     means3D_final, scales_final, rotations_final, opacity_final, shs_final, extras = pc._deformation(
         means3D, scales, rotations, opacity, time, cam_no, pc, None, shs, iter=iter, num_down_emb_c=num_down_emb_c,
         num_down_emb_f=num_down_emb_f)
@@ -131,7 +154,7 @@ def render(viewpoint_camera, pc, pipe, bg_color, kernel_size, scaling_modifier=1
                                                                               scales=scales_final)
     outputs = rasterizer(means3D=means3D_final, means2D=means2D, shs=shs_final if override_color is None else None,
                          colors_precomp=override_color, opacities=opacity, tongue_class=pc.tongue_class,
-                         scales=scales_final, rotations=rotations_final, cov3D_precomp=None)
+                         scales=scales_final, rotations=rotations_final, cov3D_precomp=cov3D_precomp)
     assert len(outputs) == 9, "only (depth-)diff-gaussian-rasterization from RaDe-GS supported!"
     (rendered_image, radii, rendered_expected_coord, rendered_median_coord, rendered_expected_depth,
      rendered_median_depth, rendered_alpha, rendered_tongue, rendered_normal) = outputs

@@ -184,8 +184,10 @@ def assert_report(rep, rs, noise=None):
     # differ by > 1e-3 * scale on a handful of Gaussians at P = 300K (tests/diag_c2.py). For those three
     # the bound is therefore per Gaussian: all but a few outliers meet GRAD_RTOL in max-norm (no more
     # outliers than 3x what the reference shows against itself, floor 8), and the l2 error over the rest
-    # meets GRAD_RTOL.
-    loose_keys = ("dL_dcov3D", "dL_dscales", "dL_drotations")
+    # meets GRAD_RTOL. dL_dmeans3D receives one term through the same chain (the projected covariance
+    # depends on the mean, backward.cu computeCov2DCUDA), so the same Gaussians can surface there: at C5
+    # (3 M Gaussians, R = 40 M) exactly one does, at 1.3e-3, with the trimmed l2 error at 3e-6.
+    loose_keys = ("dL_dcov3D", "dL_dscales", "dL_drotations", "dL_dmeans3D")
     for k, v in rep.items():
         if not k.startswith("grad_"):
             continue
@@ -195,7 +197,10 @@ def assert_report(rep, rs, noise=None):
         elif not loose and (k.endswith("_l2rel") or k.endswith("_relerr")):
             assert v <= GRAD_RTOL, (k, v, rep)
         elif loose and k.endswith("_l2rel_trim"):
-            assert v <= GRAD_RTOL, (k, v, rep)
+            # at the full sizes the reference's own two runs differ by more than GRAD_RTOL in this norm (the Gaussians
+            # just under the outlier threshold dominate it): the bound is then 3x that self-noise
+            nz = float(noise.get(k, 0.0)) if noise else 0.0
+            assert v <= max(GRAD_RTOL, 3.0 * nz), (k, v, nz, rep)
         elif loose and k.endswith("_outliers"):
             nz = int(noise.get(k, 0)) if noise else 0
             assert v <= max(8, 3 * nz), (k, v, nz, rep)

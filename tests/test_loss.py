@@ -71,6 +71,22 @@ def test_gpu_losses_match_golden(idx):
     assert _rel(nr.grad.cpu(), rec["d_normal"]) <= GRAD_RTOL
     dn = L.depth_double_to_normal(view, rec["depth_e"].cuda(), rec["depth_m"].cuda())
     assert float((dn.cpu() - rec["normals_from_depth"]).abs().max()) <= 1e-5
+    # differentiable like the reference's (train.py:253-266 back-propagates through it): a seeded upstream gradient
+    # on the [2,3,H,W] normals against autograd through the oracle's torch statements
+    up = torch.randn(dn.shape, generator=torch.Generator().manual_seed(idx + 1))
+    a = [rec[k].clone().cuda().requires_grad_(True) for k in ("depth_e", "depth_m")]
+    b = [rec[k].clone().requires_grad_(True) for k in ("depth_e", "depth_m")]
+    (L.depth_double_to_normal(view, *a) * up.cuda()).sum().backward()
+    (loss_oracle.depth_double_to_normal(view, *b) * up).sum().backward()
+    for x, y in zip(a, b):
+        assert x.grad is not None and _rel(x.grad.cpu(), y.grad) <= GRAD_RTOL
+    # the regulariser built from it, as train.py writes it, equals the fused depth_normal_loss
+    c = [rec[k].clone().cuda().requires_grad_(True) for k in ("depth_e", "depth_m", "normal")]
+    nrm = L.depth_double_to_normal(view, c[0], c[1])
+    err = 1 - (c[2].unsqueeze(0) * nrm).sum(dim=1)
+    (0.4 * err[0].mean() + 0.6 * err[1].mean()).backward()
+    for x, k in zip(c, ("d_depth_e", "d_depth_m", "d_normal")):
+        assert _rel(x.grad.cpu(), rec[k]) <= GRAD_RTOL, k
 
 
 @pytest.mark.gpu
