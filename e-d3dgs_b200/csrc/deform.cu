@@ -743,13 +743,13 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
       gr.nseg = 1;
       gr.seg[0] = WgSegment{g->head_w2[h], 128, 1, 0, hHeadDim[h], 0, 128};
     }
-    if (g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dhT[o][n] emb[n][i]
+    if (g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dhT[o][n] emb[n][i]: the 32 embedding columns on the N side
       WgGroup& gr = a.g[a.ngroups++];
       gr = WgGroup{};
-      gr.P = emb; gr.ldp = gemb; gr.pcols = gemb;
-      gr.Q = wk.dhT; gr.qk = 1; gr.qrow_total = 128; gr.qcols = 128;
+      gr.P = wk.dhT; gr.pk = 1; gr.prow_total = 128; gr.pcols = 128;
+      gr.Q = emb; gr.ldq = gemb; gr.qcols = gemb;
       gr.nseg = 1;
-      gr.seg[0] = WgSegment{g->feat_w[0] + temb, ld0, 1, 0, 128, 0, gemb};
+      gr.seg[0] = WgSegment{g->feat_w[0] + temb, 1, ld0, 0, gemb, 0, 128};
     }
     TC_TRY(tc_wgrad_launch(a, stream));
   }

@@ -6,6 +6,7 @@
 #include "tc_rows.cuh"
 #include "tc_wgrad.cuh"
 #include "profiler.h"
+#include <cstdlib>
 
 namespace ed3dgs {
 
@@ -151,7 +152,9 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
     const cudaError_t e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
     if (e != cudaSuccess) return e;
   }
-  const int items = ((a.N + WG_SLICE - 1) / WG_SLICE) * a.ngroups;
+  static const int slice_env = [] { const char* e = getenv("ED3DGS_WG_SLICE"); const int v = e ? atoi(e) : 0; return v >= 128 ? v / 128 * 128 : 0; }();
+  a.slice = slice_env ? slice_env : WG_SLICE;
+  const int items = ((a.N + a.slice - 1) / a.slice) * a.ngroups;
   const int grid = items < tc_sm_count() ? items : tc_sm_count();
   ProfScope ps("tc_wgrad_kernel", stream);
   tc_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(a);

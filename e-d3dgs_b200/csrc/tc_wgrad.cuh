@@ -24,7 +24,7 @@
 
 namespace ed3dgs {
 
-constexpr int WG_SLICE = 2048;                    // Gaussians per work item (tensor-core accumulation chain)
+constexpr int WG_SLICE = 2048;                    // default Gaussians per work item (tensor-core accumulation chain)
 constexpr int WG_MAX_GROUPS = 9;                  // one stage's dW1 pairs, dW2 heads and dW0 in a single launch
 constexpr int WG_EPI_WARPS = 8;                   // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int WG_MMA_WARP = 8;
@@ -61,14 +61,15 @@ struct WgGroup {
   int pk, qk, qbox;
   long prow_total, qrow_total;
 };
-__device__ __forceinline__ int wg_q_bytes(const WgGroup& g) {
-  return g.qk ? g.qbox * 64 : (g.qcols > 128 ? 8 : 4) * WG_BLOCK_BYTES;
-}
-__device__ __forceinline__ int wg_mma_n(const WgGroup& g) { return g.qk ? g.qbox : (g.qcols > 128 ? 256 : 128); }
+// Row-major (MN-major) Q: blocks of 32 features, as many as its columns need (1..4, or 8 for two heads side by side).
+__device__ __forceinline__ int wg_q_blocks(const WgGroup& g) { return g.qcols > 128 ? 8 : (g.qcols + 31) >> 5; }
+__device__ __forceinline__ int wg_q_bytes(const WgGroup& g) { return g.qk ? g.qbox * 64 : wg_q_blocks(g) * WG_BLOCK_BYTES; }
+__device__ __forceinline__ int wg_mma_n(const WgGroup& g) { return g.qk ? g.qbox : 32 * wg_q_blocks(g); }
 struct WgArgs {
   WgGroup g[WG_MAX_GROUPS];
   int ngroups;
   int N;            // Gaussians
+  int slice;        // Gaussians per work item (multiple of 128)
   // tensor maps of P and Q of every group: dims {cols, N}, box {32, 16}, SWIZZLE_128B_ATOM_32B (tc_wgrad_launch)
   alignas(64) CUtensorMap pmap[WG_MAX_GROUPS];
   alignas(64) CUtensorMap qmap[WG_MAX_GROUPS];
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
   tc_fence_after();
   const uint32_t tmem = s_tmem;
 
-  const int nslices = (p.N + WG_SLICE - 1) / WG_SLICE;
+  const int nslices = (p.N + p.slice - 1) / p.slice;
   const int nitems = nslices * p.ngroups;
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -123,8 +124,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
     const int item = (int)blockIdx.x + k * (int)gridDim.x;
     const int slice = item / p.ngroups;
     group = item - slice * p.ngroups;
-    row0 = (long)slice * WG_SLICE;
-    const int rows = (int)min((long)WG_SLICE, (long)p.N - row0);
+    row0 = (long)slice * p.slice;
+    const int rows = (int)min((long)p.slice, (long)p.N - row0);
     nslab = (rows + 15) >> 4;
   };
 
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
-      const int nqb = p.g[group].qcols > 128 ? 8 : 4;
+      const int nqb = wg_q_blocks(p.g[group]);
       const uint32_t bytes = (uint32_t)(WG_P_BYTES + wg_q_bytes(p.g[group]));
       for (int s = 0; s < nslab; ++s) {
         mbar_wait(&bars.hi_free[hr.idx], hr.phase ^ 1u);

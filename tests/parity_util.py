@@ -161,6 +161,14 @@ def compare(rs, a, b):
                 keep = (~bad).view(-1, *([1] * (x.dim() - 1))) & fin
                 nk = float(y[keep.expand_as(y)].double().norm())
                 rep["grad_" + k + "_l2rel_trim"] = (float((x - y)[keep.expand_as(y)].double().norm()) / nk) if nk > 0 else 0.0
+                # the 64 worst Gaussians with their share of the squared error / squared norm: lets assert_report
+                # evaluate "l2 error without the K worst Gaussians" for any K <= 64 (a fixed COUNT instead of a
+                # threshold, so that Gaussians sitting just under the threshold cannot flip the verdict run to run)
+                d2 = torch.where(fin, (x - y).double() ** 2, torch.zeros_like(y, dtype=torch.float64)).flatten(1).sum(1)
+                y2 = torch.where(fin, y.double() ** 2, torch.zeros_like(y, dtype=torch.float64)).flatten(1).sum(1)
+                top = torch.topk(e, min(64, e.numel())).indices
+                rep["grad_" + k + "_worst"] = dict(e=e[top].tolist(), d2=d2[top].tolist(), y2=y2[top].tolist(),
+                                                   d2_total=float(d2.sum()), y2_total=float(y2.sum()))
             rep["grad_" + k + "_nonfinite_diff"] = int((torch.isfinite(x) != fin).sum())
     return rep
 
@@ -182,9 +190,9 @@ def assert_report(rep, rs, noise=None):
     # Gaussians (an axis at the 1e-5 scale floor) are numerically unstable in the reference itself: its
     # per-Gaussian stage changes by O(1) under any rounding difference, and two runs of the REFERENCE
     # differ by > 1e-3 * scale on a handful of Gaussians at P = 300K (tests/diag_c2.py). For those three
-    # the bound is therefore per Gaussian: all but a few outliers meet GRAD_RTOL in max-norm (no more
-    # outliers than 3x what the reference shows against itself, floor 8), and the l2 error over the rest
-    # meets GRAD_RTOL. dL_dmeans3D receives one term through the same chain (the projected covariance
+    # the bound is therefore per Gaussian: all but the K worst Gaussians meet GRAD_RTOL in max-norm (K = 3x the number the
+    # reference misses against itself, floor 8), and the l2 error over the rest meets GRAD_RTOL (or 3x what two runs of the
+    # reference show with the same K). dL_dmeans3D receives one term through the same chain (the projected covariance
     # depends on the mean, backward.cu computeCov2DCUDA), so the same Gaussians can surface there: at C5
     # (3 M Gaussians, R = 40 M) exactly one does, at 1.3e-3, with the trimmed l2 error at 3e-6.
     loose_keys = ("dL_dcov3D", "dL_dscales", "dL_drotations", "dL_dmeans3D")
@@ -196,14 +204,24 @@ def assert_report(rep, rs, noise=None):
             assert v == 0, (k, rep)
         elif not loose and (k.endswith("_l2rel") or k.endswith("_relerr")):
             assert v <= GRAD_RTOL, (k, v, rep)
-        elif loose and k.endswith("_l2rel_trim"):
-            # at the full sizes the reference's own two runs differ by more than GRAD_RTOL in this norm (the Gaussians
-            # just under the outlier threshold dominate it): the bound is then 3x that self-noise
-            nz = float(noise.get(k, 0.0)) if noise else 0.0
-            assert v <= max(GRAD_RTOL, 3.0 * nz), (k, v, nz, rep)
-        elif loose and k.endswith("_outliers"):
-            nz = int(noise.get(k, 0)) if noise else 0
-            assert v <= max(8, 3 * nz), (k, v, nz, rep)
+        elif loose and k.endswith("_worst"):
+            # all but K Gaussians meet GRAD_RTOL in max-norm, K = 3x the number the reference misses against itself
+            # (floor 8); the l2 error over the rest meets GRAD_RTOL or 3x the reference's own figure with the same K
+            # (at the full sizes two runs of the reference differ by more than GRAD_RTOL in this norm)
+            nz = noise.get(k) if noise else None
+            nz_out = int(noise.get(k[:-len("_worst")] + "_outliers", 0)) if noise else 0
+            K = min(max(8, 3 * nz_out), 63)
+            assert len(v["e"]) <= K or v["e"][K] <= GRAD_RTOL, (k, K, v["e"][:K + 1], rep)
+            t = trimmed_l2(v, K)
+            tn = trimmed_l2(nz, K) if nz else 0.0
+            assert t <= max(GRAD_RTOL, 3.0 * tn), (k, K, t, tn, rep)
+
+
+def trimmed_l2(w, K):
+    """Relative l2 error without the K worst Gaussians of a compare() "_worst" record."""
+    d2 = w["d2_total"] - sum(w["d2"][:K])
+    y2 = w["y2_total"] - sum(w["y2"][:K])
+    return (max(d2, 0.0) / y2) ** 0.5 if y2 > 0 else 0.0
 
 
 def fmt(rep):

@@ -50,8 +50,12 @@ def _p(t):
 class RefRasterizer:
     """One reference rasterizer context (owns the geom/binning/image buffers)."""
 
-    def __init__(self):
+    def __init__(self, sync=True):
+        """sync=False (timing runs): no device synchronisation around the calls. The shim launches on the legacy
+        default stream, which is also torch's current stream, so ordering holds without it; the reference's own
+        blocking read-back of the instance count (rasterizer_impl.cu:359) stays."""
         self.ctx = lib().ref_create()
+        self.sync = sync
 
     def __del__(self):
         try:
@@ -71,7 +75,8 @@ class RefRasterizer:
         M = shs.shape[1] if shs is not None and shs.numel() else 0
         self.saved = dict(rs=rs, means3D=means3D, shs=shs, colors_precomp=colors_precomp, scales=scales,
                           rotations=rotations, cov3D_precomp=cov3D_precomp, M=M, out=out)
-        torch.cuda.synchronize()
+        if self.sync:
+            torch.cuda.synchronize()
         R = lib().ref_forward(
             self.ctx, P, int(rs.sh_degree), M, _p(rs.bg), W, H, _p(means3D), _p(shs), _p(colors_precomp),
             _p(opacities), _p(tongue_class), _p(scales), float(rs.scale_modifier), _p(rotations), _p(cov3D_precomp),
@@ -79,7 +84,8 @@ class RefRasterizer:
             float(rs.kernel_size), int(rs.prefiltered), _p(out["color"]), _p(out["coord"]), _p(out["mcoord"]),
             _p(out["depth"]), _p(out["mdepth"]), _p(out["alpha"]), _p(out["tongue"]), _p(out["normal"]),
             _p(out["radii"]), int(rs.require_coord), int(rs.require_depth), int(rs.debug))
-        torch.cuda.synchronize()
+        if self.sync:
+            torch.cuda.synchronize()
         if R < 0:
             raise RuntimeError(lib().ref_last_error().decode())
         self.R = R
@@ -100,7 +106,8 @@ class RefRasterizer:
                    dL_dcolors=z(P, 3), dL_dts=z(P, 1), dL_dcamera_planes=z(P, 6), dL_dray_planes=z(P, 2),
                    dL_dnormals=z(P, 3), dL_dmeans3D=z(P, 3), dL_dcov3D=z(P, 6), dL_dsh=z(P, M, 3),
                    dL_dscales=z(P, 3), dL_drotations=z(P, 4))
-        torch.cuda.synchronize()
+        if self.sync:
+            torch.cuda.synchronize()
         st = lib().ref_backward(
             self.ctx, P, int(rs.sh_degree), M, self.R, _p(rs.bg), W, H, _p(s["means3D"]), _p(s["shs"]),
             _p(s["colors_precomp"]), _p(out["alpha"]), _p(s["scales"]), float(rs.scale_modifier), _p(s["rotations"]),
@@ -113,7 +120,8 @@ class RefRasterizer:
             _p(res["dL_dnormals"]), _p(res["dL_dmeans3D"]), _p(res["dL_dcov3D"]), _p(res["dL_dsh"]),
             _p(res["dL_dscales"]), _p(res["dL_drotations"]),
             int(rs.require_coord), int(rs.require_depth), int(rs.debug))
-        torch.cuda.synchronize()
+        if self.sync:
+            torch.cuda.synchronize()
         if st != 0:
             raise RuntimeError(lib().ref_last_error().decode())
         return res
