@@ -37,15 +37,45 @@ def parse():
     ap.add_argument("--workload", default="C3")
     ap.add_argument("--splat-scale", type=float, default=0.3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
     return ap.parse_args()
 
 
 def load_peaks():
+    """HBM GB/s and dense bf16 TFLOP/s: MEASURED_PEAKS.json (driver-written) else the profiling recipe's fallback.
+    The tf32 tensor peak the MLP rooflines use is measured in this run (measure_tf32_peak) and falls back to half
+    the sustained bf16 figure."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return dict(hbm_gbs=d["hbm_gbs"], tensor_tflops=d.get("bf16_tflops_sustained", d["bf16_tflops"]), source="measured")
-    return dict(hbm_gbs=6650.0, tensor_tflops=1400.0, source="fallback")
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d.get("bf16_tflops_sustained", d["bf16_tflops"]), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1400.0, source="fallback")
+
+
+def measure_tf32_peak(device, n=8192, iters=10):
+    """cuBLAS tf32 throughput on this GPU, the denominator of the MLP tensor rooflines: torch.matmul of fp32
+    n^3 with TF32 allowed, best of `iters` (burst) -- measured outside every timed region; the flag is restored."""
+    keep = torch.backends.cuda.matmul.allow_tf32
+    try:
+        torch.backends.cuda.matmul.allow_tf32 = True
+        a = torch.randn(n, n, device=device)
+        b = torch.randn(n, n, device=device)
+        for _ in range(3):
+            a @ b
+        best = 1e30
+        for _ in range(iters):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    except Exception:  # noqa: BLE001
+        return None
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = keep
+        torch.cuda.empty_cache()
 
 
 class SmiClockSampler:
@@ -161,11 +191,22 @@ class ClockSampler:
                     samples=len(sm))
 
 
+def workload_hyper(cfg):
+    """ModelHiddenParams of the dataset config a workload stands for: nersemble / dynerf
+    defaults for C1-C4, technicolor (arguments/technicolor/default.py:6-24: defor_depth 0, no SH head, 5/25
+    temporal embeddings) for C5."""
+    from ed3dgs_b200.renderer import default_hyper
+    kw = dict(total_num_frames=cfg["frames"])
+    if cfg.get("family") == "technicolor":
+        kw.update(defor_depth=0, no_dc=True, min_embeddings=5, max_embeddings=25)
+    return default_hyper(**kw)
+
+
 def build_scene(cfg, splat_scale, device, n_cams=16):
     from ed3dgs_b200 import synthetic
-    from ed3dgs_b200.renderer import GaussianScene, default_hyper
+    from ed3dgs_b200.renderer import GaussianScene
     g = synthetic.make_gaussians(cfg["P"], splat_scale=splat_scale, device="cpu")
-    hyper = default_hyper(total_num_frames=cfg["frames"])
+    hyper = workload_hyper(cfg)
     torch.manual_seed(synthetic.SEED)
     scene = GaussianScene(g, hyper, sh_degree=cfg["sh_degree"]).to(device)
     with torch.no_grad():
@@ -198,30 +239,48 @@ def profile_report():
     return out
 
 
+def profile_pairs():
+    import ctypes
+    from ed3dgs_b200 import _lib
+    lib = _lib.lib()
+    out = (ctypes.c_ulonglong * 2)()
+    lib.ed3dgs_profile_pairs.restype = ctypes.c_int
+    lib.ed3dgs_profile_pairs.argtypes = [ctypes.POINTER(ctypes.c_ulonglong)]
+    return (int(out[0]), int(out[1])) if lib.ed3dgs_profile_pairs(out) == 0 else None
+
+
 def profile_enable(on):
     from ed3dgs_b200 import _lib
     _lib.lib().ed3dgs_profile_enable(1 if on else 0)
 
 
-def algorithmic_work(cfg, hyper, R, visible_frac, sort_passes):
-    """Per-step algorithmic bytes / flops of each kernel group."""
-    P, px = cfg["P"], cfg["W"] * cfg["H"]
-    W = hyper.net_width
+MLP_GROUPS = ("fused_fwd_kernel", "fused_bwd_kernel", "tc_wgrad_kernel",
+              "tc_rows_kernel<fwd>", "tc_rows_kernel<dgrad>")
+RASTER_GROUPS = ("preprocess_fwd", "scan_tiles", "emit_keys", "radix_sort_pairs", "tile_ranges", "render_fwd",
+                 "blend_bwd", "gaussian_bwd")
+
+
+def mlp_shape(hyper):
     heads = [True, not hyper.no_ds, not hyper.no_dr, not hyper.no_do, not hyper.no_dc]
     k_on = sum(k for k, on in zip((3, 3, 4, 1, 48), heads) if on)
     stages = (0 if hyper.no_coarse_deform else 1) + (0 if hyper.no_fine_deform else 1)
-    nh, ge, D = sum(heads), hyper.gaussian_embedding_dim, hyper.defor_depth
-    # Deformation network: HBM bytes per Gaussian per stage that the algorithm cannot avoid with
-    # activations kept in fp32 for the backward pass (DESIGN.md 3): every activation matrix is written once
-    # by its producer and read once by each consumer GEMM; weights (<= 0.6 MB) are L2-resident.
-    fwd_b = 4 * ((ge + W) + (D - 1) * 2 * W + (W + nh * W) + (nh * W + 2 * k_on))
-    dgrad_b = 4 * ((80 + 2 * nh * W) + (nh * W + 2 * W) + (D - 1) * 3 * W + (W + ge))
-    wgrad_b = 4 * ((80 + nh * W) + (W + nh * W) + (D - 1) * 2 * W + (ge + W))
+    return dict(W=hyper.net_width, nh=sum(heads), k_on=k_on, stages=stages, ge=hyper.gaussian_embedding_dim,
+                D=max(hyper.defor_depth, 1))
+
+
+def algorithmic_work(cfg, hyper, R, visible_frac):
+    """Per-step algorithmic work of each kernel group, exactly as SURVEY.md 8(d) / BASELINE.md 5 define it.
+    Deformation network: TENSOR model on the minimal flops -- per stage and pass (forward, input gradients, weight
+    gradients) 2*(32*W + (D-1)*W^2 + H_on*W^2 + W*k_on) flop per Gaussian (187 136 at the defaults; 1.123 MFLOP
+    per Gaussian for forward + backward of both stages); the kernels execute 3 tf32 MMAs per algorithmic product
+    (3xTF32) and are reported against this 1x figure. Rasterizer kernels: HBM bytes."""
+    P, px = cfg["P"], cfg["W"] * cfg["H"]
+    m = mlp_shape(hyper)
+    W, nh, k_on, stages, ge, D = m["W"], m["nh"], m["k_on"], m["stages"], m["ge"], m["D"]
+    flop_pass = 2 * (ge * W + (D - 1) * W * W + nh * W * W + W * k_on) * stages * P
     V = visible_frac
-    return {
-        "tc_rows_kernel<fwd>": ("hbm", fwd_b * stages * P),
-        "tc_rows_kernel<dgrad>": ("hbm", dgrad_b * stages * P + (4 * ge * P if stages == 2 else 0)),
-        "tc_wgrad_kernel": ("hbm", wgrad_b * stages * P),
+    work = {name: ("tensor", flop_pass) for name in MLP_GROUPS}
+    work.update({
         "preprocess_fwd": ("hbm", P * (240 + 143 * V)),
         "scan_tiles": ("hbm", 8 * P),
         "emit_keys": ("hbm", 20 * P + 12 * R),
@@ -230,7 +289,6 @@ def algorithmic_work(cfg, hyper, R, visible_frac, sort_passes):
         "render_fwd": ("hbm", 68 * R + 56 * px),
         "blend_bwd": ("hbm", 128 * R + 68 * px),
         "gaussian_bwd": ("hbm", (367 + 260) * V * P),
-        "build_head_grads": ("hbm", (236 + 320) * P),
         # fused activations: forward reads + writes 32 B per Gaussian, backward reads 64 B and writes 32 B
         "activations": ("hbm", (64 + 96) * P),
         # fused image losses: image + target read, three derivative maps written / read back, gradient written
@@ -238,13 +296,39 @@ def algorithmic_work(cfg, hyper, R, visible_frac, sort_passes):
         "ssim_l1_backward": ("hbm", 3 * px * 4 * (2 + 3 + 1)),
         "depth_normal_forward": ("hbm", px * 4 * 5),
         "depth_normal_backward": ("hbm", px * 4 * (5 + 5)),
+    })
+    return work
+
+
+def mlp_hbm_model(hyper, P):
+    """HBM side of the deformation kernels, bytes per step. `algorithmic` is SURVEY 8(d)'s figure for a fully fused
+    network (forward: 364 B in + 236 B out + 236 B extras per Gaussian for both stages together; backward: the
+    upstream gradients of the outputs and of the coarse-stage extras in, the embedding gradient out; the weight
+    gradients need no per-Gaussian bytes of their own). `design` is what THIS design moves: the forward leaves the
+    post-ReLU activations feature-major per 128-Gaussian tile (zT, hT) and the ReLU masks, the backward chain leaves
+    dzT / dhT / GT, and the weight-gradient kernel contracts those matrices over the Gaussians."""
+    m = mlp_shape(hyper)
+    W, nh, k_on, stages, ge = m["W"], m["nh"], m["k_on"], m["stages"], m["ge"]
+    out_b = 4 * k_on
+    masks = (nh + 1) * (W // 8)
+    fwd = stages * (4 * ge + out_b + out_b + 4 * W * (nh + 1) + masks)
+    bwd = stages * (2 * out_b + masks + 4 * W * (nh + 1) + 4 * 64 + 4 * ge) + 4 * ge
+    wg = stages * (2 * 4 * W * nh + 2 * 4 * W + 4 * 64 + 4 * ge)
+    return {
+        "fused_fwd_kernel": {"algorithmic": (4 * ge + 3 * out_b + 4 * ge) * P if stages else 0, "design": fwd * P},
+        "fused_bwd_kernel": {"algorithmic": (2 * out_b + 4 * ge) * P, "design": bwd * P},
+        "tc_wgrad_kernel": {"algorithmic": 0, "design": wg * P},
     }
+
+
+SORT_DIGIT_BITS = 8
+SORT_LAUNCHES_PER_PASS, SORT_LAUNCHES_FIXED = 5, 0   # csrc/radix_sort.cu: hist, scan x3, scatter per pass
 
 
 def launches_per_step(prof, steps, sort_passes):
     """Kernel launches of THIS library per step, from its own event scopes (a scope holding
     several launches is weighted; the dozen tiny unscoped kernels are added as a constant)."""
-    mult = {"scan_tiles": 3, "radix_sort_pairs": 5 * sort_passes}
+    mult = {"scan_tiles": 3, "radix_sort_pairs": SORT_LAUNCHES_PER_PASS * sort_passes + SORT_LAUNCHES_FIXED}
     n = 0
     for name, (_ms, cnt) in prof.items():
         n += cnt * mult.get(name, 1)
@@ -253,98 +337,121 @@ def launches_per_step(prof, steps, sort_passes):
 
 # ------------------------------------------------------------------------------------------------
 # CPU legs: the oracle port (oracle/deform_oracle.py + oracle/oracle_raster.cpp) on the host cores.
-def cpu_step_sample(cfg, splat_scale, sample_P, scale_div, iters=1):
-    """One fwd+bwd step of the SAME pipeline on the CPU oracle, on a bounded sample of the workload:
-    the first sample_P Gaussians of the scene, image and focal divided by scale_div."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import deform_oracle
-    import loss_oracle
-    import raster_oracle
-    from ed3dgs_b200 import synthetic
-    from ed3dgs_b200.renderer import default_hyper
-    from ed3dgs_b200.deformation import deform_network
-    torch.set_num_threads(os.cpu_count() or 1)
-    W, H = cfg["W"] // scale_div, cfg["H"] // scale_div
-    focal = cfg["focal_full"] * cfg["W"] / cfg["full_w"] / scale_div
-    g = synthetic.make_gaussians(sample_P, splat_scale=splat_scale * (cfg["P"] / sample_P) ** (1 / 3) * 0.5, device="cpu")
-    hyper = default_hyper(total_num_frames=cfg["frames"])
-    torch.manual_seed(synthetic.SEED)
-    net = deform_network(W=hyper.net_width, D=hyper.defor_depth, args=hyper)
-    sd = {k: v.detach().clone().requires_grad_(True) for k, v in net.state_dict().items()}
-    cam = synthetic.make_camera(3, 16, W, H, focal, frame=21, frames=cfg["frames"], device="cpu")
-    rs = synthetic.raster_settings(cam, cfg["sh_degree"], kernel_size=0.0, require_coord=False, require_depth=True)
-    gt = torch.rand(3, H, W, generator=torch.Generator().manual_seed(1))
-    times = []
-    for _ in range(iters):
+# ONE helper serves both the GPU arm's `cpu_baseline` and `--impl reference`, so the two figures are the same
+# measurement: the FULL workload (same seeded scene, same camera, same loss as the GPU arm), no extrapolation.
+class CpuReference:
+    """The reference path restated for the host cores: torch-CPU deformation oracle (fp32, all threads) ->
+    activations -> C++/OpenMP rasterizer oracle -> the reference's torch losses -> backward through all of it."""
+
+    def __init__(self, cfg, splat_scale):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import deform_oracle
+        import loss_oracle
+        import raster_oracle
+        from ed3dgs_b200 import synthetic
+        torch.set_num_threads(os.cpu_count() or 1)
+        self.mods = (deform_oracle, loss_oracle, raster_oracle)
+        self.cfg = cfg
+        scene, cams = build_scene(cfg, splat_scale, "cpu")
+        self.hyper = scene.hyper
+        self.sd = {k: v.detach().clone().requires_grad_(True) for k, v in scene._deformation.state_dict().items()}
+        self.g = dict(xyz=scene._xyz.detach(), scaling=scene._scaling.detach(), rotation=scene._rotation.detach(),
+                      opacity=scene._opacity.detach(), embedding=scene._embedding.detach(),
+                      features=torch.cat((scene._features_dc, scene._features_rest), 1).detach())
+        self.tongue = scene.tongue_class
+        self.cams = cams
+        self.sh_degree = cfg["sh_degree"]
+        self.gt = torch.rand(3, cfg["H"], cfg["W"], generator=torch.Generator().manual_seed(11))
+        self.R = 0
+
+    def step(self, i=0):
+        """One fwd+bwd step at the full size. Returns (total, network, rasterizer+loss) seconds."""
+        deform_oracle, loss_oracle, raster_oracle = self.mods
+        from ed3dgs_b200 import synthetic
+        hyper, cfg = self.hyper, self.cfg
+        cam = self.cams[i % len(self.cams)]
+        P = cfg["P"]
+        rs = synthetic.raster_settings(cam, self.sh_degree, kernel_size=0.0, require_coord=False, require_depth=True)
         t0 = time.perf_counter()
-        leaves = {k: v.clone().requires_grad_(True) for k, v in g.items() if k != "tongue_class"}
-        time_emb = torch.tensor(cam.time).repeat(sample_P, 1)
-        out = deform_oracle.forward(sd, hyper, max(hyper.defor_depth, 1), hyper.max_embeddings, leaves["xyz"],
-                                    leaves["scaling"], leaves["rotation"], leaves["opacity"], time_emb, 1,
-                                    leaves["embedding"], leaves["features"], 20000)
+        for v in self.sd.values():
+            v.grad = None
+        leaves = {k: v.clone().requires_grad_(True) for k, v in self.g.items()}
+        time_emb = torch.tensor(cam.time).repeat(P, 1)
+        out = deform_oracle.forward(self.sd, hyper, max(hyper.defor_depth, 1), hyper.max_embeddings, leaves["xyz"],
+                                    leaves["scaling"], leaves["rotation"], leaves["opacity"], time_emb, cam.uid % 30,
+                                    leaves["embedding"], leaves["features"], 20000,
+                                    num_down_emb_c=hyper.min_embeddings, num_down_emb_f=hyper.min_embeddings)
         means, scales = out[0], torch.exp(out[1])
         rots, opac = torch.nn.functional.normalize(out[2]), torch.sigmoid(out[3])
         t1 = time.perf_counter()
         orc = raster_oracle.OracleRasterizer()
-        R, o = orc.forward(rs, means, opac, g["tongue_class"], shs=out[4], scales=scales, rotations=rots)
-        # the step's loss (renderer.training_loss) through the torch restatement of the reference's losses
+        self.R, o = orc.forward(rs, means, opac, self.tongue, shs=out[4], scales=scales, rotations=rots)
         names = ("color", "depth", "mdepth", "alpha", "normal")
         leaf = {k: o[k].clone().requires_grad_(True) for k in names}
-        loss = (loss_oracle.l1_loss(leaf["color"], gt) + 0.2 * (1 - loss_oracle.ssim(leaf["color"], gt)) / 2
+        loss = (loss_oracle.l1_loss(leaf["color"], self.gt) + 0.2 * (1 - loss_oracle.ssim(leaf["color"], self.gt)) / 2
                 + 0.05 * loss_oracle.depth_normal_loss(cam, leaf["depth"], leaf["mdepth"], leaf["normal"])
                 + 0.01 * leaf["alpha"].mean())
         gr = dict(zip(names, torch.autograd.grad(loss, [leaf[k] for k in names])))
         gb = orc.backward(gr)
         t2 = time.perf_counter()
-        # chain through the activations and the deformation oracle (torch autograd on CPU)
         torch.autograd.backward(
             [means, scales, rots, opac, out[4]],
             [gb["dL_dmeans3D"], gb["dL_dscales"], gb["dL_drotations"], gb["dL_dopacity"], gb["dL_dsh"]])
         t3 = time.perf_counter()
-        times.append((t3 - t0, (t1 - t0) + (t3 - t2), t2 - t1))
-    times.sort()
-    return times[len(times) // 2], R, (W, H)
+        return t3 - t0, (t1 - t0) + (t3 - t2), t2 - t1
 
+    def run(self, steps, warmup, budget_s):
+        """`warmup` untimed full steps (at least one, so thread pools, allocator and page cache are warm), then up
+        to `steps` timed ones; stops early once `budget_s` seconds of timed work are spent (never below 1 step)."""
+        for i in range(max(1, warmup)):
+            self.step(i)
+        ts, spent = [], 0.0
+        for i in range(max(1, steps)):
+            t = self.step(i)
+            ts.append(t)
+            spent += t[0]
+            if spent >= budget_s:
+                break
+        med = sorted(ts)[len(ts) // 2]
+        return med, ts
 
-# instances of the full seeded scene at splat_scale 0.3 (measured by the GPU arm: config.num_rendered)
-FULL_R = {"C3": 8_819_050}
-
-
-def cpu_full_workload(cfg, workload, sample_P, t3, R_sample):
-    """Seconds per full-workload step extrapolated from the sample: the deformation network scales with
-    the number of Gaussians, the rasterizer with the number of (tile, Gaussian) instances."""
-    _t, t_mlp, t_raster = t3
-    R_full = FULL_R.get(workload, R_sample * cfg["P"] / sample_P * 2.5)
-    return t_mlp * cfg["P"] / sample_P + t_raster * R_full / max(R_sample, 1)
+    def describe(self, med, ts, asked_steps):
+        c = self.cfg
+        return (f"FULL workload, no extrapolation: {c['P']} Gaussians at {c['W']}x{c['H']}, R={self.R}, same scene / "
+                f"cameras / loss as the GPU arm; torch-CPU fp32 deformation oracle + C++/OpenMP rasterizer oracle on "
+                f"{os.cpu_count()} threads; {len(ts)} timed steps of {asked_steps} asked (time-capped) after a full "
+                f"warm-up step, median {med[0]:.2f} s (network {med[1]:.2f} s, rasterizer + losses {med[2]:.2f} s)")
 
 
 def run_reference_arm(args, rank, world):
-    """--impl reference: the CPU port of the reference path on rank 0, bounded sample per step."""
+    """--impl reference: the CPU port of the reference path on rank 0: full-size steps, honouring --steps/--warmup
+    up to a wall-clock cap (BENCH_REF_BUDGET_S, default 120 s of timed steps; warm-up capped at 1 full step)."""
     if rank != 0:
         return
     from ed3dgs_b200 import synthetic
     cfg = synthetic.CONFIGS[args.workload]
-    sample_P, div = 20_000, 4
-    for _ in range(max(args.warmup, 0) and 1):
-        cpu_step_sample(cfg, args.splat_scale, sample_P, div)
-    ts = []
-    R = 0
-    for _ in range(max(1, min(args.steps, 5))):
-        t3, R, wh = cpu_step_sample(cfg, args.splat_scale, sample_P, div)
-        ts.append(t3)
-    t3 = tuple(sum(x[i] for x in ts) / len(ts) for i in range(3))
-    t_full = cpu_full_workload(cfg, args.workload, sample_P, t3, R)
-    sample = (f"{sample_P} Gaussians of the {args.workload} scene at {wh[0]}x{wh[1]} (1/{div} linear resolution), "
-              f"R={R}, fwd+bwd, torch-CPU deformation oracle + C++/OpenMP rasterizer oracle: {t3[0]:.2f} s per sample step "
-              f"(network {t3[1]:.2f} s, rasterizer {t3[2]:.2f} s); value = full-workload views/s extrapolated with "
-              f"network time x P/sample_P and rasterizer time x R/R_sample")
-    line = {"impl": "reference", "metric": METRIC, "value": 1.0 / t_full, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": len(ts), "warmup": 1, "ms_per_step": t_full * 1e3, "higher_is_better": True, "scaling": "weak",
+    budget = float(os.environ.get("BENCH_REF_BUDGET_S", "120"))
+    ref = CpuReference(cfg, args.splat_scale)
+    med, ts = ref.run(args.steps, min(max(args.warmup, 1), 1), budget)
+    mean = sum(t[0] for t in ts) / len(ts)
+    sample = ref.describe(med, ts, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": 1.0 / mean, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": len(ts), "warmup": 1, "ms_per_step": mean * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload} (CPU leg runs a bounded sample: {sample})"},
-            "cpu_baseline": {"value": 1.0 / t_full, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
-            "e2e": {"value": 1.0 / t_full, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "config": workload_config(args.workload, cfg, args.splat_scale, ref.R, 1, None),
+            "cpu_baseline": {"value": 1.0 / mean, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
+            "e2e": {"value": 1.0 / mean, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def workload_config(name, cfg, splat_scale, R, world, vis):
+    """The `config` object both arms print (same keys, so the driver sees the same workload)."""
+    d = {"workload": f"{name}: {cfg['P']} Gaussians, {cfg['W']}x{cfg['H']}, SH degree {cfg['sh_degree']}, "
+                     f"variant <coord=0,depth=1,normal=1>, kernel_size 0, one view per rank per step",
+         "num_rendered": R, "R_over_P": R / cfg["P"], "splat_scale": splat_scale, "views_per_step": world}
+    if vis is not None:
+        d["visible_fraction"] = vis
+    return d
 
 
 # ------------------------------------------------------------------------------------------------
@@ -533,6 +640,36 @@ def run_ours(args, rank, local, world):
         multi = {"allreduce_ms": float(mt_max[0]), "compute_only_ms_per_step_max_rank": float(mt_max[1]),
                  "compute_only_ms_per_step_min_rank": float(mt[1])}
 
+    # ---- sustained leg (untimed for the headline): the same loop for >= BENCH_SUSTAINED_S seconds with the clock
+    #      sampler running, so the line also says what a long training run holds once clocks settle ----
+    sustained = None
+    sus_s = float(os.environ.get("BENCH_SUSTAINED_S", "3"))
+    if sus_s > 0:
+        s_sampler = sampler_cls(local) if rank == 0 and os.environ.get("BENCH_CLOCKS") != "off" else None
+        n_sus = max(args.steps, int(sus_s * 1e3 / max(ms_total / args.steps, 1e-3)) + 1)
+        gc.disable()
+        barrier()
+        if s_sampler:
+            s_sampler.mark_begin()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(n_sus):
+            v = view_of(i)
+            step(i, cams_dev[v], gts_dev[v % 4])
+        s1.record()
+        barrier()
+        gc.enable()
+        ms_sus = s0.elapsed_time(s1) / n_sus
+        sc = None
+        if s_sampler:
+            s_sampler.mark_end()
+            sc = s_sampler.stop()
+        st = torch.tensor([ms_sus], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        sustained = {"steps": n_sus, "seconds": float(st[0]) * n_sus / 1e3, "ms_per_step": float(st[0]),
+                     "value": world * 1e3 / float(st[0]), "unit": UNIT, "clocks": sc}
+
     # ---- roofline pass: per-kernel CUDA-event times from the library's own scopes ----
     prof_steps = min(args.steps, 5)
     profile_enable(True)
@@ -541,64 +678,119 @@ def run_ours(args, rank, local, world):
         step(i, cams_dev[v], gts_dev[v % 4])
     torch.cuda.synchronize()
     prof = profile_report()
+    pairs = profile_pairs()
     profile_enable(False)
 
     t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, ms_e2e = float(t[0]), float(t[1])
+
+    # ---- GPU reference leg (N = 1, rank 0, outside every product timing): BASELINE.md B1 + B2 ----
+    gpu_ref = None
+    if world == 1 and not args.no_gpu_reference:
+        try:
+            gpu_ref = gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R)
+        except Exception as ex:  # noqa: BLE001
+            gpu_ref = {"unavailable": f"{type(ex).__name__}: {ex}"}
+        torch.cuda.empty_cache()
     if rank != 0:
         return
     ms_step = ms_total / args.steps
     ms_step_e2e = ms_e2e / args.steps
     peaks = load_peaks()
+    tf32_measured = measure_tf32_peak(device)
+    tf32_peak = tf32_measured if tf32_measured else 0.5 * peaks["bf16_tflops"]
+    tf32_src = ("cuBLAS tf32 measured in this run (torch.matmul fp32 8192^3, TF32 allowed, best of 10)" if tf32_measured
+                else "half of the bf16 figure (tf32 probe failed)")
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     bits = 32 + max(1, math.ceil(math.log2(tiles + 1)))
-    sort_passes = (bits + 7) // 8
-    work = algorithmic_work(cfg, hyper, R, vis, sort_passes)
+    sort_passes = (bits + SORT_DIGIT_BITS - 1) // SORT_DIGIT_BITS
+    work = algorithmic_work(cfg, hyper, R, vis)
+    hbm_side = mlp_hbm_model(hyper, cfg["P"])
     breakdown = {k: ms / prof_steps for k, (ms, n) in prof.items()}
     launches = {k: n / prof_steps for k, (ms, n) in prof.items()}
+    try:   # DRAM traffic per step from ncu --set full captures of this build (profiles/r02_traffic.json)
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            measured = json.load(f)["per_step_bytes"] if args.workload == "C3" else {}
+    except (OSError, KeyError, ValueError):
+        measured = {}
     rooflines = {}
     for name, ms in breakdown.items():
         if name not in work or ms <= 0:
             continue
         bound, amount = work[name]
-        per_launch = amount / max(launches[name], 1)
-        dur = ms / max(launches[name], 1) * 1e-3
+        nl = max(launches[name], 1)
+        per_launch = amount / nl
+        dur = ms / nl * 1e-3
         if bound == "hbm":
             ach, peak, unit = per_launch / dur / 1e9, peaks["hbm_gbs"], "GB/s"
         else:
-            ach, peak, unit = per_launch / dur / 1e12, peaks["tensor_tflops"], "TFLOP/s"
-        rooflines[name] = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
-                           "traffic": None, "ms_per_step": ms, "launches_per_step": launches[name],
-                           "algorithmic_per_step": amount}
-    # DRAM traffic measured once with ncu --set full (profiles/r01_traffic.json), per launch like `achieved`
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            measured = json.load(f)["per_step_bytes"]
-        if args.workload == "C3":
-            for name, b in measured.items():
-                if name in rooflines:
-                    rooflines[name]["traffic"] = b / max(rooflines[name]["launches_per_step"], 1)
-    except (OSError, KeyError, ValueError):
-        pass
+            ach, peak, unit = per_launch / dur / 1e12, tf32_peak, "TFLOP/s"
+        r = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
+             "traffic": (measured[name] / nl) if name in measured else None, "ms_per_step": ms,
+             "launches_per_step": launches[name], "algorithmic_per_step": amount}
+        if name in hbm_side:
+            h = hbm_side[name]
+            r["hbm_model"] = {"algorithmic_bytes_per_step": h["algorithmic"], "design_bytes_per_step": h["design"],
+                              "design_gbs": h["design"] / (ms * 1e-3) / 1e9,
+                              "design_frac_of_hbm_peak": h["design"] / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                              "traffic_over_design": (measured[name] / h["design"]) if name in measured else None}
+        rooflines[name] = r
+    # section-level lines, the definitions of BASELINE.md section 5
+    mlp_ms = sum(breakdown.get(k, 0.0) for k in MLP_GROUPS) + breakdown.get("fused_prepare", 0.0) + \
+        breakdown.get("tc_prepare_b", 0.0) + breakdown.get("build_head_grads", 0.0)
+    ras_ms = sum(breakdown.get(k, 0.0) for k in RASTER_GROUPS)
+    sections = {}
+    if mlp_ms > 0:
+        m = mlp_shape(hyper)
+        flop = 3 * work["fused_fwd_kernel"][1]
+        mlp_traffic = sum(measured.get(k, 0) for k in MLP_GROUPS) or None
+        sections["mlp"] = {"bound": "tensor", "ms_per_step": mlp_ms, "algorithmic_flop_per_step": flop,
+                           "achieved": flop / (mlp_ms * 1e-3) / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
+                           "frac": flop / (mlp_ms * 1e-3) / 1e12 / tf32_peak,
+                           "frac_of_bf16_peak": flop / (mlp_ms * 1e-3) / 1e12 / peaks["bf16_tflops"],
+                           "executed_over_algorithmic": 3.0, "launches_per_step": sum(
+                               launches.get(k, 0) for k in MLP_GROUPS + ("fused_prepare", "tc_prepare_b", "build_head_grads")),
+                           "hbm_algorithmic_bytes_per_step": sum(h["algorithmic"] for h in hbm_side.values()),
+                           "hbm_traffic_bytes_per_step": mlp_traffic, "shape": m}
+    if ras_ms > 0:
+        P_, px_ = cfg["P"], W * H
+        b_ras = P_ * (268 + 770 * vis) + 240 * R + 124 * px_
+        sm_mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
+        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6
+        e_f, e_b = (pairs[0] / prof_steps, pairs[1] / prof_steps) if pairs else (None, None)
+        sec = {"bound": "hbm", "ms_per_step": ras_ms, "algorithmic_bytes_per_step": b_ras,
+               "achieved": b_ras / (ras_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+               "frac": b_ras / (ras_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+               "traffic_bytes_per_step": sum(measured.get(k, 0) for k in RASTER_GROUPS) or None,
+               "fp32_alu": {"pairs_listed": R * 256, "pairs_walked_fwd": e_f, "pairs_walked_bwd": e_b,
+                            "flop_per_pair": {"fwd": 30, "bwd": 110}, "peak_tflops": fp32_peak / 1e12,
+                            "peak_how": "148 SMs x 128 FMA x 2 x max SM clock (derived, BASELINE.md 2)"}}
+        blend_ms = breakdown.get("render_fwd", 0.0) + breakdown.get("blend_bwd", 0.0)
+        if e_f is not None and blend_ms > 0:
+            fl = 30 * e_f + 110 * e_b
+            sec["fp32_alu"].update({"flop_per_step": fl, "blend_kernels_ms": blend_ms,
+                                    "achieved_tflops": fl / (blend_ms * 1e-3) / 1e12,
+                                    "frac": fl / (blend_ms * 1e-3) / fp32_peak,
+                                    "frac_listed_pairs_model": 140 * R * 256 / (blend_ms * 1e-3) / fp32_peak})
+        sections["rasterizer"] = sec
     dominant = max(rooflines, key=lambda k: rooflines[k]["ms_per_step"]) if rooflines else None
-    roof = dict(rooflines[dominant], kernel=dominant, peak_source=peaks["source"]) if dominant else None
+    roof = dict(rooflines[dominant], kernel=dominant, peak_source=(
+        tf32_src if rooflines[dominant]["bound"] == "tensor" else "MEASURED_PEAKS.json" if peaks["source"] == "measured"
+        else "B200_PROFILING.md fallback")) if dominant else None
     if roof and roof["bound"] == "tensor":
-        roof["note"] = ("peak = measured bf16 cuBLAS (sustained); the kernel runs kind::tf32 (nominal half rate) and "
-                        "executes 3 MMAs per algorithmic product (3xTF32), so frac <= 1/6 by construction")
+        roof["note"] = ("algorithmic flops = minimal formulation of SURVEY 8(d) for ONE pass (this kernel) over both "
+                        "stages; the kernel executes 3 tf32 MMAs per algorithmic product (3xTF32, fp32-grade "
+                        "parity), so frac <= 1/3 by construction")
     line = {
         "metric": METRIC, "value": world * 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 (rasterizer fp32; MLP 3xTF32 on tcgen05, fp32-grade)", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {cfg['P']} Gaussians, {W}x{H}, SH degree {cfg['sh_degree']}, "
-                               f"variant <coord=0,depth=1,normal=1>, kernel_size 0, one view per rank per step",
-                   "num_rendered": R, "R_over_P": R / cfg["P"], "visible_fraction": vis,
-                   "splat_scale": args.splat_scale, "views_per_step": world,
-                   "l2_policy": "per-step working set (Gaussian records 64 MB + keys/lists %.0f MB + MLP activations "
-                                "%.1f GB) exceeds the 126 MB L2" % (R * 36 / 1e6, cfg["P"] * 9.9e3 / 1e9),
-                   "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi,
-                   "host": host_info},
+        "config": dict(workload_config(args.workload, cfg, args.splat_scale, R, world, vis), **{
+            "l2_policy": "per-step working set (Gaussian records 64 MB + keys/lists %.0f MB + MLP activations "
+                         "%.1f GB) exceeds the 126 MB L2" % (R * 36 / 1e6, cfg["P"] * 7.0e3 / 1e9),
+            "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi, "host": host_info}),
         "clocks": clocks,
         "e2e": {"value": world * 1e3 / ms_step_e2e, "unit": UNIT, "ms_per_step": ms_step_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
@@ -607,23 +799,118 @@ def run_ours(args, rank, local, world):
                         "ahead, like a prefetching loader) and the loss is copied back to pinned host memory"},
         "gpu_launches": launches_per_step(prof, prof_steps, sort_passes) * args.steps,
         "roofline": roof,
+        "roofline_sections": sections,
         "roofline_all": rooflines,
+        "sustained": sustained,
+        "gpu_reference": gpu_ref,
         "loss_last": host_losses[-1] if host_losses else None,
     }
     if world == 1 and not args.no_cpu_baseline:
         try:
-            t3, R_cpu, wh = cpu_step_sample(cfg, args.splat_scale, 20_000, 4)
-            t_full = cpu_full_workload(cfg, args.workload, 20_000, t3, R_cpu)
-            line["cpu_baseline"] = {
-                "value": 1.0 / t_full, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-                "sample": f"20000 Gaussians of the {args.workload} scene at {wh[0]}x{wh[1]} (1/4 linear resolution), "
-                          f"R={R_cpu}, one fwd+bwd step, torch-CPU deformation oracle + C++/OpenMP rasterizer oracle: "
-                          f"{t3[0]:.2f} s (network {t3[1]:.2f} s, rasterizer {t3[2]:.2f} s); value = full-workload views/s "
-                          f"extrapolated with network time x P/20000 and rasterizer time x R/R_sample"}
+            ref = CpuReference(cfg, args.splat_scale)
+            med, ts = ref.run(int(os.environ.get("BENCH_CPU_STEPS", "1")), 1, float(os.environ.get("BENCH_CPU_BUDGET_S", "30")))
+            mean = sum(x[0] for x in ts) / len(ts)
+            line["cpu_baseline"] = {"value": 1.0 / mean, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                    "sample": ref.describe(med, ts, len(ts))}
         except Exception as ex:  # noqa: BLE001
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"failed: {ex}"}
     print(json.dumps(line))
+
+
+def gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R_product, warm=3, iters=10):
+    """BASELINE.md section 3, B1 + B2 on the same GPU and the same seeded inputs, outside the product's timed
+    regions: the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built from /root/reference by oracle/Makefile)
+    wired through autograd like diff_gaussian_rasterization/__init__.py:46-174 wires it, the deformation network as
+    the reference's own torch statements (oracle/deform_oracle.py: F.linear -> cuBLAS SGEMM, TF32 off) and the
+    reference's torch losses. A reported baseline (the "3x" denominator); nothing here is on the product path."""
+    import ctypes  # noqa: F401
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import deform_oracle
+    import ref_binding
+    from ed3dgs_b200 import synthetic
+    from ed3dgs_b200.renderer import training_loss
+    if not os.path.exists(ref_binding.REF_LIB):
+        return {"unavailable": "oracle/_ref/libref_ed3dgs.so not built (needs /root/reference at build time)"}
+    keep_tf32 = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = ref_binding.RefRasterizer(sync=False)
+    marks = {}
+
+    def mark(name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        marks[name] = e
+
+    class RefRaster(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, means3D, sh, opac, scales, rots, rs, tongue):
+            _R, out = ref.forward(rs, means3D.contiguous(), opac.contiguous(), tongue, shs=sh.contiguous(),
+                                  scales=scales.contiguous(), rotations=rots.contiguous())
+            return out["color"], out["depth"], out["mdepth"], out["alpha"], out["normal"]
+
+        @staticmethod
+        def backward(ctx, gc_, gd, gmd, ga, gn):
+            mark("raster_bwd_begin")
+            g = ref.backward(dict(color=gc_, depth=gd, mdepth=gmd, alpha=ga, normal=gn))
+            mark("raster_bwd_end")
+            return g["dL_dmeans3D"], g["dL_dsh"], g["dL_dopacity"], g["dL_dscales"], g["dL_drotations"], None, None
+
+    params = dict(scene.named_parameters())
+    sd = {k[len("_deformation."):]: v for k, v in params.items() if k.startswith("_deformation.")}
+    P = cfg["P"]
+    hyper = scene.hyper
+    bg = torch.zeros(3, device=device)
+
+    def ref_step(i):
+        cam, gt = cams_dev[i % len(cams_dev)], gts_dev[i % len(gts_dev)]
+        rs = synthetic.raster_settings(cam, cfg["sh_degree"], kernel_size=0.0, require_coord=False, require_depth=True, bg=bg)
+        for p_ in scene.parameters():
+            p_.grad = None
+        mark("begin")
+        time_emb = torch.full((P, 1), cam.time, device=device)
+        shs = torch.cat((scene._features_dc, scene._features_rest), dim=1)
+        out = deform_oracle.forward(sd, hyper, max(hyper.defor_depth, 1), hyper.max_embeddings, scene._xyz,
+                                    scene._scaling, scene._rotation, scene._opacity, time_emb, cam.uid % 30,
+                                    scene._embedding, shs, 20000, num_down_emb_c=hyper.min_embeddings,
+                                    num_down_emb_f=hyper.min_embeddings)
+        rots = torch.nn.functional.normalize(out[2])
+        scales, opac = torch.exp(out[1]), torch.sigmoid(out[3])
+        mark("mlp_fwd_end")
+        color, depth, mdepth, alpha, normal = RefRaster.apply(out[0], out[4], opac, scales, rots, rs, scene.tongue_class)
+        mark("raster_fwd_end")
+        pkg = dict(render=color, expected_depth=depth, median_depth=mdepth, mask=alpha, normal=normal)
+        training_loss(pkg, gt, view=cam, fused=False).backward()
+        mark("end")
+
+    try:
+        for i in range(warm):
+            ref_step(i)
+        torch.cuda.synchronize()
+        rows = []
+        for i in range(iters):
+            ref_step(i)
+            torch.cuda.synchronize()
+            m = marks
+            rows.append(dict(total=m["begin"].elapsed_time(m["end"]),
+                             mlp_fwd=m["begin"].elapsed_time(m["mlp_fwd_end"]),
+                             raster_fwd=m["mlp_fwd_end"].elapsed_time(m["raster_fwd_end"]),
+                             loss_fwd_bwd=m["raster_fwd_end"].elapsed_time(m["raster_bwd_begin"]),
+                             raster_bwd=m["raster_bwd_begin"].elapsed_time(m["raster_bwd_end"]),
+                             mlp_bwd=m["raster_bwd_end"].elapsed_time(m["end"])))
+        med = {k: sorted(r[k] for r in rows)[len(rows) // 2] for k in rows[0]}
+        return {"what": "unmodified reference CUDA rasterizer (oracle/_ref) + the reference's torch fp32 deformation "
+                        "network (cuBLAS SGEMM, TF32 off) + the reference's torch losses, same scene / views / loss, "
+                        f"median of {iters} after {warm} warm-ups, CUDA events, outside the product's timed regions",
+                "ms_per_step": med["total"], "value": 1e3 / med["total"], "unit": UNIT,
+                "sections_ms": {k: v for k, v in med.items() if k != "total"},
+                "mlp_ms": med["mlp_fwd"] + med["mlp_bwd"], "raster_ms": med["raster_fwd"] + med["raster_bwd"],
+                "num_rendered_last": int(ref.R), "num_rendered_product": R_product}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = keep_tf32
+        for p_ in scene.parameters():
+            p_.grad = None
 
 
 def main():

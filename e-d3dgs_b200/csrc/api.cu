@@ -21,7 +21,9 @@ struct ProfRec { const char* name; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;
 static std::mutex g_prof_mu;
+static unsigned long long* g_pair_counters = nullptr;
 bool prof_enabled() { return g_prof_on; }
+unsigned long long* prof_pair_counters() { return g_prof_on ? g_pair_counters : nullptr; }
 void prof_push(const char* name, cudaEvent_t a, cudaEvent_t b) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   g_prof.push_back(ProfRec{name, a, b});
@@ -97,7 +99,26 @@ extern "C" {
 const char* ed3dgs_last_error(void) { return g_error; }
 const char* ed3dgs_version(void) { return "0.1.0 (sm_100a)"; }
 
-void ed3dgs_profile_enable(int on) { g_prof_on = on != 0; }
+void ed3dgs_profile_enable(int on) {
+  g_prof_on = on != 0;
+  if (g_prof_on) {   // pair counters live on the device that is current when profiling is switched on
+    if (!g_pair_counters && cudaMalloc(&g_pair_counters, 2 * sizeof(unsigned long long)) != cudaSuccess) g_pair_counters = nullptr;
+    if (g_pair_counters) cudaMemset(g_pair_counters, 0, 2 * sizeof(unsigned long long));
+  }
+}
+
+// (pixel, Gaussian) pairs walked since profiling was switched on: out[0] by the forward blend (list entries up to
+// each pixel's early exit), out[1] by the backward blend (up to each pixel's last contributor). Resets the counters.
+int ed3dgs_profile_pairs(unsigned long long* out) {
+  if (!out || !g_pair_counters) { set_error("profile_pairs: profiling was never enabled"); return ED3DGS_ERR_ARG; }
+  if (cudaDeviceSynchronize() != cudaSuccess ||
+      cudaMemcpy(out, g_pair_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("profile_pairs: %s", cudaGetErrorString(cudaGetLastError()));
+    return ED3DGS_ERR_CUDA;
+  }
+  cudaMemset(g_pair_counters, 0, 2 * sizeof(unsigned long long));
+  return ED3DGS_OK;
+}
 
 // Synchronises the device, writes "name total_ms launches\n" lines into buf and clears the log.
 int ed3dgs_profile_report(char* buf, size_t nbytes) {

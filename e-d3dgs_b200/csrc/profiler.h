@@ -9,6 +9,8 @@ namespace ed3dgs {
 
 bool prof_enabled();
 void prof_push(const char* name, cudaEvent_t start, cudaEvent_t stop);
+// Device counters {pairs walked by render_fwd, pairs walked by blend_bwd} while profiling is on, else nullptr.
+unsigned long long* prof_pair_counters();
 
 struct ProfScope {
   cudaEvent_t start_ = nullptr, stop_ = nullptr;

@@ -391,7 +391,8 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
            float* __restrict__ out_mcoord, float* __restrict__ out_depth, float* __restrict__ out_mdepth,
            float* __restrict__ out_alpha, float* __restrict__ out_tongue, float* __restrict__ out_normal,
            uint32_t* __restrict__ n_contrib, float* __restrict__ accum_depth,
-           float* __restrict__ normal_length, float* __restrict__ accum_coord) {
+           float* __restrict__ normal_length, float* __restrict__ accum_coord,
+           unsigned long long* __restrict__ pair_counters) {
   constexpr bool NORMAL = COORD || DEPTH;
   constexpr bool GEO = NORMAL;
   constexpr int NQ = GEO ? 4 : 3;
@@ -477,7 +478,7 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
       cand &= cand - 1;
       const float4 q0 = SQ(buf, 0, j);
       const float4 q1 = SQ(buf, 1, j);
-      contributor = (uint32_t)(i * RENDER_BATCH + j + 1);
+      if (!done) contributor = (uint32_t)(i * RENDER_BATCH + j + 1);   // a finished pixel keeps the index it stopped at
       const float2 d = make_float2(q0.x - pixf.x, q0.y - pixf.y);
       const float power = -0.5f * (q1.x * d.x * d.x + q1.z * d.y * d.y) - q1.y * d.x * d.y;
       bool use = !done && !(power > 0.0f);
@@ -536,6 +537,16 @@ render_fwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_
   }
   cp_async_wait_all();
 
+  if (pair_counters) {   // profiling pass only (bench.py's FP32-ALU roofline): list entries this pixel walked
+    unsigned long long f = inside ? (unsigned long long)(done ? contributor : (uint32_t)total) : 0ull;
+    unsigned long long b = inside ? (unsigned long long)last_contributor : 0ull;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      f += __shfl_xor_sync(0xffffffffu, f, off);
+      b += __shfl_xor_sync(0xffffffffu, b, off);
+    }
+    if (lane == 0) { atomicAdd(pair_counters, f); atomicAdd(pair_counters + 1, b); }
+  }
   if (inside) {
     const size_t HW = (size_t)H * W;
     n_contrib[pix_id] = last_contributor;
@@ -588,7 +599,7 @@ static cudaError_t launch_render_fwd(dim3 grid, cudaStream_t stream, const Image
   render_fwd<COORD, DEPTH><<<grid, RENDER_THREADS, smem, stream>>>(
       img.ranges, point_list, W, H, geom.rec, geom.rec_coord, fx, fy, bg, out_color, out_coord, out_mcoord,
       out_depth, out_mdepth, out_alpha, out_tongue, out_normal, img.n_contrib, img.accum_depth,
-      img.normal_length, img.accum_coord);
+      img.normal_length, img.accum_coord, prof_pair_counters());
   return cudaGetLastError();
 }
 

@@ -20,7 +20,7 @@ CONFIGS = {
     "C2": dict(P=300_000, W=802, H=550, sh_degree=3, frames=150, focal_full=8200.0, full_w=3208),
     "C3": dict(P=1_000_000, W=1604, H=1100, sh_degree=3, frames=150, focal_full=8200.0, full_w=3208),
     "C4": dict(P=500_000, W=1352, H=1014, sh_degree=3, frames=300, focal_full=8200.0, full_w=2704),
-    "C5": dict(P=3_000_000, W=2048, H=1088, sh_degree=3, frames=50, focal_full=8200.0, full_w=4096),
+    "C5": dict(P=3_000_000, W=2048, H=1088, sh_degree=3, frames=50, focal_full=8200.0, full_w=4096, family="technicolor"),
 }
 
 

@@ -33,6 +33,16 @@ const char* ed3dgs_last_error(void);
 const char* ed3dgs_version(void);
 
 /*
+ * Measurement hooks (no counterpart in the reference; bench.py's roofline pass). While enabled every kernel group
+ * of the library is bracketed by CUDA events on its launching stream; _report synchronises the device, writes
+ * "name total_ms launches\n" lines into buf and clears the log; _pairs returns (and resets) the number of
+ * (pixel, Gaussian) list entries the forward blend walked (out[0]) and the backward blend walked (out[1]).
+ */
+void ed3dgs_profile_enable(int on);
+int ed3dgs_profile_report(char* buf, size_t nbytes);
+int ed3dgs_profile_pairs(unsigned long long* out);
+
+/*
  * Resize callback for the three opaque state buffers (geometry, binning, image).
  * Replaces std::function<char*(size_t)> of CudaRasterizer::Rasterizer::forward
  * (cuda_rasterizer/rasterizer.h:31-34) which the reference binds to torch resize_()
