@@ -467,7 +467,9 @@ def run_ours(args, rank, local, world):
     cfg = synthetic.CONFIGS[args.workload]
     scene, cams = build_scene(cfg, args.splat_scale, device)
     hyper = scene.hyper
-    arena = dp.GradArena(list(scene.parameters()))
+    # gradients: set to None before every step like the reference's zero_grad(set_to_none=True) (train.py:448); for N > 1
+    # all of them are reduced in one NCCL group (ed3dgs_b200/dp.py: GradSync)
+    arena = dp.GradSync(list(scene.parameters()))
     pipe = NS(debug=False)
     bg = torch.zeros(3, device=device)
     H, W = cfg["H"], cfg["W"]
@@ -512,6 +514,7 @@ def run_ours(args, rank, local, world):
         v = view_of(i)
         step(i, cams_dev[v], gts_dev[v % 4])
     barrier()
+    grad_bytes = arena.nbytes()
     vis = state["pkg"]["visibility_filter"].float().mean().item()
     from ed3dgs_b200.rasterizer import _RasterizeGaussians  # noqa: F401
     R = int(state["pkg"]["render"].grad_fn.num_rendered) if hasattr(state["pkg"]["render"].grad_fn, "num_rendered") else 0
@@ -790,7 +793,7 @@ def run_ours(args, rank, local, world):
         "config": dict(workload_config(args.workload, cfg, args.splat_scale, R, world, vis), **{
             "l2_policy": "per-step working set (Gaussian records 64 MB + keys/lists %.0f MB + MLP activations "
                          "%.1f GB) exceeds the 126 MB L2" % (R * 36 / 1e6, cfg["P"] * 7.0e3 / 1e9),
-            "grad_allreduce_bytes": arena.nbytes() if world > 1 else 0, "multi_gpu": multi, "host": host_info}),
+            "grad_allreduce_bytes": grad_bytes if world > 1 else 0, "multi_gpu": multi, "host": host_info}),
         "clocks": clocks,
         "e2e": {"value": world * 1e3 / ms_step_e2e, "unit": UNIT, "ms_per_step": ms_step_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,

@@ -131,22 +131,27 @@ class _DeformFunction(torch.autograd.Function):
 
         d_sub = [prep(gouts[h], h) for h in range(5)]
         d_out = [prep(gouts[5 + h], h) for h in range(5)]
-        # one zero fill for all parameter gradients of both stages (they are slices of one buffer)
-        pad = lambda n: (n + 63) // 64 * 64  # noqa: E731  (every slice starts on a 256-byte boundary)
-        flat = torch.zeros(sum(pad(p.numel()) for p in pc) + sum(pad(p.numel()) for p in pf), dtype=torch.float32,
-                           device=dev)
-        gc, gf, o = [], [], 0
-        for src, dst in ((pc, gc), (pf, gf)):
-            for p in src:
-                dst.append(flat[o:o + p.numel()].view(p.shape))
-                o += pad(p.numel())
+        # ONE zero fill for everything the kernels accumulate into: the parameter gradients of both stages, the two
+        # temporal-row gradients, the table gradient and d_t are slices of one buffer (every slice starts on a
+        # 256-byte boundary). With .grad unset (zero_grad(set_to_none=True), train.py:448) autograd adopts these
+        # slices as the parameters' .grad without a copy.
+        pad = lambda n: (n + 63) // 64 * 64  # noqa: E731
+        sizes = [p.numel() for p in pc] + [p.numel() for p in pf] + [temb, temb, table_c.numel(), 1]
+        flat = torch.zeros(sum(pad(n) for n in sizes), dtype=torch.float32, device=dev)
+        offs, o = [], 0
+        for n in sizes:
+            offs.append(o)
+            o += pad(n)
+        gc = [flat[offs[i]:offs[i] + p.numel()].view(p.shape) for i, p in enumerate(pc)]
+        gf = [flat[offs[len(pc) + i]:offs[len(pc) + i] + p.numel()].view(p.shape) for i, p in enumerate(pf)]
+        k = len(pc) + len(pf)
+        d_tau_c = flat[offs[k]:offs[k] + temb]
+        d_tau_f = flat[offs[k + 1]:offs[k + 1] + temb]
+        d_table = flat[offs[k + 2]:offs[k + 2] + table_c.numel()].view(table_c.shape)
+        d_t = flat[offs[k + 3]:offs[k + 3] + 1]
         # the first stage that runs overwrites d_emb (accumulate flag), so it needs no zero fill
         d_emb = (torch.empty if (N > 0 and (cfg["coarse"] or cfg["fine"])) else torch.zeros)(
             N, gemb, dtype=torch.float32, device=dev)
-        d_tau_c = torch.zeros(temb, dtype=torch.float32, device=dev)
-        d_tau_f = torch.zeros(temb, dtype=torch.float32, device=dev)
-        d_table = torch.zeros_like(table_c)
-        d_t = torch.zeros(1, dtype=torch.float32, device=dev)
         wc = _weights_struct(pc, depth, W, temb, gemb, cfg["enabled"]) if cfg["coarse"] else None
         wf = _weights_struct(pf, depth, W, temb, gemb, cfg["enabled"]) if cfg["fine"] else None
         sgc = _grads_struct(gc, depth, cfg["enabled"]) if cfg["coarse"] else None

@@ -136,8 +136,16 @@ def rasterize_forward_raw(bg, means3D, colors_precomp, opacities, tongue_class, 
     f32 = dict(dtype=torch.float32, device=dev)
     # One allocation for all image planes. The kernel writes every pixel of the planes it owns;
     # planes it does not own must read as zero (rasterize_points.cu:72-80).
-    full = bool(require_coord) and bool(require_depth) and P != 0
-    planes = torch.empty((16, H, W), **f32) if full else torch.zeros((16, H, W), **f32)
+    if P == 0:
+        planes = torch.zeros((16, H, W), **f32)
+    else:   # only the planes this kernel variant does not write are zero-filled
+        planes = torch.empty((16, H, W), **f32)
+        if not require_coord:
+            planes[3:9].zero_()
+        if not require_depth:
+            planes[12:14].zero_()
+        if not (require_coord or require_depth):
+            planes[9:12].zero_()
     out_color, out_coord, out_mcoord = planes[0:3], planes[3:6], planes[6:9]
     out_normal, out_depth, out_mdepth = planes[9:12], planes[12:13], planes[13:14]
     out_alpha, out_tongue = planes[14:15], planes[15:16]
@@ -318,6 +326,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = raster_settings
         ctx.scalars = args
         ctx.num_rendered = num_rendered
+        ctx.plane_shape = tuple(color.shape[1:])
+        # outputs the loss never touched arrive as None instead of image-sized zero tensors (grad_radii, grad_tongue
+        # and, for the variants that do not own them, the coord / depth planes are never read by the kernels)
+        ctx.set_materialize_grads(False)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, normal, radii, sh,
                               geomBuffer, binningBuffer, imgBuffer, alpha)
         return color, radii, coord, mcoord, depth, mdepth, alpha, tongue, normal
@@ -329,6 +341,22 @@ class _RasterizeGaussians(torch.autograd.Function):
         a = ctx.scalars
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, normal, radii, sh, geomBuffer,
          binningBuffer, imgBuffer, alpha) = ctx.saved_tensors
+        coord, depth = a[20], a[21]
+        H, W = ctx.plane_shape
+
+        def need(g, channels, used):
+            """A missing upstream gradient: zeros where the kernel variant reads the plane, NULL where it does not."""
+            if g is not None:
+                return g
+            if used:
+                return torch.zeros((channels, H, W), dtype=torch.float32, device=means3D.device)
+            return torch.empty(0, device=means3D.device)
+
+        grad_color = need(grad_color, 3, True)
+        grad_alpha = need(grad_alpha, 1, True)
+        grad_coord, grad_mcoord = need(grad_coord, 3, coord), need(grad_mcoord, 3, coord)
+        grad_depth, grad_mdepth = need(grad_depth, 1, depth), need(grad_mdepth, 1, depth)
+        grad_normal = need(grad_normal, 3, coord or depth)
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, a[7], cov3Ds_precomp, rs.viewmatrix,
                 rs.projmatrix, a[11], a[12], a[13], grad_color, grad_coord, grad_mcoord, grad_depth, grad_mdepth,
                 grad_alpha, grad_normal, normal, sh, a[17], rs.campos, geomBuffer, ctx.num_rendered,

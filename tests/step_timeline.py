@@ -11,7 +11,7 @@ from ed3dgs_b200.renderer import render, training_loss
 cfg = synthetic.CONFIGS["C3"]
 dev = torch.device("cuda:0")
 scene, cams = bench.build_scene(cfg, 0.3, dev)
-arena = dp.GradArena(list(scene.parameters()))
+arena = dp.GradSync(list(scene.parameters()))
 cam = bench.cam_to(cams[3], dev, False)
 gt = torch.rand(3, cfg["H"], cfg["W"], device=dev)
 bg = torch.zeros(3, device=dev)

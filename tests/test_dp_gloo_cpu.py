@@ -51,6 +51,44 @@ def test_grad_arena_allreduce_world2():
     assert dict(out) == {0: True, 1: True}
 
 
+def _worker_sync(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from ed3dgs_b200 import dp
+    dp.init_from_env("gloo")
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(4, 3)
+    emb = torch.nn.Parameter(torch.ones(5, 2))
+    sync = dp.GradSync(list(lin.parameters()) + [emb])
+    ok = True
+    for _step in range(2):   # the second step checks that zero() really starts from nothing
+        sync.zero()
+        assert lin.weight.grad is None and emb.grad is None
+        # the two Linear gradients arrive as slices of ONE buffer, like the deformation network's backward hands them over
+        flat = torch.zeros(64 + 3)
+        w = float(rank + 1)
+        flat[:12] = w
+        flat[64:67] = 2 * w
+        lin.weight.grad = flat[:12].view(3, 4)
+        lin.bias.grad = flat[64:67]
+        (emb * w).sum().backward()
+        ts = sync.tensors()
+        ok = ok and len(ts) == 2 and ts[0].numel() == 67 and sync.nbytes() == 4 * (67 + 10)
+        sync.allreduce(1.0 / world)
+        ok = ok and torch.allclose(lin.weight.grad, torch.full((3, 4), 1.5)) and torch.allclose(lin.bias.grad, torch.full((3,), 3.0))
+        ok = ok and torch.allclose(emb.grad, torch.full((5, 2), 1.5))
+    out[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_grad_sync_allreduce_world2():
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_sync, args=(2, port, out), nprocs=2, join=True)
+    assert dict(out) == {0: True, 1: True}
+
+
 def test_shard_views_ragged():
     from ed3dgs_b200 import dp
     assert [dp.shard_views(8, r, 8) for r in range(8)] == [[i] for i in range(8)]
