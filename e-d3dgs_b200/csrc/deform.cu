@@ -362,8 +362,12 @@ static int check_weights(const ed3dgs_deform_weights* w) {
     }                                                                                        \
   } while (0)
 
+// precision of the call in flight on this thread (ed3dgs_deform_weights::precision): 0 = 3xTF32, 1 = single tf32 pass
+static thread_local int g_single = 0;
+
 static TcArgs tc_args(long lda, long ldb, int M, int K, int NT, int epi) {
   TcArgs a{};
+  a.single = g_single;
   a.lda = lda; a.ldb = ldb; a.M = M; a.K = K; a.NT = NT; a.epilogue = epi;
   a.k_per_cta = K > 0 ? K : 1; a.ones_col = -1;
   return a;
@@ -427,7 +431,7 @@ static int stage_forward_fused(const ed3dgs_deform_weights* w, int s, int N, con
     fused_prepare<<<ns, 128, 0, stream>>>(pa);
   }
   fa.wimg = reinterpret_cast<const float4*>(wk.wimg[s]);
-  fa.na = na; fa.has_rgb = has_rgb ? 1 : 0; fa.N = N; fa.npad = wk.npad;
+  fa.na = na; fa.has_rgb = has_rgb ? 1 : 0; fa.N = N; fa.npad = wk.npad; fa.single = g_single;
   fa.c1 = wk.c1[s];
   for (int i = 0; i < na; ++i) {
     const int h = act[i];
@@ -535,6 +539,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     // activations of two heads side by side on the N side; only the (head rows x head columns) blocks
     // of the product are kept.
     WgArgs a{};
+    a.single = g_single;
     a.N = N;
     for (int i0 = 0; i0 < na; i0 += 2) {
       WgGroup& gr = a.g[a.ngroups];
@@ -563,6 +568,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   }
   if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i]: trunk activations on the M side, two heads' dZ on the N side
     WgArgs a{};
+    a.single = g_single;
     a.N = N;
     for (int i0 = 0; i0 < na; i0 += 2) {
       WgGroup& gr = a.g[a.ngroups];
@@ -597,6 +603,8 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   for (int l = D - 1; l >= 1; --l) {
     if (g && g->feat_w[l]) {  // dW_l[o][i] += sum_n dh[n][o] * R_{l-1}[n][i]
       WgArgs a{};
+      a.single = g_single;
+    a.single = g_single;
       a.N = N; a.ngroups = 1;
       a.g[0].P = wk.R[s][l - 1]; a.g[0].ldp = W; a.g[0].pcols = W;
       a.g[0].Q = dh; a.g[0].ldq = W; a.g[0].qcols = W;
@@ -613,6 +621,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   // layer 0: weight gradient of the embedding columns, then dE (dc1 came from the MASK epilogue above)
   if (g && g->feat_w[0]) {  // dW0[o][temb + i] += sum_n dh[n][o] * emb[n][i]
     WgArgs a{};
+    a.single = g_single;
     a.N = N; a.ngroups = 1;
     a.g[0].P = emb; a.g[0].ldp = gemb; a.g[0].pcols = gemb;
     a.g[0].Q = dh; a.g[0].ldq = W; a.g[0].qcols = W;
@@ -691,7 +700,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
   ba.nseq = nseq;
   ba.wimg = reinterpret_cast<const float4*>(wk.wimg_b);
   ba.na = na; ba.has_rgb = has_rgb ? 1 : 0; ba.N = N;
-  ba.use_sub = use_sub; ba.accumulate_emb = accumulate_emb; ba.store_dz = 1;
+  ba.use_sub = use_sub; ba.accumulate_emb = accumulate_emb; ba.store_dz = 1; ba.single = g_single;
 #ifdef ED3DGS_TRACE
   { static long long* tr = nullptr; if (!tr) { cudaMalloc(&tr, 8 * 8000 * 5); } cudaMemsetAsync(tr, 0, 8 * 8000 * 5, stream); ba.trace = tr; g_trace = tr; }
 #endif
@@ -720,6 +729,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
     // every weight gradient of the stage in one launch; the groups of a slice of Gaussians are adjacent work items, so
     // hT / dzT / zT / GT are shared through L2
     WgArgs a{};
+    a.single = g_single;
     a.N = N;
     for (int i0 = 0; i0 < na; i0 += 2) {   // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n], two heads side by side (N = 256)
       WgGroup& gr = a.g[a.ngroups];
@@ -807,6 +817,7 @@ int ed3dgs_deform_forward(const ed3dgs_deform_weights* coarse, const ed3dgs_defo
   if ((rc = check_weights(coarse)) || (rc = check_weights(fine))) return rc;
   const ed3dgs_deform_weights* any = coarse ? coarse : fine;
   static const int hd[5] = {3, 3, 4, 1, 48};
+  g_single = (any && any->precision == 1) ? 1 : 0;
   if (!any) {
     for (int h = 0; h < 5; ++h) {
       cudaMemcpyAsync(sub[h], in[h], (size_t)N * hd[h] * 4, cudaMemcpyDeviceToDevice, stream);
@@ -851,6 +862,7 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
   if (N <= 0 || !any) return ED3DGS_OK;
   int rc;
   if ((rc = check_weights(coarse)) || (rc = check_weights(fine))) return rc;
+  g_single = any->precision == 1 ? 1 : 0;
   if (!workspace || workspace_bytes < ed3dgs_deform_workspace_bytes(any->W, any->depth, N)) {
     set_error("deform_backward: workspace too small");
     return ED3DGS_ERR_ARG;
@@ -933,7 +945,7 @@ int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, c
   if (amaj == TC_MN_MAJOR) {
     // weight-gradient form: A stored [K][lda] (P side, M columns), B stored [K][ldb] (Q side, n_valid columns)
     WgArgs wa{};
-    wa.N = K; wa.ngroups = 1;
+    wa.N = K; wa.ngroups = 1; wa.single = (dbg & 2) ? 1 : 0;
     wa.g[0].P = A; wa.g[0].ldp = lda; wa.g[0].pcols = (M + 3) / 4 * 4;
     wa.g[0].Q = B; wa.g[0].ldq = ldb; wa.g[0].qcols = (n_valid + 3) / 4 * 4;
     wa.g[0].nseg = 1;
@@ -946,7 +958,7 @@ int ed3dgs_test_tc_gemm(int amaj, int bmaj, int M, int n_valid, int NT, int K, c
   a.b[0] = TcBatch{A, B, C, nullptr, nullptr, bias_grad, ldc, 0, n_valid, 0, 0, 1.f};
   a.lda = lda; a.ldb = ldb;
   a.M = M; a.K = K; a.NT = NT; a.k_per_cta = k_per_cta > 0 ? k_per_cta : K;
-  a.epilogue = epilogue; a.relu = 0; a.accumulate = 0; a.ones_col = ones_col; a.dbg = dbg;
+  a.epilogue = epilogue; a.relu = 0; a.accumulate = 0; a.ones_col = ones_col; a.dbg = dbg; a.single = (dbg & 2) ? 1 : 0;
   static float* scratch_of[64] = {};   // test entry: one scratch per device, never freed
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("tc_gemm: no current device"); return ED3DGS_ERR_CUDA; }

@@ -126,6 +126,7 @@ struct FusedFwdArgs {
   uint32_t slab_off[2 + 8 * 6];  //               rgb output layer (NT = 48); float4 offsets
   int na, has_rgb;               // active heads in slot order; the rgb head, when active, is the last slot
   int N;
+  int single;                    // precision "tf32": one tf32 MMA per product instead of the 3xTF32 triple
   long npad;                     // N rounded up to whole tiles
   const float* c1;               // [128] layer-0 bias with the temporal half of the input folded in
   const float* b1[5];            // per slot
@@ -226,8 +227,10 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
       mbar_wait(&bars.e_tma[eb], ph);
       const float4* hi = reinterpret_cast<const float4*>(sEh + (size_t)eb * FM_E_BYTES);
       float4* lo = reinterpret_cast<float4*>(sEl + (size_t)eb * FM_E_BYTES);
+      if (!p.single) {
 #pragma unroll 8
-      for (int i = 0; i < FM_E_BYTES / 16 / 32; ++i) lo[lane + 32 * i] = split_lo(hi[lane + 32 * i]);
+        for (int i = 0; i < FM_E_BYTES / 16 / 32; ++i) lo[lane + 32 * i] = split_lo(hi[lane + 32 * i]);
+      }
       fence_async_smem();
       mbar_arrive(&bars.e_full[eb]);
     }
@@ -265,6 +268,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
     constexpr uint32_t E_SLAB = FM_E_SLAB_BYTES >> 4, E_KS = 32u >> 4;
     RingPos<FMF_W_SLOTS> wr;
     int go = 0;
+    const bool single = p.single != 0;
 
     auto layer0 = [&](int tl) {      // SS: ACC[g][f] = sum_k E[g][k] W0e[f][k], K = 32
       const int eb = tl & 1, buf = go & 1;
@@ -279,10 +283,12 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
           const uint32_t eh = eh_lo0 + (uint32_t)(eb * 2 + s) * E_SLAB, el = el_lo0 + (uint32_t)(eb * 2 + s) * E_SLAB;
 #pragma unroll
           for (uint32_t ks = 0; ks < 2; ++ks) {
-            umma_tf32(acc, desc64(e_desc_hi, el + ks * E_KS), desc64(w_desc_hi, wh + ks * W128_KS), idesc128,
-                      (s | ks) ? 1u : 0u);
-            umma_tf32(acc, desc64(e_desc_hi, eh + ks * E_KS), desc64(w_desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
-            umma_tf32(acc, desc64(e_desc_hi, eh + ks * E_KS), desc64(w_desc_hi, wh + ks * W128_KS), idesc128, 1u);
+            const uint32_t first = (s | ks) ? 1u : 0u;
+            if (!single) {
+              umma_tf32(acc, desc64(e_desc_hi, el + ks * E_KS), desc64(w_desc_hi, wh + ks * W128_KS), idesc128, first);
+              umma_tf32(acc, desc64(e_desc_hi, eh + ks * E_KS), desc64(w_desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
+            }
+            umma_tf32(acc, desc64(e_desc_hi, eh + ks * E_KS), desc64(w_desc_hi, wh + ks * W128_KS), idesc128, single ? first : 1u);
           }
           umma_commit(&bars.w_free[wr.idx]);
           if (s == 1) { umma_commit(&bars.e_free[eb]); umma_commit(&bars.acc_full[buf]); }
@@ -312,9 +318,12 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
 #pragma unroll
             for (uint32_t ks = 0; ks < 2; ++ks) {
               const uint32_t col = (uint32_t)s * 16u + ks * 8u;
-              umma_tf32_ts(acc, tmem + FM_H_LO + col, desc64(w_desc_hi, wh + ks * W128_KS), idesc128, (s | (int)ks) ? 1u : 0u);
-              umma_tf32_ts(acc, tmem + FM_H_HI + col, desc64(w_desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
-              umma_tf32_ts(acc, tmem + FM_H_HI + col, desc64(w_desc_hi, wh + ks * W128_KS), idesc128, 1u);
+              const uint32_t first = (s | (int)ks) ? 1u : 0u;
+              if (!single) {
+                umma_tf32_ts(acc, tmem + FM_H_LO + col, desc64(w_desc_hi, wh + ks * W128_KS), idesc128, first);
+                umma_tf32_ts(acc, tmem + FM_H_HI + col, desc64(w_desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
+              }
+              umma_tf32_ts(acc, tmem + FM_H_HI + col, desc64(w_desc_hi, wh + ks * W128_KS), idesc128, single ? first : 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
             if (s == 7) umma_commit(&bars.acc_full[buf]);
@@ -337,9 +346,12 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
 #pragma unroll
             for (uint32_t ks = 0; ks < 2; ++ks) {
               const uint32_t col = (uint32_t)s * 16u + ks * 8u;
-              umma_tf32_ts(out, a_lo + col, desc64(w_desc_hi, wh + ks * W48_KS), idesc48, (s | (int)ks) ? 1u : 0u);
-              umma_tf32_ts(out, a_hi + col, desc64(w_desc_hi, wh + W48_LO + ks * W48_KS), idesc48, 1u);
-              umma_tf32_ts(out, a_hi + col, desc64(w_desc_hi, wh + ks * W48_KS), idesc48, 1u);
+              const uint32_t first = (s | (int)ks) ? 1u : 0u;
+              if (!single) {
+                umma_tf32_ts(out, a_lo + col, desc64(w_desc_hi, wh + ks * W48_KS), idesc48, first);
+                umma_tf32_ts(out, a_hi + col, desc64(w_desc_hi, wh + W48_LO + ks * W48_KS), idesc48, 1u);
+              }
+              umma_tf32_ts(out, a_hi + col, desc64(w_desc_hi, wh + ks * W48_KS), idesc48, single ? first : 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
             if (s == 7) umma_commit(&bars.out_full);
@@ -392,7 +404,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
           }
         }
         tmem_st32(lane_base + FM_H_HI + (uint32_t)col, v);
-        tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);
+        if (!p.single) tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&bars.h_ready);
@@ -428,7 +440,7 @@ __global__ void __launch_bounds__(FM_THREADS, 1) fused_fwd_kernel(const __grid_c
         }
         if (is_rgb) {
           tmem_st32(lane_base + FM_ACC0 + (uint32_t)(buf * 128 + col), v);   // Z4_hi in place
-          tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);             // the trunk operand is dead by now
+          if (!p.single) tmem_st_lo32(lane_base + FM_H_LO + (uint32_t)col, v);   // the trunk operand is dead by now
           tmem_st_wait();
           tc_fence_before();
           mbar_arrive(&bars.z4_ready);
@@ -554,6 +566,7 @@ struct FusedBwdArgs {
   int nseq;
   int na, has_rgb, N;
   int use_sub, accumulate_emb, store_dz;
+  int single;                // precision "tf32": one tf32 MMA per product
   long long* trace;          // ED3DGS_TRACE builds: (event, clock) pairs of block 0
   const float* w2[5];        // by slot, [k][128]
   int hdim[5];
@@ -673,6 +686,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
     constexpr uint32_t G_PIECE = (128u * 16u) >> 4;
     RingPos<FM_W_SLOTS> wr;
     int u = 0;
+    const bool single = p.single != 0;
     int tcount = 0; const int tbase = 0; (void)tcount; (void)tbase;
     for (int tl = 0; tl < my_tiles; ++tl) {
       FM_TRACE(100 + tl);
@@ -692,15 +706,20 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
 #pragma unroll
               for (uint32_t ks = 0; ks < 2; ++ks) {
                 const uint32_t go = ((uint32_t)s * 4u + ks * 2u) * G_PIECE;
-                umma_tf32(acc, desc64(desc_hi, gl_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, (s | (int)ks) ? 1u : 0u);
-                umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + W64_LO + ks * W64_KS), idesc64, 1u);
-                umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, 1u);
+                const uint32_t first = (s | (int)ks) ? 1u : 0u;
+                if (!single) {
+                  umma_tf32(acc, desc64(desc_hi, gl_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, first);
+                  umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + W64_LO + ks * W64_KS), idesc64, 1u);
+                }
+                umma_tf32(acc, desc64(desc_hi, gh_lo0 + go), desc64(desc_hi, wh + ks * W64_KS), idesc64, single ? first : 1u);
               }
             } else {
               const uint32_t go = (uint32_t)(2 * hs) * G_PIECE;
-              umma_tf32(acc, desc64(desc_hi, sl_lo0 + go), desc64(desc_hi, wh), idesc64, 0u);
-              umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh + W64_LO), idesc64, 1u);
-              umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh), idesc64, 1u);
+              if (!single) {
+                umma_tf32(acc, desc64(desc_hi, sl_lo0 + go), desc64(desc_hi, wh), idesc64, 0u);
+                umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh + W64_LO), idesc64, 1u);
+              }
+              umma_tf32(acc, desc64(desc_hi, sh_lo0 + go), desc64(desc_hi, wh), idesc64, single ? 0u : 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
             if (s == nsl - 1) umma_commit(&bars.dzacc_full[hf]);
@@ -728,9 +747,12 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
 #pragma unroll
             for (uint32_t ks = 0; ks < 2; ++ks) {
               const uint32_t col = (uint32_t)s * 16u + ks * 8u;
-              umma_tf32_ts(tmem + FB_DH, a_lo + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, (uu | s | (int)ks) ? 1u : 0u);
-              umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
-              umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, 1u);
+              const uint32_t first = (uu | s | (int)ks) ? 1u : 0u;
+              if (!single) {
+                umma_tf32_ts(tmem + FB_DH, a_lo + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, first);
+                umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + W128_LO + ks * W128_KS), idesc128, 1u);
+              }
+              umma_tf32_ts(tmem + FB_DH, a_hi + col, desc64(desc_hi, wh + ks * W128_KS), idesc128, single ? first : 1u);
             }
             umma_commit(&bars.w_free[wr.idx]);
             if (s == 3 && uu == nunits - 1) umma_commit(&bars.dh_full);
@@ -751,9 +773,12 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
 #pragma unroll
           for (uint32_t ks = 0; ks < 2; ++ks) {
             const uint32_t col = (uint32_t)s * 16u + ks * 8u;
-            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH_LO + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, (s | (int)ks) ? 1u : 0u);
-            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + W32_LO + ks * W32_KS), idesc32, 1u);
-            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, 1u);
+            const uint32_t first = (s | (int)ks) ? 1u : 0u;
+            if (!single) {
+              umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH_LO + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, first);
+              umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + W32_LO + ks * W32_KS), idesc32, 1u);
+            }
+            umma_tf32_ts(tmem + FB_DZ, tmem + FB_DH + col, desc64(desc_hi, wh + ks * W32_KS), idesc32, single ? first : 1u);
           }
           umma_commit(&bars.w_free[wr.idx]);
           if (s == 7) umma_commit(&bars.de_full);
@@ -893,7 +918,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
         tmem_st32(dz_hi, v);
-        tmem_st_lo32(dz_lo, v);
+        if (!p.single) tmem_st_lo32(dz_lo, v);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&bars.dz_ready[hf]);
@@ -917,7 +942,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fused_bwd_kernel(const __grid_c
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = ((hword >> j) & 1u) ? v[j] : 0.f;
         tmem_st32(lane_base + FB_DH + (uint32_t)col, v);
-        tmem_st_lo32(lane_base + FB_DH_LO + (uint32_t)col, v);
+        if (!p.single) tmem_st_lo32(lane_base + FB_DH_LO + (uint32_t)col, v);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&bars.dh_ready);

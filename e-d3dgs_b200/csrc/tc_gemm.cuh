@@ -79,7 +79,8 @@ struct TcArgs {
   int relu;       // BIAS_ACT
   int accumulate; // ACCUM
   int ones_col;   // unused (test hook compatibility)
-  int dbg;        // test hook: 2 = single pass (hi*hi only)
+  int single;     // precision "tf32": one tf32 MMA per product (hi*hi only) instead of the 3xTF32 triple
+  int dbg;        // timing knobs of builds with -DED3DGS_TIMING_KNOBS (16: skip the epilogue, 64: wrap addresses); else unused
   // rows kernel programme (K-major A only)
   int nsteps, ntiles;
   uint32_t steps[TC_MAX_STEPS];   // batch | slab << 8 | npieces << 16 | nk << 20 | flags << 24

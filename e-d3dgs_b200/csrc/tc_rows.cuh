@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
     const uint32_t xl_lo0 = ((smem_u32(sXl) & 0x3FFFFu) >> 4) | (1u << 16);
     constexpr uint32_t W_SLOT = ROWS_W_SLOT_BYTES >> 4, W_LO = W_SLOT / 2, W_KS = (2u * 128u * 16u) >> 4;
     constexpr uint32_t X_SLAB = ROWS_X_SLAB_BYTES >> 4, X_KS = 32u >> 4;
-    const bool single = (p.dbg & 2) != 0;
+    const bool single = p.single != 0;
     int s = 0, go = 0;
     uint32_t acc = tmem;
     RingPos<ROWS_XH_SLOTS> hr;
@@ -359,7 +359,9 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
         auto mask_word = [&](int blk) -> uint32_t {
           long g0 = tile * ROWS_TG + blk * 32;
           if (!use_mask || g0 >= (long)p.M) return 0u;
+#ifdef ED3DGS_TIMING_KNOBS
           if (p.dbg & 64) g0 &= 16383;
+#endif
           return __ldg(bt.mask_in + (g0 >> 5) * bt.mask_ld + bt.mask_col + f);
         };
         // the mask kind has registers to spare: all four words of this warp's blocks before the wait
@@ -379,10 +381,16 @@ __global__ void __launch_bounds__(ROWS_THREADS, 1) tc_rows_kernel(const __grid_c
             long g0 = tile * ROWS_TG + blk * 32;
             const int jmax = (int)min(32L, (long)p.M - g0);
             if (jmax <= 0) break;
+#ifdef ED3DGS_TIMING_KNOBS
             if (p.dbg & 64) g0 &= 16383;   // timing knob: outputs stay in an L2-resident window
+#endif
             float v[32];
             tmem_ld32(lane_base + (uint32_t)(buf * ROWS_TG + blk * 32), v);
+#ifdef ED3DGS_TIMING_KNOBS
             if (f < bt.n_valid && !(p.dbg & 16)) {
+#else
+            if (f < bt.n_valid) {
+#endif
               if (ld_case == 640) colsum += rows_epilogue_dispatch<640, EPI>(p, bt, v, f, g0, jmax, mword);
               else if (ld_case == 128) colsum += rows_epilogue_dispatch<128, EPI>(p, bt, v, f, g0, jmax, mword);
               else colsum += rows_epilogue_dispatch<0, EPI>(p, bt, v, f, g0, jmax, mword);

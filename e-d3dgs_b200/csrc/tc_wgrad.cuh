@@ -70,6 +70,7 @@ struct WgArgs {
   int ngroups;
   int N;            // Gaussians
   int slice;        // Gaussians per work item (multiple of 128)
+  int single;       // precision "tf32": one tf32 MMA per product (the lo ring is not filled)
   // tensor maps of P and Q of every group: dims {cols, N}, box {32, 16}, SWIZZLE_128B_ATOM_32B (tc_wgrad_launch)
   alignas(64) CUtensorMap pmap[WG_MAX_GROUPS];
   alignas(64) CUtensorMap qmap[WG_MAX_GROUPS];
@@ -145,17 +146,21 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
         mbar_wait(&bars.hi_full[hr.idx], hr.phase);       // TMA bytes of this slab have landed
         const float4* src = reinterpret_cast<const float4*>(sHi + (size_t)hr.idx * WG_SLAB_BYTES);
         float4 r[NIT];
+        if (!p.single) {
 #pragma unroll
-        for (int i = 0; i < NIT; ++i) {
-          const int q = ct + i * WG_CONV_THREADS;
-          if (q < nchunks) r[i] = src[q];
+          for (int i = 0; i < NIT; ++i) {
+            const int q = ct + i * WG_CONV_THREADS;
+            if (q < nchunks) r[i] = src[q];
+          }
         }
         mbar_wait(&bars.lo_free[lr.idx], lr.phase ^ 1u);  // the UMMAs that read this lo slot are done
         float4* lo = reinterpret_cast<float4*>(sLo + (size_t)lr.idx * WG_SLAB_BYTES);
+        if (!p.single) {
 #pragma unroll
-        for (int i = 0; i < NIT; ++i) {
-          const int q = ct + i * WG_CONV_THREADS;
-          if (q < nchunks) lo[q] = split_lo(r[i]);
+          for (int i = 0; i < NIT; ++i) {
+            const int q = ct + i * WG_CONV_THREADS;
+            if (q < nchunks) lo[q] = split_lo(r[i]);
+          }
         }
         fence_async_smem();
         mbar_arrive(&bars.x_full[lr.idx]);
@@ -229,12 +234,17 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tc_wgrad_kernel(const __grid_co
           const uint32_t ph = hi0 + (uint32_t)hr.idx * SLAB + p_fix, pl = lo0 + (uint32_t)lr.idx * SLAB + p_fix;
           const uint32_t qh = hi0 + (uint32_t)hr.idx * SLAB + QOFF + q_fix, ql = lo0 + (uint32_t)lr.idx * SLAB + QOFF + q_fix;
           const uint32_t first = s == 0 ? 0u : 1u;
-          umma_tf32(acc, desc64(p_hi, pl), desc64(q_hi, qh), idesc, first);  // small terms first
-          umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, ql), idesc, 1u);
-          umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, qh), idesc, 1u);
-          umma_tf32(acc, desc64(p_hi, pl + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
-          umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, ql + q_ks), idesc, 1u);
-          umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
+          if (!p.single) {
+            umma_tf32(acc, desc64(p_hi, pl), desc64(q_hi, qh), idesc, first);  // small terms first
+            umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, ql), idesc, 1u);
+            umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, qh), idesc, 1u);
+            umma_tf32(acc, desc64(p_hi, pl + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
+            umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, ql + q_ks), idesc, 1u);
+            umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
+          } else {
+            umma_tf32(acc, desc64(p_hi, ph), desc64(q_hi, qh), idesc, first);
+            umma_tf32(acc, desc64(p_hi, ph + p_ks), desc64(q_hi, qh + q_ks), idesc, 1u);
+          }
           umma_commit(&bars.lo_free[lr.idx]);
           umma_commit(&bars.hi_free[hr.idx]);
           if (s == nslab - 1) umma_commit(&bars.acc_full[buf]);

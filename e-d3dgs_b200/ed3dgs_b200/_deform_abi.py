@@ -14,7 +14,8 @@ FloatArr5 = c_float * HEADS
 class DeformWeights(ctypes.Structure):
     _fields_ = [("W", c_int), ("depth", c_int), ("temb_dim", c_int), ("gemb_dim", c_int),
                 ("feat_w", PtrArr8), ("feat_b", PtrArr8),
-                ("head_w1", PtrArr5), ("head_b1", PtrArr5), ("head_w2", PtrArr5), ("head_b2", PtrArr5)]
+                ("head_w1", PtrArr5), ("head_b1", PtrArr5), ("head_w2", PtrArr5), ("head_b2", PtrArr5),
+                ("precision", c_int)]
 
 
 class DeformGrads(ctypes.Structure):

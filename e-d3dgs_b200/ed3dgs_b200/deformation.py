@@ -15,6 +15,8 @@ from . import _deform_abi as abi
 from . import _lib
 
 _HEAD_NAMES = ("pos", "scales", "rotations", "opacity", "rgb")
+# deform_network.precision -> ed3dgs_deform_weights::precision (include/ed3dgs_deform.h)
+_PRECISIONS = {"fp32": 0, "3xtf32": 0, "tf32": 1}
 
 
 def _stage_tensors(feature_out, heads):
@@ -28,9 +30,10 @@ def _stage_tensors(feature_out, heads):
     return tensors, len(feat)
 
 
-def _weights_struct(tensors, depth, W, temb, gemb, enabled):
+def _weights_struct(tensors, depth, W, temb, gemb, enabled, precision=0):
     s = abi.DeformWeights()
     s.W, s.depth, s.temb_dim, s.gemb_dim = W, depth, temb, gemb
+    s.precision = precision
     for l in range(depth):
         s.feat_w[l] = tensors[2 * l].data_ptr()
         s.feat_b[l] = tensors[2 * l + 1].data_ptr()
@@ -86,8 +89,8 @@ class _DeformFunction(torch.autograd.Function):
         t_c = t.detach().reshape(1).float().contiguous()
         emb_c = emb.detach().contiguous().float()
         ins = [x.detach().contiguous().float() for x in (pts, scales, rots, opac, sh.reshape(N, 48))]
-        wc = _weights_struct(pc, depth, W, temb, gemb, cfg["enabled"]) if cfg["coarse"] else None
-        wf = _weights_struct(pf, depth, W, temb, gemb, cfg["enabled"]) if cfg["fine"] else None
+        wc = _weights_struct(pc, depth, W, temb, gemb, cfg["enabled"], cfg["precision"]) if cfg["coarse"] else None
+        wf = _weights_struct(pf, depth, W, temb, gemb, cfg["enabled"], cfg["precision"]) if cfg["fine"] else None
         with torch.cuda.device(dev):
             tau_c = temporal_embed(table_c, cfg["rows_c"], t_c) if cfg["coarse"] else torch.zeros(temb, device=dev)
             tau_f = temporal_embed(table_c, cfg["rows_f"], t_c) if cfg["fine"] else torch.zeros(temb, device=dev)
@@ -152,8 +155,8 @@ class _DeformFunction(torch.autograd.Function):
         # the first stage that runs overwrites d_emb (accumulate flag), so it needs no zero fill
         d_emb = (torch.empty if (N > 0 and (cfg["coarse"] or cfg["fine"])) else torch.zeros)(
             N, gemb, dtype=torch.float32, device=dev)
-        wc = _weights_struct(pc, depth, W, temb, gemb, cfg["enabled"]) if cfg["coarse"] else None
-        wf = _weights_struct(pf, depth, W, temb, gemb, cfg["enabled"]) if cfg["fine"] else None
+        wc = _weights_struct(pc, depth, W, temb, gemb, cfg["enabled"], cfg["precision"]) if cfg["coarse"] else None
+        wf = _weights_struct(pf, depth, W, temb, gemb, cfg["enabled"], cfg["precision"]) if cfg["fine"] else None
         sgc = _grads_struct(gc, depth, cfg["enabled"]) if cfg["coarse"] else None
         sgf = _grads_struct(gf, depth, cfg["enabled"]) if cfg["fine"] else None
         ptr = lambda x: x.data_ptr() if x is not None else None  # noqa: E731
@@ -198,6 +201,9 @@ class deform_network(nn.Module):
         self.temporal_embedding_dim = args.temporal_embedding_dim
         self.gaussian_embedding_dim = args.gaussian_embedding_dim
         self.c2f_temporal_iter = args.c2f_temporal_iter
+        # "fp32" (default): 3xTF32 tensor-core GEMMs, fp32-grade parity with the reference's cuBLAS SGEMM path;
+        # "tf32": one tf32 MMA per product (torch's allow_tf32 arithmetic), documented looser tolerance
+        self.precision = getattr(args, "mlp_precision", "fp32")
 
         (self.feature_out_c, self.pos_deform_c, self.scales_deform_c, self.rotations_deform_c,
          self.opacity_deform_c, self.rgb_deform_c) = self.create_net()
@@ -277,7 +283,7 @@ class deform_network(nn.Module):
                    rows_c=self._rows(iter, num_down_emb_c, a.use_coarse_temporal_embedding),
                    rows_f=self._rows(iter, num_down_emb_f, False),
                    coef=(float(coef), float(coef * coef_s), float(coef), float(coef * coef_o), float(coef_c)),
-                   t_shape=tuple(t.shape))
+                   t_shape=tuple(t.shape), precision=_PRECISIONS[self.precision])
         res = _DeformFunction.apply(cfg, t, self.weight, emb, pts, scales, rotations, opacity, sh_in, *params_c,
                                     *params_f)
         sub, out = list(res[:5]), list(res[5:])

@@ -35,6 +35,11 @@ typedef struct {
   const float* head_b1[ED3DGS_DEFORM_HEADS];
   const float* head_w2[ED3DGS_DEFORM_HEADS];
   const float* head_b2[ED3DGS_DEFORM_HEADS];
+  /* Arithmetic of the tensor-core GEMMs. 0 (default): 3xTF32, every product as hi*hi + hi*lo + lo*hi of the
+     operands' tf32 halves -- fp32-grade, the mode all parity bounds are stated for (outputs <= 2e-5, gradients
+     <= 1e-4 relative). 1 ("tf32"): one tf32 MMA per product, what torch runs with allow_tf32 = True --
+     outputs <= 2e-3, gradients <= 1e-2 relative (tests/test_deform_gpu.py), a third of the tensor work. */
+  int precision;
 } ed3dgs_deform_weights;
 
 /* Same shapes as the weights; every non-NULL gradient is ACCUMULATED into (+=). */

@@ -1,5 +1,5 @@
 """Times the deformation network (forward, backward) at N Gaussians with CUDA events and prints the library's own
-per-kernel event report (csrc/profiler.h). usage: python tests/time_deform.py [N] [iters]"""
+per-kernel event report (csrc/profiler.h). usage: python tests/time_deform.py [N] [iters] [fp32|tf32]"""
 import ctypes
 import sys
 
@@ -28,6 +28,8 @@ def main():
     iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
     g = synthetic.make_gaussians(N, device="cuda")
     scene = GaussianScene(g, default_hyper()).cuda()
+    if len(sys.argv) > 3:
+        scene._deformation.precision = sys.argv[3]
     feats = scene.get_features.detach().clone().requires_grad_(True)
 
     def fwd():
