@@ -322,7 +322,7 @@ def mlp_hbm_model(hyper, P):
 
 
 SORT_DIGIT_BITS = 8
-SORT_LAUNCHES_PER_PASS, SORT_LAUNCHES_FIXED = 5, 0   # csrc/radix_sort.cu: hist, scan x3, scatter per pass
+SORT_LAUNCHES_PER_PASS, SORT_LAUNCHES_FIXED = 1, 2   # csrc/radix_sort.cu: one-sweep kernel per pass + histogram + digit scan
 
 
 def launches_per_step(prof, steps, sort_passes):

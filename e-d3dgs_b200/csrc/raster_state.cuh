@@ -51,7 +51,7 @@ struct ImageState {
 struct BinningState {
   uint64_t* keys[3];       // [0],[1] = sort ping-pong; [2] = unsorted emission order (kept intact)
   uint32_t* vals[3];
-  uint32_t* hist;          // [256][nblocks] radix digit histograms / offsets, then scan chunk sums
+  uint32_t* hist;          // radix sort scratch: digit offsets of every pass, tile tickets, look-back status words
 };
 
 constexpr int SCAN_TILE = 2048;
@@ -99,6 +99,11 @@ inline size_t image_bytes(size_t npix, size_t ntiles, bool coord) {
 }
 
 inline size_t sort_blocks(size_t R) { return (R + SORT_TILE - 1) / SORT_TILE; }
+constexpr int SORT_MAX_PASSES = 8;   // 64 key bits, 8 per pass
+// words of radix sort scratch used by `npasses` passes over R keys (radix_sort.cu: digit_base | ticket | status)
+inline size_t sort_aux_words(size_t R, int npasses) {
+  return (size_t)SORT_MAX_PASSES * 256 + 256 + (size_t)npasses * sort_blocks(R) * 256;
+}
 
 inline BinningState carve_binning(char*& p, size_t R) {
   BinningState b{};
@@ -108,7 +113,7 @@ inline BinningState carve_binning(char*& p, size_t R) {
   carve(p, b.vals[1], R);
   carve(p, b.keys[2], R);
   carve(p, b.vals[2], R);
-  carve(p, b.hist, 256 * sort_blocks(R) + (256 * sort_blocks(R) + 2047) / 2048 + 2);  // table + scan chunk sums
+  carve(p, b.hist, sort_aux_words(R, SORT_MAX_PASSES));
   return b;
 }
 // Which ping-pong half holds the sorted list after sorting key bits [0, end_bit).
