@@ -469,7 +469,15 @@ def run_ours(args, rank, local, world):
     hyper = scene.hyper
     # gradients: set to None before every step like the reference's zero_grad(set_to_none=True) (train.py:448); for N > 1
     # all of them are reduced in one NCCL group (ed3dgs_b200/dp.py: GradSync)
-    arena = dp.GradSync(list(scene.parameters()))
+    # N > 1: the 59 of 91 per-Gaussian gradient floats that are final before the network's backward starts are reduced
+    # next to it (dp.OverlapSync; BENCH_OVERLAP=0 switches back to one exchange at the end of the step)
+    overlap = world > 1 and os.environ.get("BENCH_OVERLAP", "1") != "0"
+    sm_reserve = int(os.environ.get("BENCH_SM_RESERVE", "8"))
+    arena = dp.OverlapSync(list(scene.parameters()),
+                           early=[scene._xyz, scene._features_dc, scene._features_rest, scene._scaling, scene._rotation,
+                                  scene._opacity], sm_reserve=sm_reserve)
+    if overlap:
+        overlap = arena.enable()
     pipe = NS(debug=False)
     bg = torch.zeros(3, device=device)
     H, W = cfg["H"], cfg["W"]
@@ -628,7 +636,7 @@ def run_ours(args, rank, local, world):
         barrier()
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         keep = arena.allreduce
-        arena.allreduce = lambda *_a, **_k: None
+        arena.allreduce = lambda *_a, **_k: keep(collective=False)
         c0.record()
         for i in range(10):
             v = view_of(i)
@@ -641,7 +649,14 @@ def run_ours(args, rank, local, world):
         dist.all_reduce(mt_max, op=dist.ReduceOp.MAX)
         dist.all_reduce(mt, op=dist.ReduceOp.MIN)
         multi = {"allreduce_ms": float(mt_max[0]), "compute_only_ms_per_step_max_rank": float(mt_max[1]),
-                 "compute_only_ms_per_step_min_rank": float(mt[1])}
+                 "compute_only_ms_per_step_min_rank": float(mt[1]),
+                 "overlap": bool(overlap), "sm_reserve": sm_reserve if overlap else 0,
+                 "nccl_max_ctas": os.environ.get("NCCL_MAX_CTAS"),
+                 "what": "allreduce_ms = the whole exchange alone (both buckets back to back); compute_only = the same "
+                         "steps without any collective; with overlap on, bucket A (xyz, f_dc, f_rest, opacity, scaling, "
+                         "rotation: 59 of 91 floats per Gaussian) runs next to the deformation network's backward, "
+                         "which leaves sm_reserve SMs to NCCL; exposed share = ms_per_step - compute_only"}
+        multi["exposed_ms"] = None  # filled below, once ms_per_step is reduced over ranks
 
     # ---- sustained leg (untimed for the headline): the same loop for >= BENCH_SUSTAINED_S seconds with the clock
     #      sampler running, so the line also says what a long training run holds once clocks settle ----
@@ -688,6 +703,8 @@ def run_ours(args, rank, local, world):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, ms_e2e = float(t[0]), float(t[1])
+    if multi is not None:
+        multi["exposed_ms"] = ms_total / args.steps - multi["compute_only_ms_per_step_max_rank"]
 
     # ---- GPU reference leg (N = 1, rank 0, outside every product timing): BASELINE.md B1 + B2 ----
     gpu_ref = None
@@ -923,6 +940,9 @@ def main():
         rank = int(os.environ.get("RANK", "0"))
         run_reference_arm(args, rank, int(os.environ.get("WORLD_SIZE", "1")))
         return
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("BENCH_OVERLAP", "1") != "0":
+        # the collective that runs next to the MLP backward gets exactly the SMs that backward leaves free
+        os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("BENCH_SM_RESERVE", "8"))
     rank, local, world = dp.init_from_env("nccl")
     try:
         run_ours(args, rank, local, world)

@@ -13,6 +13,7 @@
 #include "tc_gemm.cuh"
 #include "profiler.h"
 #include "tc_launch.cuh"
+#include <vector>
 #include "fused_mlp.cuh"
 #include <cstdlib>
 
@@ -341,8 +342,8 @@ static DeformWork carve_deform(char*& p, int W, int depth, size_t N) {
 
 static int check_weights(const ed3dgs_deform_weights* w) {
   if (!w) return ED3DGS_OK;
-  if (w->W < 16 || w->W > 128 || (w->W % 16) != 0) {
-    set_error("deform: net_width %d unsupported (multiple of 16, <= 128)", w->W);
+  if (w->W < 16 || w->W > 256 || (w->W % 16) != 0) {
+    set_error("deform: net_width %d unsupported (multiple of 16, <= 256)", w->W);
     return ED3DGS_ERR_ARG;
   }
   if (w->depth < 1 || w->depth > ED3DGS_DEFORM_MAX_DEPTH || (w->temb_dim % 4) || (w->gemb_dim % 16) || w->gemb_dim > 240) {
@@ -392,12 +393,7 @@ static cudaError_t fused_func_attr(const void* fn, size_t smem) {
   return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
-static int current_sm_count() {
-  int dev = 0, sms = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-    sms = 148;
-  return sms;
-}
+static int current_sm_count() { return tc_sm_count(); }
 
 // Forward of one stage in one launch (fused_mlp.cuh).
 static int stage_forward_fused(const ed3dgs_deform_weights* w, int s, int N, const float* emb, const float* tau,
@@ -471,6 +467,63 @@ static int stage_forward_fused(const ed3dgs_deform_weights* w, int s, int N, con
   return ED3DGS_OK;
 }
 
+// ---- layered path: any net_width up to 256 (multiple of 16), any defor_depth ---------------------------------------------
+// tc_rows_kernel puts at most 128 output features on the TMEM lanes, a tile programme holds TC_MAX_STEPS K slabs and a
+// launch TC_MAX_BATCH entries: wider layers become several batch entries (128 output features each, the weight / bias /
+// output / mask pointers advanced by the chunk) spread over as many launches as the limits ask for.
+struct TcEntry {
+  TcBatch b;
+  int K;   // contraction length of the entry
+};
+
+static cudaError_t tc_launch_many(int amaj, int bmaj, const TcArgs& base, const std::vector<TcEntry>& ent, float* scratch,
+                                  cudaStream_t stream) {
+  size_t i = 0;
+  while (i < ent.size()) {
+    TcArgs a = base;
+    int n = 0, steps = 0, kmax = 0;
+    while (i + n < ent.size() && n < TC_MAX_BATCH) {
+      const int K = ent[i + n].K;
+      const int st = (K + TC_KC - 1) / TC_KC;
+      const int km = K > kmax ? K : kmax;
+      const size_t floats = (size_t)((km + TC_KC - 1) / TC_KC) * 128 * (2 * TC_PC) * 4 * (size_t)(n + 1);
+      if (n > 0 && (steps + st > TC_MAX_STEPS || floats > tc_prep_scratch_floats())) break;
+      a.b[n] = ent[i + n].b;
+      a.b[n].K = K;
+      steps += st;
+      kmax = km;
+      ++n;
+    }
+    const cudaError_t e = tc_launch(amaj, bmaj, a, n, scratch, stream);
+    if (e != cudaSuccess) return e;
+    i += n;
+  }
+  return cudaSuccess;
+}
+
+// dst[g][f] = mask bit (g, f) ? dst[g][f] : 0 ; bias_grad[f] += column sums. One block per 32 Gaussians (one mask word
+// per feature), thread = feature. Only the wide layered path needs it (the input gradient of a trunk wider than the tile
+// programme is accumulated over several launches and masked afterwards).
+__global__ void __launch_bounds__(256) relu_mask_colsum(float* __restrict__ dst, long ld, int W, long N,
+                                                        const uint32_t* __restrict__ mask, long mask_ld, int mask_col,
+                                                        float* __restrict__ bias_grad) {
+  const long g0 = (long)blockIdx.x * 32;
+  const int jmax = (int)min(32L, N - g0);
+  for (int f = threadIdx.x; f < W; f += blockDim.x) {
+    const uint32_t word = mask[(g0 >> 5) * mask_ld + mask_col + f];
+    float cs = 0.f;
+    for (int j = 0; j < jmax; ++j) {
+      float* q = dst + (g0 + j) * ld + f;
+      const float r = ((word >> j) & 1u) ? *q : 0.f;
+      *q = r;
+      cs += r;
+    }
+    if (bias_grad != nullptr && cs != 0.f) atomicAdd(bias_grad + f, cs);
+  }
+}
+
+static inline int chunk_cols(int W, int c) { return W - c * 128 < 128 ? W - c * 128 : 128; }
+
 // One stage forward: base[h] -> dst[h] = base[h] + delta_h * coef[h].
 // acts_only: stop after the hidden layers (the activations and ReLU masks the layered backward reads).
 static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const float* emb, const float* tau,
@@ -478,43 +531,59 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
                          cudaStream_t stream, bool acts_only = false) {
   const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
+  const int nch = (W + 127) / 128;
   layer0_temporal_bias<<<(W + 3) / 4, 128, 0, stream>>>(w->feat_w[0], w->feat_b[0], ld0, temb, tau, wk.c1[s], W);
   {  // layer 0 on the per-Gaussian embedding
     TcArgs a = tc_args(gemb, ld0, N, gemb, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
-    a.b[0] = TcBatch{emb, w->feat_w[0] + temb, wk.R[s][0], wk.c1[s], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    a.b[0].mask_out = wk.Mr[s][0]; a.b[0].mask_ld = W;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
+    std::vector<TcEntry> ent;
+    for (int c = 0; c < nch; ++c) {
+      TcBatch b{emb, w->feat_w[0] + temb + (long)c * 128 * ld0, wk.R[s][0] + c * 128, wk.c1[s] + c * 128, nullptr, nullptr,
+                W, 0, chunk_cols(W, c), 0, 0, 1.f};
+      b.mask_out = wk.Mr[s][0]; b.mask_ld = W; b.mask_col = c * 128;
+      ent.push_back({b, gemb});
+    }
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_K_MAJOR, a, ent, wk.Wprep, stream));
   }
   for (int l = 1; l < D; ++l) {
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
-    a.b[0] = TcBatch{wk.R[s][l - 1], w->feat_w[l], wk.R[s][l], w->feat_b[l], nullptr, nullptr, W, 0, W, 0, 0, 1.f};
-    a.b[0].mask_out = wk.Mr[s][l]; a.b[0].mask_ld = W;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, 1, wk.Wprep, stream));
+    std::vector<TcEntry> ent;
+    for (int c = 0; c < nch; ++c) {
+      TcBatch b{wk.R[s][l - 1], w->feat_w[l] + (long)c * 128 * W, wk.R[s][l] + c * 128, w->feat_b[l] + c * 128, nullptr,
+                nullptr, W, 0, chunk_cols(W, c), 0, 0, 1.f};
+      b.mask_out = wk.Mr[s][l]; b.mask_ld = W; b.mask_col = c * 128;
+      ent.push_back({b, W});
+    }
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_K_MAJOR, a, ent, wk.Wprep, stream));
   }
   int act[5];
   const int na = active_heads(w, act);
-  {  // head hidden layers, all active heads in one launch
+  {  // head hidden layers, all active heads
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_BIAS_ACT);
     a.relu = 1;
+    std::vector<TcEntry> ent;
     for (int i = 0; i < na; ++i) {
       const int h = act[i];
-      a.b[i] = TcBatch{wk.R[s][D - 1], w->head_w1[h], wk.Rz[s] + (long)i * W, w->head_b1[h], nullptr, nullptr,
-                       5L * W, 0, W, 0, 0, 1.f};
-      a.b[i].mask_out = wk.Mz[s]; a.b[i].mask_ld = 5L * W; a.b[i].mask_col = i * W;
+      for (int c = 0; c < nch; ++c) {
+        TcBatch b{wk.R[s][D - 1], w->head_w1[h] + (long)c * 128 * W, wk.Rz[s] + (long)i * W + c * 128, w->head_b1[h] + c * 128,
+                  nullptr, nullptr, 5L * W, 0, chunk_cols(W, c), 0, 0, 1.f};
+        b.mask_out = wk.Mz[s]; b.mask_ld = 5L * W; b.mask_col = i * W + c * 128;
+        ent.push_back({b, W});
+      }
     }
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_K_MAJOR, a, ent, wk.Wprep, stream));
   }
   if (acts_only) return ED3DGS_OK;
   {  // head outputs fused with  x = x + delta * coef
     TcArgs a = tc_args(5L * W, W, N, W, 48, TC_EPI_HEAD);
+    std::vector<TcEntry> ent;
     for (int i = 0; i < na; ++i) {
       const int h = act[i];
-      a.b[i] = TcBatch{wk.Rz[s] + (long)i * W, w->head_w2[h], dst[h], w->head_b2[h], base[h], nullptr,
-                       hHeadDim[h], hHeadDim[h], hHeadDim[h], 0, 0, coef[h]};
+      ent.push_back({TcBatch{wk.Rz[s] + (long)i * W, w->head_w2[h], dst[h], w->head_b2[h], base[h], nullptr,
+                             hHeadDim[h], hHeadDim[h], hHeadDim[h], 0, 0, coef[h]}, W});
     }
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_K_MAJOR, a, na, wk.Wprep, stream));
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_K_MAJOR, a, ent, wk.Wprep, stream));
   }
   for (int h = 0; h < 5; ++h)
     if (!w->head_w1[h] && dst[h] != base[h])
@@ -522,11 +591,34 @@ static int stage_forward(const ed3dgs_deform_weights* w, int s, int N, const flo
   return ED3DGS_OK;
 }
 
+// Weight-gradient groups are collected and flushed WG_MAX_GROUPS at a time.
+struct WgBatcher {
+  WgArgs a{};
+  cudaStream_t stream;
+  WgBatcher(int N, cudaStream_t st) : stream(st) { a.single = g_single; a.N = N; }
+  cudaError_t add(const WgGroup& g) {
+    if (g.nseg <= 0) return cudaSuccess;
+    a.g[a.ngroups++] = g;
+    return a.ngroups == WG_MAX_GROUPS ? flush() : cudaSuccess;
+  }
+  cudaError_t flush() {
+    if (a.ngroups == 0) return cudaSuccess;
+    const cudaError_t e = tc_wgrad_launch(a, stream);
+    const int N = a.N;
+    a = WgArgs{};
+    a.single = g_single;
+    a.N = N;
+    return e;
+  }
+};
+
 static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
                           const float* emb, const float* tau, const float* G, const float* colsum, DeformWork& wk,
                           float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
   const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
+  const int nch = (W + 127) / 128;
+  const int pair = 2 * W <= 256 ? 2 : 1;   // heads side by side on the N = 256 side of a weight-gradient group
   int act[5];
   const int na = active_heads(w, act);
 
@@ -536,53 +628,55 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
       if (g->head_b2[h]) add_vec<<<1, 64, 0, stream>>>(g->head_b2[h], colsum + hHeadOff[h], hHeadDim[h]);
     }
     // dW2_h[j][f] += sum_n G_h[n][j] * Rz_h[n][f]: all 80 columns of G on the M side, the hidden
-    // activations of two heads side by side on the N side; only the (head rows x head columns) blocks
+    // activations of one or two heads on the N side; only the (head rows x head columns) blocks
     // of the product are kept.
-    WgArgs a{};
-    a.single = g_single;
-    a.N = N;
-    for (int i0 = 0; i0 < na; i0 += 2) {
-      WgGroup& gr = a.g[a.ngroups];
+    WgBatcher wb(N, stream);
+    for (int i0 = 0; i0 < na; i0 += pair) {
+      WgGroup gr{};
+      const int cnt = i0 + pair <= na ? pair : na - i0;
       gr.P = G; gr.ldp = GW; gr.pcols = GW;
-      gr.Q = wk.Rz[s] + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = (i0 + 1 < na ? 2 : 1) * W;
-      for (int i = i0; i < i0 + 2 && i < na; ++i) {
+      gr.Q = wk.Rz[s] + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = cnt * W;
+      for (int i = i0; i < i0 + cnt; ++i) {
         const int h = act[i];
         if (!g->head_w2[h]) continue;
         gr.seg[gr.nseg++] = WgSegment{g->head_w2[h], 1, (long)W, (i - i0) * W, W, hHeadOff[h], hHeadDim[h]};
       }
-      if (gr.nseg > 0) ++a.ngroups;
-      else gr = WgGroup{};
+      TC_TRY(wb.add(gr));
     }
-    TC_TRY(tc_wgrad_launch(a, stream));
+    TC_TRY(wb.flush());
   }
   {  // dZ_h = (G_h * W2_h) masked by Rz_h > 0
     TcArgs a = tc_args(GW, W, N, 0, W, TC_EPI_MASK);
+    a.K = 48;
+    std::vector<TcEntry> ent;
     for (int i = 0; i < na; ++i) {
       const int h = act[i];
-      a.b[i] = TcBatch{G + hHeadOff[h], w->head_w2[h], wk.dZ + (long)i * W, nullptr, wk.Rz[s] + (long)i * W,
-                       g ? g->head_b1[h] : nullptr, 5L * W, 5L * W, W, hHeadPad[h], hHeadDim[h], 1.f};
-      a.b[i].mask_in = wk.Mz[s]; a.b[i].mask_ld = 5L * W; a.b[i].mask_col = i * W;
-    }
-    a.K = 48;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, na, wk.Wprep, stream));
-  }
-  if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i]: trunk activations on the M side, two heads' dZ on the N side
-    WgArgs a{};
-    a.single = g_single;
-    a.N = N;
-    for (int i0 = 0; i0 < na; i0 += 2) {
-      WgGroup& gr = a.g[a.ngroups];
-      gr.P = wk.R[s][D - 1]; gr.ldp = W; gr.pcols = W;
-      gr.Q = wk.dZ + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = (i0 + 1 < na ? 2 : 1) * W;
-      for (int i = i0; i < i0 + 2 && i < na; ++i) {
-        const int h = act[i];
-        if (!g->head_w1[h]) continue;
-        gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], (long)W, 1, (i - i0) * W, W, 0, W};
+      for (int c = 0; c < nch; ++c) {
+        TcBatch b{G + hHeadOff[h], w->head_w2[h] + c * 128, wk.dZ + (long)i * W + c * 128, nullptr,
+                  wk.Rz[s] + (long)i * W + c * 128, (g && g->head_b1[h]) ? g->head_b1[h] + c * 128 : nullptr, 5L * W, 5L * W,
+                  chunk_cols(W, c), hHeadPad[h], hHeadDim[h], 1.f};
+        b.mask_in = wk.Mz[s]; b.mask_ld = 5L * W; b.mask_col = i * W + c * 128;
+        ent.push_back({b, hHeadPad[h]});
       }
-      if (gr.nseg > 0) ++a.ngroups;
-      else gr = WgGroup{};
     }
-    TC_TRY(tc_wgrad_launch(a, stream));
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_MN_MAJOR, a, ent, wk.Wprep, stream));
+  }
+  if (g) {  // dW1_h[o][i] += sum_n dZ_h[n][o] * R[n][i]: trunk activations (128 at a time) on the M side, dZ on the N side
+    WgBatcher wb(N, stream);
+    for (int mc = 0; mc < nch; ++mc)
+      for (int i0 = 0; i0 < na; i0 += pair) {
+        WgGroup gr{};
+        const int cnt = i0 + pair <= na ? pair : na - i0;
+        gr.P = wk.R[s][D - 1] + mc * 128; gr.ldp = W; gr.pcols = chunk_cols(W, mc);
+        gr.Q = wk.dZ + (long)i0 * W; gr.ldq = 5L * W; gr.qcols = cnt * W;
+        for (int i = i0; i < i0 + cnt; ++i) {
+          const int h = act[i];
+          if (!g->head_w1[h]) continue;
+          gr.seg[gr.nseg++] = WgSegment{g->head_w1[h] + mc * 128, (long)W, 1, (i - i0) * W, W, 0, gr.pcols};
+        }
+        TC_TRY(wb.add(gr));
+      }
+    TC_TRY(wb.flush());
   }
   // dR = (dZ[N, na*W] * W1_all[na*W, W]) masked by R > 0
   for (int i = 0; i < na; ++i)
@@ -594,28 +688,53 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
   // for layer 0 it is dc1, which also carries the temporal half of the first Linear
   TC_TRY(cudaMemsetAsync(wk.dc1, 0, W * sizeof(float), stream));
   auto trunk_bias_grad = [&](int l) -> float* { return l == 0 ? wk.dc1 : (g ? g->feat_b[l] : nullptr); };
-  {
+  if ((na * W + TC_KC - 1) / TC_KC <= TC_MAX_STEPS) {
     TcArgs a = tc_args(5L * W, W, N, na * W, W, TC_EPI_MASK);
-    a.b[0] = TcBatch{wk.dZ, wk.Wpack, dh, nullptr, wk.R[s][D - 1], trunk_bias_grad(D - 1), W, W, W, 0, 0, 1.f};
-    a.b[0].mask_in = wk.Mr[s][D - 1]; a.b[0].mask_ld = W;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
+    std::vector<TcEntry> ent;
+    float* bg = trunk_bias_grad(D - 1);
+    for (int c = 0; c < nch; ++c) {
+      TcBatch b{wk.dZ, wk.Wpack + c * 128, dh + c * 128, nullptr, wk.R[s][D - 1] + c * 128, bg ? bg + c * 128 : nullptr,
+                W, W, chunk_cols(W, c), 0, 0, 1.f};
+      b.mask_in = wk.Mr[s][D - 1]; b.mask_ld = W; b.mask_col = c * 128;
+      ent.push_back({b, na * W});
+    }
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_MN_MAJOR, a, ent, wk.Wprep, stream));
+  } else {
+    // contraction longer than one tile programme: accumulate head by head, then mask and take the column sums
+    for (int i = 0; i < na; ++i) {
+      TcArgs a = tc_args(5L * W, W, N, W, W, TC_EPI_ACCUM);
+      a.accumulate = i > 0;
+      std::vector<TcEntry> ent;
+      for (int c = 0; c < nch; ++c)
+        ent.push_back({TcBatch{wk.dZ + (long)i * W, wk.Wpack + (size_t)i * W * W + c * 128, dh + c * 128, nullptr, nullptr,
+                               nullptr, W, 0, chunk_cols(W, c), 0, 0, 1.f}, W});
+      TC_TRY(tc_launch_many(TC_K_MAJOR, TC_MN_MAJOR, a, ent, wk.Wprep, stream));
+    }
+    relu_mask_colsum<<<(N + 31) / 32, 256, 0, stream>>>(dh, W, W, N, wk.Mr[s][D - 1], W, 0, trunk_bias_grad(D - 1));
   }
   for (int l = D - 1; l >= 1; --l) {
     if (g && g->feat_w[l]) {  // dW_l[o][i] += sum_n dh[n][o] * R_{l-1}[n][i]
-      WgArgs a{};
-      a.single = g_single;
-    a.single = g_single;
-      a.N = N; a.ngroups = 1;
-      a.g[0].P = wk.R[s][l - 1]; a.g[0].ldp = W; a.g[0].pcols = W;
-      a.g[0].Q = dh; a.g[0].ldq = W; a.g[0].qcols = W;
-      a.g[0].nseg = 1;
-      a.g[0].seg[0] = WgSegment{g->feat_w[l], (long)W, 1, 0, W, 0, W};
-      TC_TRY(tc_wgrad_launch(a, stream));
+      WgBatcher wb(N, stream);
+      for (int mc = 0; mc < nch; ++mc) {
+        WgGroup gr{};
+        gr.P = wk.R[s][l - 1] + mc * 128; gr.ldp = W; gr.pcols = chunk_cols(W, mc);
+        gr.Q = dh; gr.ldq = W; gr.qcols = W;
+        gr.nseg = 1;
+        gr.seg[0] = WgSegment{g->feat_w[l] + mc * 128, (long)W, 1, 0, W, 0, gr.pcols};
+        TC_TRY(wb.add(gr));
+      }
+      TC_TRY(wb.flush());
     }
     TcArgs a = tc_args(W, W, N, W, W, TC_EPI_MASK);
-    a.b[0] = TcBatch{dh, w->feat_w[l], dh_other, nullptr, wk.R[s][l - 1], trunk_bias_grad(l - 1), W, W, W, 0, 0, 1.f};
-    a.b[0].mask_in = wk.Mr[s][l - 1]; a.b[0].mask_ld = W;
-    TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
+    std::vector<TcEntry> ent;
+    float* bg = trunk_bias_grad(l - 1);
+    for (int c = 0; c < nch; ++c) {
+      TcBatch b{dh, w->feat_w[l] + c * 128, dh_other + c * 128, nullptr, wk.R[s][l - 1] + c * 128, bg ? bg + c * 128 : nullptr,
+                W, W, chunk_cols(W, c), 0, 0, 1.f};
+      b.mask_in = wk.Mr[s][l - 1]; b.mask_ld = W; b.mask_col = c * 128;
+      ent.push_back({b, W});
+    }
+    TC_TRY(tc_launch_many(TC_K_MAJOR, TC_MN_MAJOR, a, ent, wk.Wprep, stream));
     float* t = dh; dh = dh_other; dh_other = t;
   }
   // layer 0: weight gradient of the embedding columns, then dE (dc1 came from the MASK epilogue above)
@@ -798,6 +917,12 @@ int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, in
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("temporal_embed_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
   return ED3DGS_OK;
+}
+
+int ed3dgs_deform_set_sm_reserve(int n_sms) {
+  const int prev = tc_sm_reserve();
+  tc_sm_reserve() = n_sms > 0 ? n_sms : 0;
+  return prev;
 }
 
 size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N) {

@@ -35,11 +35,20 @@ inline bool tc_rows_build(TcArgs& a) {
   return ns > 0;
 }
 
+// SMs the persistent kernels of the deformation network leave free (ed3dgs_deform_set_sm_reserve): a concurrent NCCL
+// collective needs a few SMs of its own, otherwise its CTAs wait for a persistent CTA to retire and the CTAs of the
+// next persistent launch that lose the race form a second wave (static tile assignment: the kernel takes twice as long).
+inline int& tc_sm_reserve() {
+  static int reserve = 0;
+  return reserve;
+}
+
 inline int tc_sm_count() {   // of the current device (not cached: a process may drive several GPUs)
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
     sms = 148;
-  return sms;
+  const int r = tc_sm_reserve();
+  return (r > 0 && r < sms) ? sms - r : sms;
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda).

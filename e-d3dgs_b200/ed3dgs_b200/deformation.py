@@ -14,6 +14,20 @@ import torch.nn as nn
 from . import _deform_abi as abi
 from . import _lib
 
+# Multi-GPU overlap (dp.OverlapSync): when a side stream is set, the kernels of the network's backward are issued on
+# it, so that the all-reduce of the Gaussian-parameter gradients (which are this node's *upstream* gradients and hence
+# final before it starts) can run on NCCL's stream at the same time. Everything the side stream still reads or writes
+# is parked in `keep` until dp.OverlapSync has made the main stream wait for it.
+_overlap = {"stream": None, "sm_reserve": 0, "keep": []}
+
+
+def set_backward_stream(stream, sm_reserve=0):
+    """stream = None switches the overlap off. sm_reserve: SMs the persistent backward kernels leave to NCCL."""
+    _overlap["stream"] = stream
+    _overlap["sm_reserve"] = int(sm_reserve) if stream is not None else 0
+    _overlap["keep"].clear()
+
+
 _HEAD_NAMES = ("pos", "scales", "rotations", "opacity", "rgb")
 # deform_network.precision -> ed3dgs_deform_weights::precision (include/ed3dgs_deform.h)
 _PRECISIONS = {"fp32": 0, "3xtf32": 0, "tf32": 1}
@@ -72,11 +86,14 @@ def temporal_embed(weight, n_rows, t_dev):
 
 
 class _DeformFunction(torch.autograd.Function):
-    """inputs: cfg (dict), t (1-element CUDA tensor), temporal table, embedding, 5 per-Gaussian
-    inputs, then the coarse and fine Linear parameters. outputs: 5 coarse (sub) + 5 final tensors."""
+    """inputs: cfg (dict), t (1-element CUDA tensor), the per-camera time offsets, temporal table, embedding, 5
+    per-Gaussian inputs, then the coarse and fine Linear parameters. outputs: 5 coarse (sub) + 5 final tensors.
+    `offsets` takes no part in the forward arithmetic (the caller has already added the camera's offset to t,
+    deformation.py:122-127 of the reference); it is an input so that its gradient -- d_t routed to row cam_no, or spread
+    over the non-zero rows when cam_no is None -- leaves this node finished, on whichever stream the backward runs."""
 
     @staticmethod
-    def forward(ctx, cfg, t, table, emb, pts, scales, rots, opac, sh, *params):
+    def forward(ctx, cfg, t, offsets, table, emb, pts, scales, rots, opac, sh, *params):
         dev = emb.device
         N = emb.shape[0]
         lib = _lib.lib()
@@ -109,7 +126,7 @@ class _DeformFunction(torch.autograd.Function):
                     ctypes.byref(out_arr), ctypes.byref(coef), work.data_ptr(), nbytes, _lib.stream_handle()))
         ctx.cfg = cfg
         ctx.set_materialize_grads(False)   # unused outputs arrive as None instead of N-sized zero tensors
-        ctx.save_for_backward(t_c, table_c, emb_c, tau_c, tau_f, work, *pc, *pf)
+        ctx.save_for_backward(t_c, table_c, emb_c, tau_c, tau_f, work, offsets.detach(), *pc, *pf)
         subs[4] = subs[4].view(N, 16, 3)
         outs[4] = outs[4].view(N, 16, 3)
         return (*subs, *outs)
@@ -117,8 +134,8 @@ class _DeformFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, *gouts):
         cfg = ctx.cfg
-        t_c, table_c, emb_c, tau_c, tau_f, work = ctx.saved_tensors[:6]
-        params = list(ctx.saved_tensors[6:])
+        t_c, table_c, emb_c, tau_c, tau_f, work, offsets = ctx.saved_tensors[:7]
+        params = list(ctx.saved_tensors[7:])
         nc = cfg["n_params_c"]
         pc, pf = params[:nc], params[nc:]
         dev = emb_c.device
@@ -139,7 +156,7 @@ class _DeformFunction(torch.autograd.Function):
         # 256-byte boundary). With .grad unset (zero_grad(set_to_none=True), train.py:448) autograd adopts these
         # slices as the parameters' .grad without a copy.
         pad = lambda n: (n + 63) // 64 * 64  # noqa: E731
-        sizes = [p.numel() for p in pc] + [p.numel() for p in pf] + [temb, temb, table_c.numel(), 1]
+        sizes = [p.numel() for p in pc] + [p.numel() for p in pf] + [temb, temb, table_c.numel(), 1, offsets.numel()]
         flat = torch.zeros(sum(pad(n) for n in sizes), dtype=torch.float32, device=dev)
         offs, o = [], 0
         for n in sizes:
@@ -152,6 +169,7 @@ class _DeformFunction(torch.autograd.Function):
         d_tau_f = flat[offs[k + 1]:offs[k + 1] + temb]
         d_table = flat[offs[k + 2]:offs[k + 2] + table_c.numel()].view(table_c.shape)
         d_t = flat[offs[k + 3]:offs[k + 3] + 1]
+        d_offsets = flat[offs[k + 4]:offs[k + 4] + offsets.numel()].view(offsets.shape)
         # the first stage that runs overwrites d_emb (accumulate flag), so it needs no zero fill
         d_emb = (torch.empty if (N > 0 and (cfg["coarse"] or cfg["fine"])) else torch.zeros)(
             N, gemb, dtype=torch.float32, device=dev)
@@ -160,8 +178,19 @@ class _DeformFunction(torch.autograd.Function):
         sgc = _grads_struct(gc, depth, cfg["enabled"]) if cfg["coarse"] else None
         sgf = _grads_struct(gf, depth, cfg["enabled"]) if cfg["fine"] else None
         ptr = lambda x: x.data_ptr() if x is not None else None  # noqa: E731
-        with torch.cuda.device(dev):
+        side = _overlap["stream"] if N > 0 else None
+        k_out, k_sub = d_out, d_sub
+        if side is not None:
+            # the caller all-reduces the pass-through gradients in place while these kernels run: they read copies
+            k_out = [None if x is None else x.clone() for x in d_out]
+            k_sub = [None if x is None else x.clone() for x in d_sub]
+            side.wait_stream(torch.cuda.current_stream(dev))
+            if _overlap["sm_reserve"]:
+                lib.ed3dgs_deform_set_sm_reserve(_overlap["sm_reserve"])
+        with torch.cuda.device(dev), torch.cuda.stream(side):
             if N > 0:
+                d_out_keep, d_sub_keep = d_out, d_sub
+                d_out, d_sub = k_out, k_sub
                 dout_arr = abi.PtrArr5(*[ptr(x) for x in d_out])
                 dsub_arr = abi.PtrArr5(*[ptr(x) for x in d_sub])
                 coef = abi.FloatArr5(*cfg["coef"])
@@ -177,6 +206,21 @@ class _DeformFunction(torch.autograd.Function):
                         _lib.check(lib.ed3dgs_temporal_embed_backward(
                             table_c.data_ptr(), max_emb, dim, int(rows), t_c.data_ptr(), d_tau.data_ptr(),
                             d_table.data_ptr(), d_t.data_ptr(), _lib.stream_handle()))
+                d_out, d_sub = d_out_keep, d_sub_keep
+                if ctx.needs_input_grad[2]:   # the camera's time offset (same stream as the kernels)
+                    cam_no = cfg["cam_no"]
+                    if cam_no is not None:
+                        d_offsets[cam_no] = d_t
+                    else:   # offset = mean of the non-zero rows; no non-zero row: the reference's nan -> 0, no gradient
+                        nz = offsets.ne(0)
+                        d_offsets.copy_(torch.where(nz, d_t / nz.sum().clamp_min(1), torch.zeros_like(d_t)).view(offsets.shape))
+        if side is not None:
+            if _overlap["sm_reserve"]:
+                lib.ed3dgs_deform_set_sm_reserve(0)
+            # (not flat / d_emb: a second reference would make AccumulateGrad copy them -- on the main stream, too early)
+            _overlap["keep"].append((k_out, k_sub, work, t_c, table_c, emb_c, tau_c, tau_f, offsets, params))
+            if ctx.needs_input_grad[1]:   # somebody differentiates the time itself: its gradient is consumed on the main stream
+                torch.cuda.current_stream(dev).wait_stream(side)
 
         def passthrough(h):
             a, b = d_out[h], d_sub[h]
@@ -186,7 +230,8 @@ class _DeformFunction(torch.autograd.Function):
             return g.view(N, 16, 3) if h == 4 else g
 
         d_ins = [passthrough(h) for h in range(5)]
-        return (None, d_t.view(()).reshape(ctx.cfg["t_shape"]), d_table, d_emb, *d_ins, *gc, *gf)
+        return (None, d_t.view(()).reshape(ctx.cfg["t_shape"]) if ctx.needs_input_grad[1] else None,
+                d_offsets if ctx.needs_input_grad[2] else None, d_table, d_emb, *d_ins, *gc, *gf)
 
 
 class deform_network(nn.Module):
@@ -247,12 +292,13 @@ class deform_network(nn.Module):
         pts, scales, rotations, opacity = point[:, :3], scales[:, :3], rotations[:, :4], opacity[:, :1]
         orig = (pts, scales, rotations, opacity, sh_coefs)
         a = self.args
-        if cam_no is None:
-            offset = torch.masked_select(self.offsets, self.offsets.ne(0)).mean()
-            offset[torch.isnan(offset)] = 0
-        else:
-            offset = self.offsets[cam_no]
-        time_emb += offset
+        with torch.no_grad():   # the gradient of the offsets comes out of the autograd node below
+            if cam_no is None:
+                offset = torch.masked_select(self.offsets, self.offsets.ne(0)).mean()
+                offset[torch.isnan(offset)] = 0
+            else:
+                offset = self.offsets[cam_no]
+            time_emb += offset
 
         use_anneal = a.use_anneal
         coef = 1 if not use_anneal else np.clip(iter / 1000, 0, 1)
@@ -283,9 +329,9 @@ class deform_network(nn.Module):
                    rows_c=self._rows(iter, num_down_emb_c, a.use_coarse_temporal_embedding),
                    rows_f=self._rows(iter, num_down_emb_f, False),
                    coef=(float(coef), float(coef * coef_s), float(coef), float(coef * coef_o), float(coef_c)),
-                   t_shape=tuple(t.shape), precision=_PRECISIONS[self.precision])
-        res = _DeformFunction.apply(cfg, t, self.weight, emb, pts, scales, rotations, opacity, sh_in, *params_c,
-                                    *params_f)
+                   t_shape=tuple(t.shape), precision=_PRECISIONS[self.precision], cam_no=cam_no)
+        res = _DeformFunction.apply(cfg, t, self.offsets, self.weight, emb, pts, scales, rotations, opacity, sh_in,
+                                    *params_c, *params_f)
         sub, out = list(res[:5]), list(res[5:])
         if sh_coefs is None:
             sub[4], out[4] = None, None

@@ -123,6 +123,67 @@ class GradSync:
         return ts
 
 
+class OverlapSync(GradSync):
+    """GradSync with the exchange split in two and the first half hidden behind the deformation network's backward.
+
+    Bucket A = the gradients of the per-Gaussian rasterizer inputs (xyz, f_dc, f_rest, opacity, scaling, rotation:
+    59 of the 91 floats per Gaussian). They are the *upstream* gradients of the deformation node, i.e. final once the
+    rasterizer backward and the activations backward have run. Bucket B = embedding + deformation network.
+    With the overlap on, `deformation._DeformFunction.backward` issues its kernels on a side stream with `sm_reserve`
+    SMs left free; allreduce() then (1) reduces bucket A -- NCCL's stream only waits for the main stream, so the
+    collective runs next to the MLP backward --, (2) makes the main stream wait for the side stream, (3) reduces bucket B.
+    Host logic only: without CUDA (gloo tests) or with one rank it degrades to GradSync."""
+
+    def __init__(self, params, early, sm_reserve=8):
+        super().__init__(params)
+        early_ids = {id(p) for p in early}
+        self.early = [p for p in self.params if id(p) in early_ids]
+        self.late = [p for p in self.params if id(p) not in early_ids]
+        self.sm_reserve = sm_reserve
+        self.side = None
+        self.active = False
+
+    def enable(self):
+        """Switch the side stream on (needs CUDA and more than one rank); returns whether it is active."""
+        from . import deformation
+        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        if multi and torch.cuda.is_available() and self.params and self.params[0].is_cuda:
+            self.side = torch.cuda.Stream(device=self.params[0].device)
+            deformation.set_backward_stream(self.side, self.sm_reserve)
+            self.active = True
+        return self.active
+
+    def disable(self):
+        from . import deformation
+        self.join()
+        deformation.set_backward_stream(None)
+        self.side, self.active = None, False
+
+    def join(self):
+        """Main stream waits for the side stream; releases what the side stream was using."""
+        from . import deformation
+        if self.side is not None:
+            torch.cuda.current_stream(self.side.device).wait_stream(self.side)
+        deformation._overlap["keep"].clear()
+
+    def _reduce(self, params, scale, collective):
+        keep = self.params
+        self.params = params
+        try:
+            return GradSync.allreduce(self, scale) if collective else self.tensors()
+        finally:
+            self.params = keep
+
+    def allreduce(self, scale=None, collective=True):
+        """collective=False: only the stream join (bench's 'steps without the collective' breakdown)."""
+        if not self.active:
+            return GradSync.allreduce(self, scale) if collective else self.tensors()
+        a = self._reduce(self.early, scale, collective)
+        self.join()
+        b = self._reduce(self.late, scale, collective)
+        return a + b
+
+
 def shard_views(n_views, rank, world):
     """Indices of the views rank handles in a step of n_views (contiguous, ragged tail allowed)."""
     per = (n_views + world - 1) // world

@@ -68,6 +68,15 @@ int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, in
 size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N);
 
 /*
+ * Multi-GPU overlap (no reference counterpart: the reference is single-GPU, train.py:171-187). The persistent
+ * tcgen05 kernels of the deformation network launch one CTA per SM; `n_sms` > 0 makes every later launch leave that
+ * many SMs free, so that an NCCL collective running on another stream (the all-reduce of the Gaussian-parameter
+ * gradients, final before the network's backward starts) has SMs of its own. 0 restores the full grid. Process-wide;
+ * returns the previous value.
+ */
+int ed3dgs_deform_set_sm_reserve(int n_sms);
+
+/*
  * Forward of both stages. coarse / fine may be NULL (no_coarse_deform / no_fine_deform).
  *   in[h], sub[h], out[h]: [N, k_h] for h = pos, scales, rotations, opacity, rgb.
  *   sub = in + delta_coarse * coef   (the reference's *_sub tuple), out = sub + delta_fine * coef.

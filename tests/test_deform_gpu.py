@@ -256,3 +256,12 @@ def test_full_c3_size_rows_match_fp64_oracle():
         assert _rel(leaves[k].grad[p], gref) <= GRAD_TOL, k
     for k in leaves:
         assert torch.isfinite(leaves[k].grad).all()
+
+
+@pytest.mark.parametrize("W,D,N", [(256, 1, 3000 + 7), (256, 2, 1500 + 3), (192, 2, 777), (256, 8, 600)])
+def test_net_width_up_to_256(W, D, N):
+    """deform_network(D=8, W=256) is the reference's constructor default (scene/deformation.py:16): widths above 128 take
+    the layered path with the output features of every Linear split into chunks of 128 (two M-side passes) and the
+    5*W-long contraction of the trunk's input gradient accumulated head by head."""
+    rec = oracle_record(N=N, W=W, D=D, kink_free=True, seed=7)
+    check(rec, *run_product(rec))

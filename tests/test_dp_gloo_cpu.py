@@ -93,3 +93,38 @@ def test_shard_views_ragged():
     from ed3dgs_b200 import dp
     assert [dp.shard_views(8, r, 8) for r in range(8)] == [[i] for i in range(8)]
     assert dp.shard_views(3, 3, 4) == [] and dp.shard_views(3, 2, 4) == [2]
+
+
+def _worker_overlap(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from ed3dgs_b200 import dp
+    dp.init_from_env("gloo")
+    torch.manual_seed(0)
+    xyz = torch.nn.Parameter(torch.ones(6, 3))
+    emb = torch.nn.Parameter(torch.ones(6, 2))
+    lin = torch.nn.Linear(2, 2)
+    sync = dp.OverlapSync([xyz, emb] + list(lin.parameters()), early=[xyz], sm_reserve=8)
+    ok = [p is xyz for p in sync.early] == [True] and len(sync.late) == 3
+    ok = ok and sync.enable() is False          # no CUDA here: stays a plain two-bucket exchange
+    for _step in range(2):
+        sync.zero()
+        w = float(rank + 1)
+        ((xyz * w).sum() + (lin(emb) * w).sum()).backward()
+        lw = lin.weight.detach().clone()
+        ts = sync.allreduce(1.0 / world)
+        ok = ok and len(ts) == 4
+        ok = ok and torch.allclose(xyz.grad, torch.full((6, 3), 1.5))
+        ok = ok and torch.allclose(emb.grad, (lw.sum(0) * 1.5).expand(6, 2))
+        ok = ok and len(sync.allreduce(1.0 / world, collective=False)) == 4   # the join-only form bench.py uses
+    sync.disable()
+    out[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_overlap_sync_world2():
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_overlap, args=(2, port, out), nprocs=2, join=True)
+    assert dict(out) == {0: True, 1: True}

@@ -1,0 +1,59 @@
+"""Single-GPU checks of the two mechanisms dp.OverlapSync relies on (the NCCL side needs two devices:
+tests/dp_overlap_check.py under torchrun): the SM reserve of the persistent kernels and the deformation backward issued
+on a side stream must both leave every gradient unchanged (up to the arrival order of fp32 atomics)."""
+import pytest
+import torch
+
+import test_deform_gpu as T
+
+pytestmark = pytest.mark.gpu
+
+
+def _grads(rec):
+    net, finals, subs, leaves, _ = T.run_product(rec)
+    out = {"in_" + k: v.grad.detach().clone() for k, v in leaves.items()}
+    out.update({"p_" + k: p.grad.detach().clone() for k, p in net.named_parameters() if p.grad is not None})
+    out.update({f"final{i}": x.detach().clone() for i, x in enumerate(finals)})
+    return out
+
+
+def _compare(a, b, tol=2e-5):
+    assert a.keys() == b.keys()
+    for k in a:
+        scale = float(a[k].abs().max()) + 1e-30
+        err = float((a[k] - b[k]).abs().max()) / scale
+        assert err <= tol, (k, err)
+
+
+@pytest.mark.parametrize("shape", [dict(N=40_000 + 5, W=128, D=1), dict(N=3000, W=64, D=2)])
+def test_sm_reserve_leaves_results_unchanged(shape):
+    from ed3dgs_b200 import _lib
+    rec = T.oracle_record(kink_free=True, **shape)
+    ref = _grads(rec)
+    lib = _lib.lib()
+    assert lib.ed3dgs_deform_set_sm_reserve(8) == 0
+    try:
+        got = _grads(rec)
+    finally:
+        assert lib.ed3dgs_deform_set_sm_reserve(0) == 8
+    _compare(ref, got)
+
+
+@pytest.mark.parametrize("shape", [dict(N=40_000 + 5, W=128, D=1), dict(N=3000, W=64, D=2)])
+def test_backward_on_side_stream_leaves_results_unchanged(shape):
+    from ed3dgs_b200 import deformation
+    rec = T.oracle_record(kink_free=True, **shape)
+    ref = _grads(rec)
+    side = torch.cuda.Stream()
+    deformation.set_backward_stream(side, sm_reserve=8)
+    try:
+        from ed3dgs_b200.deformation import deform_network  # noqa: F401
+        net, finals, subs, leaves, _ = T.run_product(rec)   # ends with a device-wide synchronize
+        assert len(deformation._overlap["keep"]) == 1
+        torch.cuda.current_stream().wait_stream(side)
+        got = {"in_" + k: v.grad.detach().clone() for k, v in leaves.items()}
+        got.update({"p_" + k: p.grad.detach().clone() for k, p in net.named_parameters() if p.grad is not None})
+        got.update({f"final{i}": x.detach().clone() for i, x in enumerate(finals)})
+    finally:
+        deformation.set_backward_stream(None)
+    _compare(ref, got)
