@@ -14,7 +14,6 @@
 #include "profiler.h"
 #include "tc_launch.cuh"
 #include <vector>
-#include "fused_mlp.cuh"
 #include <cstdlib>
 
 namespace ed3dgs {
@@ -850,12 +849,16 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
     WgArgs a{};
     a.single = g_single;
     a.N = N;
-    for (int i0 = 0; i0 < na; i0 += 2) {   // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n], two heads side by side (N = 256)
+    // dW1_h[o][i] += sum_n dzT_h[o][n] hT[i][n]: one head per group (tensor-memory kernel, N = 128) or two heads side by
+    // side (shared-memory kernel, N = 256)
+    static const bool wg_ts = [] { const char* e = getenv("ED3DGS_WG_TS"); return e ? atoi(e) != 0 : true; }();
+    const int per = wg_ts ? 1 : 2;
+    for (int i0 = 0; i0 < na; i0 += per) {
       WgGroup& gr = a.g[a.ngroups];
       gr = WgGroup{};
       gr.P = wk.hT[s]; gr.pk = 1; gr.prow_total = 128; gr.pcols = 128;
-      gr.Q = wk.dzT + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? 2 : 1) * 128;
-      for (int i = i0; i < i0 + 2 && i < na; ++i) {
+      gr.Q = wk.dzT + (size_t)i0 * 128 * 128; gr.qk = 1; gr.qrow_total = (long)na * 128; gr.qcols = (i0 + 1 < na ? per : 1) * 128;
+      for (int i = i0; i < i0 + per && i < na; ++i) {
         const int h = act[i];
         if (!g->head_w1[h]) continue;
         gr.seg[gr.nseg++] = WgSegment{g->head_w1[h], 128, 1, (i - i0) * 128, 128, 0, 128};
@@ -880,7 +883,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
       gr.nseg = 1;
       gr.seg[0] = WgSegment{g->feat_w[0] + temb, 1, ld0, 0, gemb, 0, 128};
     }
-    TC_TRY(tc_wgrad_launch(a, stream));
+    TC_TRY(tc_wgrad_launch(a, stream, wg_ts));
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, 128, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);

@@ -5,6 +5,8 @@
 #include "tc_gemm.cuh"
 #include "tc_rows.cuh"
 #include "tc_wgrad.cuh"
+#include "fused_mlp.cuh"
+#include "tc_wgrad_ts.cuh"
 #include "profiler.h"
 #include <cstdlib>
 
@@ -114,10 +116,14 @@ inline cudaError_t tc_rows_launch(TcArgs& a, const char* name, cudaStream_t stre
 }
 
 // Weight gradients: D = P^T Q over all Gaussians, scattered into the gradient matrices (tc_wgrad.cuh).
-inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
+// ts: the kernel of tc_wgrad_ts.cuh (P of every group feature-major and fed through tensor memory, Q at most 128 columns).
+inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream, bool ts = false) {
   if (a_in.ngroups <= 0 || a_in.N <= 0) return cudaSuccess;
   if (a_in.ngroups > WG_MAX_GROUPS) return cudaErrorInvalidValue;
   WgArgs a = a_in;
+  if (ts)
+    for (int i = 0; i < a.ngroups; ++i)
+      if (!a.g[i].pk || a.g[i].qcols > 128) return cudaErrorInvalidValue;
   tc_encode_tiled_fn enc = tc_encode_tiled();
   if (!enc) return cudaErrorNotSupported;
   for (int i = 0; i < a.ngroups; ++i) {
@@ -158,7 +164,8 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
     }
   }
   {  // a per-device attribute: set on every launch (a process-wide flag would miss the second GPU)
-    const cudaError_t e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
+    const cudaError_t e = ts ? cudaFuncSetAttribute(tc_wgrad_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WT_SMEM_BYTES)
+                             : cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM_BYTES);
     if (e != cudaSuccess) return e;
   }
   static const int slice_env = [] { const char* e = getenv("ED3DGS_WG_SLICE"); const int v = e ? atoi(e) : 0; return v >= 128 ? v / 128 * 128 : 0; }();
@@ -166,7 +173,8 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream) {
   const int items = ((a.N + a.slice - 1) / a.slice) * a.ngroups;
   const int grid = items < tc_sm_count() ? items : tc_sm_count();
   ProfScope ps("tc_wgrad_kernel", stream);
-  tc_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(a);
+  if (ts) tc_wgrad_ts_kernel<<<grid, WT_THREADS, WT_SMEM_BYTES, stream>>>(a);
+  else tc_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(a);
   return cudaGetLastError();
 }
 

@@ -25,7 +25,7 @@
 namespace ed3dgs {
 
 constexpr int WG_SLICE = 2048;                    // default Gaussians per work item (tensor-core accumulation chain)
-constexpr int WG_MAX_GROUPS = 9;                  // one stage's dW1 pairs, dW2 heads and dW0 in a single launch
+constexpr int WG_MAX_GROUPS = 12;                 // one stage's dW1 heads (or pairs), dW2 heads and dW0 in a single launch
 constexpr int WG_EPI_WARPS = 8;                   // warps 0..7 (TMEM lane quarter = warp % 4)
 constexpr int WG_MMA_WARP = 8;
 constexpr int WG_LOAD_WARP = 9;

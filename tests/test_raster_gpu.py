@@ -199,3 +199,28 @@ def test_buffer_callback_cycle_is_broken_on_cpu_objects():
         assert r() is None
     finally:
         gc.enable()
+
+
+@needs_ref
+def test_needle_gaussians_survive_the_patch_cull():
+    """Screen-space needles hundreds of pixels long at ~45 degrees: det = a c - b^2 of their conic cancels to a few
+    percent, more than the margin of the warp-level patch cull (raster_cull.cuh), which therefore hands such splats to
+    the exact per-pixel test. The render must still match the reference pixel for pixel (<= 1e-5), n_contrib exactly."""
+    import math
+    rs, inp = pu.make_case(P=4000, W=640, H=480)
+    g = torch.Generator(device="cuda").manual_seed(21)
+    n = 600
+    idx = torch.randperm(4000, device="cuda", generator=g)[:n]
+    scales = inp["scales"].clone()
+    scales[idx] = torch.tensor([0.08, 2e-5, 2e-5], device="cuda") * (0.5 + torch.rand(n, 1, device="cuda", generator=g))
+    ang = math.pi / 4 + 0.2 * (torch.rand(n, device="cuda", generator=g) - 0.5)
+    rot = inp["rotations"].clone()
+    rot[idx] = torch.stack([torch.cos(ang / 2), torch.zeros_like(ang), torch.zeros_like(ang), torch.sin(ang / 2)], -1)
+    op = inp["opacities"].clone()
+    op[idx] = 0.9
+    inp = dict(inp, scales=scales.contiguous(), rotations=rot.contiguous(), opacities=op.contiguous())
+    a = pu.run_product(rs, inp)
+    b = pu.run_reference(rs, inp)
+    rep = pu.compare(rs, a, b)
+    print({k: v for k, v in rep.items() if not k.startswith("grad_")})
+    pu.assert_report(rep, rs)
