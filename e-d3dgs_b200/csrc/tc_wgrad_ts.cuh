@@ -34,14 +34,17 @@ constexpr int WT_P_BYTES = 16 * 128 * 4;          // P box: 128 features x 16 Ga
 constexpr int WT_Q_BYTES = 16 * 128 * 4;          // Q box: up to 128 features
 constexpr int WT_HI_SLAB = WT_P_BYTES + WT_Q_BYTES;
 constexpr int WT_HI_SLOTS = 8;                    // = slots of the TMEM A ring (same index, same phase)
-constexpr int WT_LO_SLOTS = 6;
+constexpr int WT_LO_SLOTS = WT_HI_SLOTS;           // lo slot i belongs to hi slot i: one ring position, one pair of barriers
 constexpr uint32_t WT_A_BASE = 256;
 constexpr size_t WT_SMEM_BYTES = (size_t)WT_HI_SLOTS * WT_HI_SLAB + (size_t)WT_LO_SLOTS * WT_Q_BYTES + 1024;
 
+// The MMA warp's issue loop is the critical path of this kernel (one thread: waits, fence, descriptors, six UMMAs, commits
+// per 16 Gaussians), so a slab costs it ONE wait and ONE commit: `ready` collects the fill warps and the stagers, `free`
+// releases the shared-memory slot, its lo slot and the TMEM A slot together.
 struct WtBars {
-  uint64_t hi_full[WT_HI_SLOTS], hi_free[WT_HI_SLOTS];
-  uint64_t a_full[WT_HI_SLOTS];
-  uint64_t x_full[WT_LO_SLOTS], lo_free[WT_LO_SLOTS];
+  uint64_t landed[WT_HI_SLOTS];   // TMA bytes of the slab (waited for by fill warps and stagers)
+  uint64_t ready[WT_HI_SLOTS];    // A slot in tensor memory written (128 threads) + lo of Q written (192 threads)
+  uint64_t free_[WT_HI_SLOTS];    // the UMMAs of the slab have completed
   uint64_t acc_full[2], acc_free[2];
 };
 
@@ -57,11 +60,10 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   if (tid == 32) {
     for (int i = 0; i < WT_HI_SLOTS; ++i) {
-      mbar_init(&bars.hi_full[i], 1);
-      mbar_init(&bars.hi_free[i], 1);
-      mbar_init(&bars.a_full[i], 128);
+      mbar_init(&bars.landed[i], 1);
+      mbar_init(&bars.ready[i], 128 + WT_CONV_THREADS);
+      mbar_init(&bars.free_[i], 1);
     }
-    for (int i = 0; i < WT_LO_SLOTS; ++i) { mbar_init(&bars.x_full[i], WT_CONV_THREADS); mbar_init(&bars.lo_free[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&bars.acc_full[i], 1); mbar_init(&bars.acc_free[i], 128); }
     fence_mbar_init();
   }
@@ -88,14 +90,15 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
     const int ct = tid - WT_CONV_WARP0 * 32;
     constexpr int NIT = (WT_Q_BYTES / 16 + WT_CONV_THREADS - 1) / WT_CONV_THREADS;
     RingPos<WT_HI_SLOTS> hr;
-    RingPos<WT_LO_SLOTS> lr;
     for (int k = 0; k < my_items; ++k) {
       int group, nslab;
       long row0;
       item_setup(k, group, row0, nslab);
       const int nchunks = wg_q_bytes(p.g[group]) / 16;
       for (int s = 0; s < nslab; ++s) {
-        mbar_wait(&bars.hi_full[hr.idx], hr.phase);
+        // a landed box also says that the previous round's UMMAs on this slot (and its lo slot) are done: the loader
+        // refilled it only after `free_`
+        mbar_wait(&bars.landed[hr.idx], hr.phase);
         const float4* src = reinterpret_cast<const float4*>(sHi + (size_t)hr.idx * WT_HI_SLAB + WT_P_BYTES);
         float4 r[NIT];
         if (!p.single) {
@@ -105,8 +108,7 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
             if (q < nchunks) r[i] = src[q];
           }
         }
-        mbar_wait(&bars.lo_free[lr.idx], lr.phase ^ 1u);
-        float4* lo = reinterpret_cast<float4*>(sLo + (size_t)lr.idx * WT_Q_BYTES);
+        float4* lo = reinterpret_cast<float4*>(sLo + (size_t)hr.idx * WT_Q_BYTES);
         if (!p.single) {
 #pragma unroll
           for (int i = 0; i < NIT; ++i) {
@@ -115,9 +117,8 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
           }
         }
         fence_async_smem();
-        mbar_arrive(&bars.x_full[lr.idx]);
+        mbar_arrive(&bars.ready[hr.idx]);
         hr.advance();
-        lr.advance();
       }
     }
   } else if (warp == WT_LOAD_WARP) {
@@ -130,9 +131,9 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
       const int nqb = wg_q_blocks(p.g[group]);
       const uint32_t bytes = (uint32_t)(WT_P_BYTES + wg_q_bytes(p.g[group]));
       for (int s = 0; s < nslab; ++s) {
-        mbar_wait(&bars.hi_free[hr.idx], hr.phase ^ 1u);
+        mbar_wait(&bars.free_[hr.idx], hr.phase ^ 1u);
         if (elect_one()) {
-          uint64_t* bar = &bars.hi_full[hr.idx];
+          uint64_t* bar = &bars.landed[hr.idx];
           mbar_arrive_expect_tx(bar, bytes);
           unsigned char* dst = sHi + (size_t)hr.idx * WT_HI_SLAB;
           const int row = (int)row0 + s * 16;
@@ -154,7 +155,6 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
     const uint32_t lo0 = ((smem_u32(sLo) & 0x3FFFFu) >> 4) | lbo;
     constexpr uint32_t HSLAB = WT_HI_SLAB >> 4, LSLAB = WT_Q_BYTES >> 4, KS = 1024u >> 4;
     RingPos<WT_HI_SLOTS> hr;
-    RingPos<WT_LO_SLOTS> lr;
     for (int k = 0; k < my_items; ++k) {
       int group, nslab;
       long row0;
@@ -169,12 +169,11 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
       tc_fence_after();
       const uint32_t acc = tmem + (uint32_t)buf * 128u;
       for (int s = 0; s < nslab; ++s) {
-        mbar_wait(&bars.x_full[lr.idx], lr.phase);        // lo of Q written (and its hi landed)
-        mbar_wait(&bars.a_full[hr.idx], hr.phase);        // hi / lo of P in tensor memory
+        mbar_wait(&bars.ready[hr.idx], hr.phase);         // hi / lo of P in tensor memory, lo of Q written (its hi landed)
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_hi = tmem + WT_A_BASE + (uint32_t)hr.idx * 32u, a_lo = a_hi + 16u;
-          const uint32_t qh = hi0 + (uint32_t)hr.idx * HSLAB + q_fix, ql = lo0 + (uint32_t)lr.idx * LSLAB + q_fix;
+          const uint32_t qh = hi0 + (uint32_t)hr.idx * HSLAB + q_fix, ql = lo0 + (uint32_t)hr.idx * LSLAB + q_fix;
           const uint32_t first = s == 0 ? 0u : 1u;
           if (!p.single) {
             umma_tf32_ts(acc, a_lo, desc64(q_hi, qh), idesc, first);  // small terms first
@@ -187,13 +186,11 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
             umma_tf32_ts(acc, a_hi, desc64(q_hi, qh), idesc, first);
             umma_tf32_ts(acc, a_hi + 8u, desc64(q_hi, qh + q_ks), idesc, 1u);
           }
-          umma_commit(&bars.lo_free[lr.idx]);
-          umma_commit(&bars.hi_free[hr.idx]);             // frees the shared-memory slot AND the TMEM A slot of this index
+          umma_commit(&bars.free_[hr.idx]);               // shared-memory slot, its lo slot and the TMEM A slot of this index
           if (s == nslab - 1) umma_commit(&bars.acc_full[buf]);
         }
         __syncwarp();
         hr.advance();
-        lr.advance();
       }
     }
   } else if (warp >= WT_FILL_WARP0) {
@@ -209,9 +206,9 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
       long row0;
       item_setup(k, group, row0, nslab);
       for (int s = 0; s < nslab; ++s) {
-        // the loader refills slot i only after the UMMAs that read A slot i have completed (hi_free), so a landed box
+        // the loader refills slot i only after the UMMAs that read A slot i have completed (free_), so a landed box
         // also says that the TMEM columns of this slot are free
-        mbar_wait(&bars.hi_full[hr.idx], hr.phase);
+        mbar_wait(&bars.landed[hr.idx], hr.phase);
         const float4* rowp = reinterpret_cast<const float4*>(sHi + (size_t)hr.idx * WT_HI_SLAB + m * 64);
         float v[16];
 #pragma unroll
@@ -230,7 +227,7 @@ __global__ void __launch_bounds__(WT_THREADS, 1) tc_wgrad_ts_kernel(const __grid
         }
         tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(&bars.a_full[hr.idx]);
+        mbar_arrive(&bars.ready[hr.idx]);
         hr.advance();
       }
     }
