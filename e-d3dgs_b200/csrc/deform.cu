@@ -883,6 +883,20 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
       gr.nseg = 1;
       gr.seg[0] = WgSegment{g->feat_w[0] + temb, 1, ld0, 0, gemb, 0, 128};
     }
+#ifdef ED3DGS_TIMING_KNOBS
+    {  // timing only (results are wrong): ED3DGS_WG_SKIP bit 0 drops the dW1 groups, bit 1 the dW2 groups, bit 2 dW0
+      static const int skip = [] { const char* e = getenv("ED3DGS_WG_SKIP"); return e ? atoi(e) : 0; }();
+      if (skip) {
+        WgArgs b = a;
+        b.ngroups = 0;
+        for (int i = 0; i < a.ngroups; ++i) {
+          const int kind = a.g[i].P == wk.hT[s] ? 1 : (a.g[i].P == wk.dhT ? 4 : 2);
+          if (!(skip & kind)) b.g[b.ngroups++] = a.g[i];
+        }
+        a = b;
+      }
+    }
+#endif
     TC_TRY(tc_wgrad_launch(a, stream, wg_ts));
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
