@@ -469,9 +469,10 @@ def run_ours(args, rank, local, world):
     hyper = scene.hyper
     # gradients: set to None before every step like the reference's zero_grad(set_to_none=True) (train.py:448); for N > 1
     # all of them are reduced in one NCCL group (ed3dgs_b200/dp.py: GradSync)
-    # N > 1: the 59 of 91 per-Gaussian gradient floats that are final before the network's backward starts are reduced
-    # next to it (dp.OverlapSync; BENCH_OVERLAP=0 switches back to one exchange at the end of the step)
-    overlap = world > 1 and os.environ.get("BENCH_OVERLAP", "1") != "0"
+    # N > 1, BENCH_OVERLAP=1: the 59 of 91 per-Gaussian gradient floats that are final before the network's backward starts
+    # are reduced next to it (dp.OverlapSync). Off by default: on this pool the NCCL all-reduce needs far more CTAs than the
+    # persistent MLP kernels can spare (8 GPUs, 525-528 views/s with the overlap, 539 without)
+    overlap = world > 1 and os.environ.get("BENCH_OVERLAP", "0") != "0"
     sm_reserve = int(os.environ.get("BENCH_SM_RESERVE", "8"))
     arena = dp.OverlapSync(list(scene.parameters()),
                            early=[scene._xyz, scene._features_dc, scene._features_rest, scene._scaling, scene._rotation,
@@ -940,7 +941,7 @@ def main():
         rank = int(os.environ.get("RANK", "0"))
         run_reference_arm(args, rank, int(os.environ.get("WORLD_SIZE", "1")))
         return
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("BENCH_OVERLAP", "1") != "0":
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("BENCH_OVERLAP", "0") != "0":
         # the collective that runs next to the MLP backward gets exactly the SMs that backward leaves free
         os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("BENCH_SM_RESERVE", "8"))
     rank, local, world = dp.init_from_env("nccl")

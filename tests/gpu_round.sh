@@ -25,11 +25,11 @@ if [ "$want_ncu" = ncu ]; then
   BENCH_SUSTAINED_S=0 BENCH_CLOCKS=off timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv \
     --log-file $out/launches_bench.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-gpu-reference > $out/ncu_bench.log 2>&1
   echo "ncu launch list exit $?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'fused_fwd_kernel|fused_bwd_kernel|tc_wgrad_kernel|tc_rows_kernel' \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'fused_fwd_kernel|fused_bwd_kernel|tc_wgrad|tc_rows_kernel' \
     -s 10 -c 14 -o $out/mlp -f python tests/profile_deform.py 1000000 3 > $out/ncu_mlp.log 2>&1
   echo "ncu mlp exit $?"
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'blend_bwd|render_fwd|gaussian_bwd|preprocess_fwd|onesweep|radix|emit_keys' \
-    -s 30 -c 30 -o $out/raster -f python tests/profile_raster.py mine C3 0.3 > $out/ncu_raster.log 2>&1
+    -c 40 -o $out/raster -f python tests/profile_raster.py mine C3 0.3 > $out/ncu_raster.log 2>&1
   echo "ncu raster exit $?"
 fi
 ls -la $out

@@ -120,7 +120,8 @@ if traffic and os.path.exists(bj):
     per_step = {}
     for k, t in traffic.items():
         base = re.sub(r"<.*", "", k)
-        group = {"radix_onesweep": "radix_sort_pairs", "radix_hist_all": "radix_sort_pairs"}.get(base, base)
+        group = {"radix_onesweep": "radix_sort_pairs", "radix_hist_all": "radix_sort_pairs",
+                 "tc_wgrad_ts_kernel": "tc_wgrad_kernel"}.get(base, base)
         if group in d["roofline_all"]:
             nl = d["roofline_all"][group]["launches_per_step"]
             if group == "radix_sort_pairs":
