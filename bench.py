@@ -469,16 +469,34 @@ def run_ours(args, rank, local, world):
     hyper = scene.hyper
     # gradients: set to None before every step like the reference's zero_grad(set_to_none=True) (train.py:448); for N > 1
     # all of them are reduced in one NCCL group (ed3dgs_b200/dp.py: GradSync)
-    # N > 1, BENCH_OVERLAP=1: the 59 of 91 per-Gaussian gradient floats that are final before the network's backward starts
-    # are reduced next to it (dp.OverlapSync). Off by default: on this pool the NCCL all-reduce needs far more CTAs than the
-    # persistent MLP kernels can spare (8 GPUs, 525-528 views/s with the overlap, 539 without)
-    overlap = world > 1 and os.environ.get("BENCH_OVERLAP", "0") != "0"
-    sm_reserve = int(os.environ.get("BENCH_SM_RESERVE", "8"))
+    # N > 1: the 59 of 91 per-Gaussian gradient floats that are final before the network's backward starts are exchanged
+    # next to it (dp.OverlapSync). Default transport "ce": peer-to-peer copy-engine transfers between symmetric-memory
+    # buffers (8 GPUs, C3: 631 views/s against 591 with one NCCL exchange at the end of the step;
+    # NCCL next to the backward is slower than either, it needs far more CTAs than the persistent MLP kernels can spare).
+    # BENCH_OVERLAP = ce | nccl | 0. If symmetric memory cannot be set up the bench falls back to the single exchange.
+    ov_mode = os.environ.get("BENCH_OVERLAP", "ce")
+    ov_mode = "nccl" if ov_mode == "1" else ov_mode
+    overlap = world > 1 and ov_mode != "0"
+    transport = "ce" if ov_mode == "ce" else "nccl"
+    sm_reserve = int(os.environ.get("BENCH_SM_RESERVE", "8" if transport == "nccl" else "2"))
     arena = dp.OverlapSync(list(scene.parameters()),
                            early=[scene._xyz, scene._features_dc, scene._features_rest, scene._scaling, scene._rotation,
-                                  scene._opacity], sm_reserve=sm_reserve)
+                                  scene._opacity], sm_reserve=sm_reserve, transport=transport,
+                           embedding=scene._embedding if os.environ.get("BENCH_CE_EMB", "0") != "0" else None)
+    overlap_note = None
     if overlap:
-        overlap = arena.enable()
+        try:
+            overlap = arena.enable()
+        except Exception as ex:  # noqa: BLE001   (no symmetric memory on this box: one NCCL exchange at the end of the step)
+            overlap_note = f"{transport} exchange unavailable ({type(ex).__name__}: {ex}); single NCCL exchange"
+            arena.transport, arena.ce, arena.active = "nccl", None, False
+            overlap = False
+        if world > 1:   # every rank must have made the same choice
+            flag = torch.tensor([1 if overlap else 0], device=device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if overlap and int(flag) == 0:
+                arena.disable()
+                overlap, overlap_note = False, "a rank could not set the overlapped exchange up; single NCCL exchange"
     pipe = NS(debug=False)
     bg = torch.zeros(3, device=device)
     H, W = cfg["H"], cfg["W"]
@@ -651,7 +669,8 @@ def run_ours(args, rank, local, world):
         dist.all_reduce(mt, op=dist.ReduceOp.MIN)
         multi = {"allreduce_ms": float(mt_max[0]), "compute_only_ms_per_step_max_rank": float(mt_max[1]),
                  "compute_only_ms_per_step_min_rank": float(mt[1]),
-                 "overlap": bool(overlap), "sm_reserve": sm_reserve if overlap else 0,
+                 "overlap": (transport if overlap else False), "overlap_note": overlap_note,
+                 "sm_reserve": sm_reserve if overlap else 0,
                  "nccl_max_ctas": os.environ.get("NCCL_MAX_CTAS"),
                  "what": "allreduce_ms = the whole exchange alone (both buckets back to back); compute_only = the same "
                          "steps without any collective; with overlap on, bucket A (xyz, f_dc, f_rest, opacity, scaling, "
@@ -941,7 +960,7 @@ def main():
         rank = int(os.environ.get("RANK", "0"))
         run_reference_arm(args, rank, int(os.environ.get("WORLD_SIZE", "1")))
         return
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("BENCH_OVERLAP", "0") != "0":
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("BENCH_OVERLAP", "ce") in ("1", "nccl"):
         # the collective that runs next to the MLP backward gets exactly the SMs that backward leaves free
         os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("BENCH_SM_RESERVE", "8"))
     rank, local, world = dp.init_from_env("nccl")

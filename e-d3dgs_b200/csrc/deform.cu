@@ -362,6 +362,14 @@ static int check_weights(const ed3dgs_deform_weights* w) {
     }                                                                                        \
   } while (0)
 
+// Event recorded right after the LAST writer of d_embedding in ed3dgs_deform_backward (ed3dgs_deform_set_emb_ready_event):
+// the embedding gradient is final one weight-gradient launch (1.2 ms at 1 M Gaussians) before the call's last kernel, and
+// a multi-GPU caller starts its exchange from there.
+static void* g_emb_ready_event = nullptr;
+static inline void record_emb_ready(bool last_stage, cudaStream_t stream) {
+  if (last_stage && g_emb_ready_event) cudaEventRecord(static_cast<cudaEvent_t>(g_emb_ready_event), stream);
+}
+
 // precision of the call in flight on this thread (ed3dgs_deform_weights::precision): 0 = 3xTF32, 1 = single tf32 pass
 static thread_local int g_single = 0;
 
@@ -613,7 +621,7 @@ struct WgBatcher {
 
 static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
                           const float* emb, const float* tau, const float* G, const float* colsum, DeformWork& wk,
-                          float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
+                          float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream, bool last_stage) {
   const int W = w->W, D = w->depth, temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
   const int nch = (W + 127) / 128;
@@ -752,6 +760,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     a.accumulate = accumulate_emb;
     a.b[0] = TcBatch{dh, w->feat_w[0] + temb, d_emb, nullptr, nullptr, nullptr, gemb, 0, gemb, 0, 0, 1.f};
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
+    record_emb_ready(last_stage, stream);
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, W, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
@@ -767,7 +776,7 @@ static long long* g_trace = nullptr;
 static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_deform_grads* g, int s, int N,
                                 const float* emb, const float* tau, const float* const d_out[5],
                                 const float* const d_sub[5], int use_sub, const float coef[5], DeformWork& wk,
-                                float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream) {
+                                float* d_emb, int accumulate_emb, float* d_tau, cudaStream_t stream, bool last_stage) {
   const int temb = w->temb_dim, gemb = w->gemb_dim;
   const long ld0 = temb + gemb;
   int act[5];
@@ -842,6 +851,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
     fused_bwd_kernel<<<ntiles < sms ? ntiles : sms, FB_THREADS, FM_BWD_SMEM, stream>>>(ba);
   }
   TC_TRY(cudaGetLastError());
+  record_emb_ready(last_stage, stream);   // d_emb is complete: the weight gradients below do not touch it
 
   if (g) {
     // every weight gradient of the stage in one launch; the groups of a slice of Gaussians are adjacent work items, so
@@ -935,6 +945,8 @@ int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, in
   if (e != cudaSuccess) { set_error("temporal_embed_backward: %s", cudaGetErrorString(e)); return ED3DGS_ERR_CUDA; }
   return ED3DGS_OK;
 }
+
+void ed3dgs_deform_set_emb_ready_event(void* cuda_event) { g_emb_ready_event = cuda_event; }
 
 int ed3dgs_deform_set_sm_reserve(int n_sms) {
   const int prev = tc_sm_reserve();
@@ -1030,13 +1042,13 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
     int accumulate = 0;
     if (fine) {
       if ((rc = stage_backward_fused(fine, g_fine, 1, N, embedding, tau_f, gp.d_out, gp.d_sub, 0, coef, wk, d_embedding,
-                                     accumulate, d_tau_f, stream)))
+                                     accumulate, d_tau_f, stream, coarse == nullptr)))
         return rc;
       accumulate = 1;
     }
     if (coarse) {
       if ((rc = stage_backward_fused(coarse, g_coarse, 0, N, embedding, tau_c, gp.d_out, gp.d_sub, any_sub ? 1 : 0, coef,
-                                     wk, d_embedding, accumulate, d_tau_c, stream)))
+                                     wk, d_embedding, accumulate, d_tau_c, stream, true)))
         return rc;
     }
   } else {
@@ -1056,13 +1068,13 @@ int ed3dgs_deform_backward(const ed3dgs_deform_weights* coarse, const ed3dgs_def
   int accumulate = 0;
   if (fine) {
     if ((rc = stage_backward(fine, g_fine, 1, N, embedding, tau_f, wk.G[1], wk.colsum[1], wk, d_embedding, accumulate,
-                             d_tau_f, stream)))
+                             d_tau_f, stream, coarse == nullptr)))
       return rc;
     accumulate = 1;
   }
   if (coarse) {
     if ((rc = stage_backward(coarse, g_coarse, 0, N, embedding, tau_c, Gc, colc, wk, d_embedding, accumulate, d_tau_c,
-                             stream)))
+                             stream, true)))
       return rc;
   }
   }

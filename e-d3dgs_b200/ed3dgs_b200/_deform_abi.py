@@ -31,6 +31,8 @@ def declare(lib):
     lib.ed3dgs_temporal_embed_backward.argtypes = [P, c_int, c_int, c_int, P, P, P, P, c_void_p]
     lib.ed3dgs_deform_workspace_bytes.restype = c_size_t
     lib.ed3dgs_deform_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.ed3dgs_deform_set_emb_ready_event.restype = None
+    lib.ed3dgs_deform_set_emb_ready_event.argtypes = [c_void_p]
     lib.ed3dgs_deform_set_sm_reserve.restype = c_int
     lib.ed3dgs_deform_set_sm_reserve.argtypes = [c_int]
     lib.ed3dgs_deform_forward.restype = c_int

@@ -18,13 +18,15 @@ from . import _lib
 # it, so that the all-reduce of the Gaussian-parameter gradients (which are this node's *upstream* gradients and hence
 # final before it starts) can run on NCCL's stream at the same time. Everything the side stream still reads or writes
 # is parked in `keep` until dp.OverlapSync has made the main stream wait for it.
-_overlap = {"stream": None, "sm_reserve": 0, "keep": []}
+_overlap = {"stream": None, "sm_reserve": 0, "clone": True, "keep": []}
 
 
-def set_backward_stream(stream, sm_reserve=0):
-    """stream = None switches the overlap off. sm_reserve: SMs the persistent backward kernels leave to NCCL."""
+def set_backward_stream(stream, sm_reserve=0, clone=True):
+    """stream = None switches the overlap off. sm_reserve: SMs the persistent backward kernels leave to the exchange.
+    clone: the kernels read copies of the pass-through gradients (needed when the caller reduces them in place)."""
     _overlap["stream"] = stream
     _overlap["sm_reserve"] = int(sm_reserve) if stream is not None else 0
+    _overlap["clone"] = bool(clone)
     _overlap["keep"].clear()
 
 
@@ -182,8 +184,9 @@ class _DeformFunction(torch.autograd.Function):
         k_out, k_sub = d_out, d_sub
         if side is not None:
             # the caller all-reduces the pass-through gradients in place while these kernels run: they read copies
-            k_out = [None if x is None else x.clone() for x in d_out]
-            k_sub = [None if x is None else x.clone() for x in d_sub]
+            if _overlap["clone"]:
+                k_out = [None if x is None else x.clone() for x in d_out]
+                k_sub = [None if x is None else x.clone() for x in d_sub]
             side.wait_stream(torch.cuda.current_stream(dev))
             if _overlap["sm_reserve"]:
                 lib.ed3dgs_deform_set_sm_reserve(_overlap["sm_reserve"])

@@ -123,6 +123,75 @@ class GradSync:
         return ts
 
 
+class CopyEngineExchange:
+    """Mean over ranks of a list of tensors whose TRANSFERS use no SM: a reduce-scatter and an all-gather made of
+    peer-to-peer `cudaMemcpyAsync` copies (NVLink copy engines) between symmetric-memory buffers, with one small reduction
+    kernel in between. It is what can run next to persistent kernels that own every SM: NCCL's
+    all-reduce needs tens of CTAs to reach its bandwidth.
+
+        pack      the tensors, back to back, into this rank's symmetric buffer `buf`                      (local copies)
+        barrier   every rank's buffer is packed
+        pull      chunk `rank` of every peer's buffer into `stage[peer]`                                  (P2P copies)
+        reduce    buf[chunk rank] = mean over peers of stage            (nobody pulls that chunk of MY buffer: no barrier)
+        barrier   every rank's reduced chunk is in place, all pulls of the first phase have completed
+        pull      every peer's reduced chunk into the same chunk of `buf`                                 (P2P copies)
+        barrier   nobody repacks its buffer while a peer still reads it
+
+    Everything is issued on `self.stream`; the results are views of `buf` (valid until the next call)."""
+
+    def __init__(self, max_floats, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.align = self.world * 64                       # chunks start on 256-byte boundaries
+        cap = (int(max_floats) + self.align - 1) // self.align * self.align
+        self.cap = cap
+        self.buf = symm.empty(cap, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.peers = [self.hdl.get_buffer(r, (cap,), torch.float32) for r in range(self.world)]
+        self.stage = torch.empty(self.world, cap // self.world, dtype=torch.float32, device=device)
+        self.stream = torch.cuda.Stream(device=device)
+        self.timeout_ms = 30000   # a rank that never arrives makes the barrier kernel trap instead of hanging the box
+
+    def allreduce_mean(self, tensors):
+        total = sum(t.numel() for t in tensors)
+        used = (total + self.align - 1) // self.align * self.align
+        if used > self.cap:
+            raise ValueError(f"CopyEngineExchange: {total} floats do not fit the symmetric buffer of {self.cap}")
+        chunk = used // self.world
+        rank, world, buf = self.rank, self.world, self.buf
+        self.stream.wait_stream(torch.cuda.current_stream(buf.device))
+        outs = []
+        with torch.cuda.stream(self.stream):
+            off = 0
+            for t in tensors:
+                n = t.numel()
+                buf[off:off + n].copy_(t.detach().reshape(-1))
+                outs.append(buf[off:off + n].view(t.shape))
+                off += n
+            if used > total:
+                buf[total:used].zero_()
+            self.hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+            mine = slice(rank * chunk, (rank + 1) * chunk)
+            for step in range(world):
+                r = (rank - step) % world
+                self.stage[r, :chunk].copy_(self.peers[r][mine])
+            torch.mean(self.stage[:, :chunk], dim=0, out=buf[mine])
+            self.hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+            for step in range(1, world):
+                r = (rank - step) % world
+                theirs = slice(r * chunk, (r + 1) * chunk)
+                buf[theirs].copy_(self.peers[r][theirs])
+            self.hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+        return outs
+
+
+def deformation_ran():
+    """True when a deformation backward of this step went to the side stream (its tensors are parked until the join)."""
+    from . import deformation
+    return len(deformation._overlap["keep"]) > 0
+
+
 class OverlapSync(GradSync):
     """GradSync with the exchange split in two and the first half hidden behind the deformation network's backward.
 
@@ -134,13 +203,24 @@ class OverlapSync(GradSync):
     collective runs next to the MLP backward --, (2) makes the main stream wait for the side stream, (3) reduces bucket B.
     Host logic only: without CUDA (gloo tests) or with one rank it degrades to GradSync."""
 
-    def __init__(self, params, early, sm_reserve=8):
+    def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None):
+        """transport: "nccl" = bucket A through NCCL next to the backward (needs `sm_reserve` SMs and a matching
+        NCCL_MAX_CTAS); "ce" = bucket A through CopyEngineExchange (no SMs for the transfers).
+        embedding (transport "ce" only): the per-Gaussian embedding parameter. Its gradient is final after the chain kernel
+        of the network's last stage, one weight-gradient launch before the backward ends; the library records an event
+        there (ed3dgs_deform_set_emb_ready_event) and a second exchange starts from it, so that only the network's own
+        parameters (a few MB) are left for the end of the step."""
         super().__init__(params)
         early_ids = {id(p) for p in early}
         self.early = [p for p in self.params if id(p) in early_ids]
-        self.late = [p for p in self.params if id(p) not in early_ids]
+        self.embedding = embedding if (embedding is not None and transport == "ce") else None
+        self.late = [p for p in self.params if id(p) not in early_ids and p is not self.embedding]
+        self.ce_emb = None
+        self.emb_event = None
         self.sm_reserve = sm_reserve
+        self.transport = transport
         self.side = None
+        self.ce = None
         self.active = False
 
     def enable(self):
@@ -148,8 +228,19 @@ class OverlapSync(GradSync):
         from . import deformation
         multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
         if multi and torch.cuda.is_available() and self.params and self.params[0].is_cuda:
-            self.side = torch.cuda.Stream(device=self.params[0].device)
-            deformation.set_backward_stream(self.side, self.sm_reserve)
+            dev = self.params[0].device
+            if self.transport == "ce":
+                self.ce = CopyEngineExchange(sum(p.numel() for p in self.early) + 64 * len(self.early), dev)
+                if self.embedding is not None:
+                    from . import _lib
+                    import ctypes
+                    self.ce_emb = CopyEngineExchange(self.embedding.numel(), dev)
+                    self.emb_event = torch.cuda.Event()
+                    self.emb_event.record(torch.cuda.current_stream(dev))      # creates the cudaEvent_t
+                    _lib.lib().ed3dgs_deform_set_emb_ready_event(ctypes.c_void_p(self.emb_event.cuda_event))
+            self.side = torch.cuda.Stream(device=dev)
+            # with the copy-engine transport nothing reduces the pass-through gradients in place: no copies needed
+            deformation.set_backward_stream(self.side, self.sm_reserve, clone=self.ce is None)
             self.active = True
         return self.active
 
@@ -157,6 +248,9 @@ class OverlapSync(GradSync):
         from . import deformation
         self.join()
         deformation.set_backward_stream(None)
+        if self.emb_event is not None:
+            from . import _lib
+            _lib.lib().ed3dgs_deform_set_emb_ready_event(None)
         self.side, self.active = None, False
 
     def join(self):
@@ -178,6 +272,28 @@ class OverlapSync(GradSync):
         """collective=False: only the stream join (bench's 'steps without the collective' breakdown)."""
         if not self.active:
             return GradSync.allreduce(self, scale) if collective else self.tensors()
+        if self.ce is not None and collective:
+            world = dist.get_world_size()
+            if scale is None or abs(scale * world - 1.0) > 1e-12:
+                raise ValueError("OverlapSync(transport='ce') computes the mean over ranks: pass scale = 1 / world")
+            ps = [p for p in self.early if p.grad is not None]
+            outs = self.ce.allreduce_mean([p.grad for p in ps])       # on the exchange's own stream
+            late = self.late
+            if self.ce_emb is not None and self.embedding.grad is not None and deformation_ran():
+                # starts when the library's event fires (after the last stage's chain kernel), not at the end of the backward
+                self.ce_emb.stream.wait_event(self.emb_event)
+                outs += self.ce_emb.allreduce_mean([self.embedding.grad])
+                ps = ps + [self.embedding]
+            elif self.embedding is not None:
+                late = late + [self.embedding]
+            self.join()
+            main = torch.cuda.current_stream(self.ce.stream.device)
+            main.wait_stream(self.ce.stream)
+            if self.ce_emb is not None:
+                main.wait_stream(self.ce_emb.stream)
+            for p, o in zip(ps, outs):
+                p.grad = o
+            return outs + self._reduce(late, scale, collective)
         a = self._reduce(self.early, scale, collective)
         self.join()
         b = self._reduce(self.late, scale, collective)

@@ -77,6 +77,14 @@ size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N);
 int ed3dgs_deform_set_sm_reserve(int n_sms);
 
 /*
+ * `cuda_event` (a cudaEvent_t, or NULL to switch it off) is recorded on the call's stream inside every later
+ * ed3dgs_deform_backward right after the last kernel that writes d_embedding, i.e. before the weight-gradient launch of
+ * the last stage: a multi-GPU caller makes its exchange stream wait for it and reduces the embedding gradient while that
+ * launch runs. Process-wide.
+ */
+void ed3dgs_deform_set_emb_ready_event(void* cuda_event);
+
+/*
  * Forward of both stages. coarse / fine may be NULL (no_coarse_deform / no_fine_deform).
  *   in[h], sub[h], out[h]: [N, k_h] for h = pos, scales, rotations, opacity, rgb.
  *   sub = in + delta_coarse * coef   (the reference's *_sub tuple), out = sub + delta_fine * coef.

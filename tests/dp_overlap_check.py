@@ -1,4 +1,4 @@
-"""torchrun --nproc-per-node 2 tests/dp_overlap_check.py [C2|C3]
+"""torchrun --nproc-per-node 2 tests/dp_overlap_check.py [C2|C3] [nccl|ce]
 Multi-GPU check of dp.OverlapSync on real devices (NCCL): the gradients every rank ends a step with must equal the ones
 the single-exchange GradSync produces (same views, same seeds), with the deformation backward on the side stream, the
 SM reserve on and bucket A reduced next to it. Prints one JSON line on rank 0."""
@@ -49,7 +49,9 @@ def main():
     plain = dp.GradSync(params)
     ref = run(plain, 3)
     ref2 = run(plain, 3)   # the same thing again: what fp32 atomics in arrival order change from run to run
-    over = dp.OverlapSync(params, early=early, sm_reserve=int(os.environ.get("BENCH_SM_RESERVE", "8")))
+    transport = sys.argv[2] if len(sys.argv) > 2 else "nccl"
+    over = dp.OverlapSync(params, early=early, sm_reserve=int(os.environ.get("BENCH_SM_RESERVE", "8")), transport=transport,
+                          embedding=scene._embedding)
     assert over.enable()
     got = run(over, 3)
     worst, per, bad = 0.0, {}, []
@@ -93,7 +95,7 @@ def main():
     t_plain = timed(plain)
     ok = not bad and spread <= 1e-9
     if rank == 0:
-        print(json.dumps({"workload": name, "world": world, "max_rel_diff_vs_single_exchange": worst,
+        print(json.dumps({"workload": name, "world": world, "transport": transport, "max_rel_diff_vs_single_exchange": worst,
                           "over_noise_bound": bad, "rank_spread": spread, "ms_per_step_overlap": t_over, "ms_per_step_single_exchange": t_plain,
                           "nccl_max_ctas": os.environ.get("NCCL_MAX_CTAS"), "ok": ok}))
     dist.destroy_process_group()

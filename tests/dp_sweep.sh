@@ -1,6 +1,7 @@
 #!/bin/bash
-# Multi-GPU sweep on one box (run through gpurun --gpus 8): C3 with / without the overlapped exchange at several NCCL CTA
-# caps, C4 at 2/4/8 ranks, C5 at 8 ranks. One bench line per run under gpurun_out/<tag>/.
+# Multi-GPU sweep on one box (run through gpurun --gpus 8): C3 / C4 / C5 with the single NCCL exchange at the end of the
+# step and with the copy-engine exchange of bucket A next to the network's backward. One bench line per run under
+# gpurun_out/<tag>/.   usage: bash tests/dp_sweep.sh <tag> [full|quick]
 tag=${1:-dp}; out=gpurun_out/$tag; mkdir -p $out
 run() {  # name nproc workload env...
   name=$1; np=$2; wl=$3; shift 3
@@ -17,20 +18,14 @@ except Exception as ex:
     print("$name failed", ex)
 PY
 }
-n=${2:-8}
-run c3_${n}gpu_single $n C3 BENCH_OVERLAP=0
-run c3_${n}gpu_overlap_r4 $n C3 BENCH_OVERLAP=1 BENCH_SM_RESERVE=4 NCCL_MAX_CTAS=4
-run c3_${n}gpu_overlap_r8 $n C3 BENCH_OVERLAP=1 BENCH_SM_RESERVE=8 NCCL_MAX_CTAS=8
-run c3_${n}gpu_overlap_r16 $n C3 BENCH_OVERLAP=1 BENCH_SM_RESERVE=16 NCCL_MAX_CTAS=16
-run c3_${n}gpu_overlap_r8_free $n C3 BENCH_OVERLAP=1 BENCH_SM_RESERVE=8 NCCL_MAX_CTAS=32
-if [ "$n" = 8 ]; then
-  run c3_4gpu_single 4 C3 BENCH_OVERLAP=0
-  run c3_2gpu_single 2 C3 BENCH_OVERLAP=0
-  run c4_2gpu_single 2 C4 BENCH_OVERLAP=0
-  run c4_4gpu_single 4 C4 BENCH_OVERLAP=0
-  run c4_8gpu_single 8 C4 BENCH_OVERLAP=0
-  run c4_8gpu_overlap_r8 8 C4 BENCH_OVERLAP=1 BENCH_SM_RESERVE=8 NCCL_MAX_CTAS=8
-  run c5_8gpu_single 8 C5 BENCH_OVERLAP=0
-  run c5_8gpu_overlap_r8 8 C5 BENCH_OVERLAP=1 BENCH_SM_RESERVE=8 NCCL_MAX_CTAS=8
-fi
-ls $out
+run c3_8gpu_single 8 C3 BENCH_OVERLAP=0
+run c3_8gpu_ce 8 C3 BENCH_OVERLAP=ce
+run c3_4gpu_ce 4 C3 BENCH_OVERLAP=ce
+run c3_4gpu_single 4 C3 BENCH_OVERLAP=0
+run c4_8gpu_ce 8 C4 BENCH_OVERLAP=ce
+run c4_8gpu_single 8 C4 BENCH_OVERLAP=0
+run c4_4gpu_ce 4 C4 BENCH_OVERLAP=ce
+run c4_2gpu_ce 2 C4 BENCH_OVERLAP=ce
+run c5_8gpu_ce 8 C5 BENCH_OVERLAP=ce
+run c5_8gpu_single 8 C5 BENCH_OVERLAP=0
+ls $out | wc -l

@@ -32,4 +32,8 @@ if [ "$want_ncu" = ncu ]; then
     -c 40 -o $out/raster -f python tests/profile_raster.py mine C3 0.3 > $out/ncu_raster.log 2>&1
   echo "ncu raster exit $?"
 fi
+for wl in C4 C5; do
+  BENCH_SUSTAINED_S=0 timeout 400 python bench.py --workload $wl --steps 20 --warmup 3 --no-cpu-baseline > $out/bench_${wl}_1gpu.json 2> $out/bench_${wl}_1gpu.err
+  echo "bench $wl exit $?"
+done
 ls -la $out

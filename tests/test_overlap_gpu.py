@@ -57,3 +57,44 @@ def test_backward_on_side_stream_leaves_results_unchanged(shape):
     finally:
         deformation.set_backward_stream(None)
     _compare(ref, got)
+
+
+def test_copy_engine_exchange_single_rank():
+    """dp.CopyEngineExchange on a one-rank NCCL group (the driver's GPU box has one device; tests/dp_overlap_check.py and
+    tests/dp_sweep.sh run it on 2-8 ranks): pack, barriers, reduction kernel and the views handed back. Skipped where
+    symmetric memory cannot be set up."""
+    import os
+    import socket
+    import torch.distributed as dist
+    from ed3dgs_b200 import dp
+    if dist.is_initialized():
+        pytest.skip("a process group already exists in this process")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    keys = ("MASTER_ADDR", "MASTER_PORT", "RANK", "WORLD_SIZE", "LOCAL_RANK")
+    saved = {k: os.environ.get(k) for k in keys}
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    dist.init_process_group("nccl", rank=0, world_size=1)
+    try:
+        try:
+            ex = dp.CopyEngineExchange(10_000, torch.device("cuda:0"))
+        except Exception as e:  # noqa: BLE001
+            pytest.skip(f"symmetric memory unavailable: {type(e).__name__}: {e}")
+        g = torch.Generator(device="cuda").manual_seed(1)
+        ts = [torch.randn(1000, 3, device="cuda", generator=g), torch.randn(77, device="cuda", generator=g),
+              torch.randn(5, 16, 3, device="cuda", generator=g)]
+        outs = ex.allreduce_mean(ts)
+        torch.cuda.current_stream().wait_stream(ex.stream)
+        torch.cuda.synchronize()
+        for a, b in zip(ts, outs):
+            assert a.shape == b.shape and torch.equal(a, b)
+        with pytest.raises(ValueError):
+            ex.allreduce_mean([torch.zeros(20_000, device="cuda")])
+    finally:
+        dist.destroy_process_group()
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
