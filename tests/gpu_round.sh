@@ -26,14 +26,14 @@ if [ "$want_ncu" = ncu ]; then
     --log-file $out/launches_bench.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-gpu-reference > $out/ncu_bench.log 2>&1
   echo "ncu launch list exit $?"
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'fused_fwd_kernel|fused_bwd_kernel|tc_wgrad|tc_rows_kernel' \
-    -s 10 -c 14 -o $out/mlp -f python tests/profile_deform.py 1000000 3 > $out/ncu_mlp.log 2>&1
+    -s 6 -c 8 -o $out/mlp -f python tests/profile_deform.py 1000000 3 > $out/ncu_mlp.log 2>&1
   echo "ncu mlp exit $?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'blend_bwd|render_fwd|gaussian_bwd|preprocess_fwd|onesweep|radix|emit_keys' \
-    -c 40 -o $out/raster -f python tests/profile_raster.py mine C3 0.3 > $out/ncu_raster.log 2>&1
+  timeout 900 ncu --set full --clock-control none -k regex:'blend_bwd|render_fwd|gaussian_bwd|preprocess_fwd|onesweep|radix|emit_keys' \
+    -s 13 -c 13 -o $out/raster -f python tests/profile_raster.py mine C3 0.3 > $out/ncu_raster.log 2>&1
   echo "ncu raster exit $?"
 fi
 for wl in C4 C5; do
   BENCH_SUSTAINED_S=0 timeout 400 python bench.py --workload $wl --steps 20 --warmup 3 --no-cpu-baseline > $out/bench_${wl}_1gpu.json 2> $out/bench_${wl}_1gpu.err
   echo "bench $wl exit $?"
 done
-ls -la $out
+du -sh $out; ls -la $out
