@@ -819,6 +819,11 @@ def run_ours(args, rank, local, world):
     roof = dict(rooflines[dominant], kernel=dominant, peak_source=(
         tf32_src if rooflines[dominant]["bound"] == "tensor" else "MEASURED_PEAKS.json" if peaks["source"] == "measured"
         else "B200_PROFILING.md fallback")) if dominant else None
+    if roof and roof["bound"] == "tensor" and roof.get("hbm_model", {}).get("design_frac_of_hbm_peak", 0) > 0.6:
+        roof["note_hbm"] = ("this kernel is HBM-bound in practice: the bytes its design moves per launch (hbm_model."
+                            "design_bytes_per_step, confirmed by ncu: traffic_over_design) over its time are %.0f %% of the "
+                            "measured HBM copy peak; the tensor line is kept because SURVEY 8(d) defines the MLP roofline on "
+                            "the tensor model" % (100 * roof["hbm_model"]["design_frac_of_hbm_peak"]))
     if roof and roof["bound"] == "tensor":
         roof["note"] = ("algorithmic flops = minimal formulation of SURVEY 8(d) for ONE pass (this kernel) over both "
                         "stages; the kernel executes 3 tf32 MMAs per algorithmic product (3xTF32, fp32-grade "
