@@ -63,7 +63,11 @@ struct BwdCfg {
   static constexpr bool NORMAL = COORD || DEPTH;
   static constexpr bool GEO = NORMAL;
   static constexpr int V = COORD ? 32 : 16;            // gradient components per pair
-  static constexpr int B = COORD ? 64 : 128;           // Gaussians per staged batch
+  // Gaussians per staged batch. 64 keeps a CTA at 41 KB of shared memory (82 KB with 128), so that three CTAs fit an SM
+  // when the registers allow it: measured at C3 (variant <0,1>) 1.46 ms with B = 128 / 2 CTAs (112 registers), 1.49 with
+  // B = 64 / 2 CTAs, 1.28 with B = 64 / 3 CTAs (79 registers, no spills), 1.39 with 4 CTAs (64 registers, spills).
+  static constexpr int B = 64;
+  static constexpr int OCC = COORD ? 2 : 3;            // CTAs per SM asked of the compiler (COORD: 78 KB per CTA)
   static constexpr int NQ = GEO ? 4 : 3;
   static constexpr int NQT = NQ + (COORD ? REC_COORD_QUADS : 0);
   static constexpr size_t rec_bytes = (size_t)2 * NQT * B * sizeof(float4);
@@ -74,7 +78,7 @@ struct BwdCfg {
 };
 
 template <bool COORD, bool DEPTH>
-__global__ void __launch_bounds__(BWD_THREADS, 2)
+__global__ void __launch_bounds__(BWD_THREADS, (BwdCfg<COORD, DEPTH>::OCC))
 blend_bwd(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
           const float* __restrict__ bg, const float4* __restrict__ rec, const float4* __restrict__ rec_coord,
           const float* __restrict__ alphas, const float* __restrict__ accum_coord,
@@ -816,7 +820,10 @@ constexpr int GB_THREADS = 128;
 constexpr int GB_SH_ROW = 49;
 
 template <bool COORD>
-__global__ void __launch_bounds__(GB_THREADS, 4)
+#ifndef ED3DGS_GB_OCC
+#define ED3DGS_GB_OCC 4
+#endif
+__global__ void __launch_bounds__(GB_THREADS, ED3DGS_GB_OCC)
 gaussian_bwd(int P, int D, int M, const float* __restrict__ means, const int* __restrict__ radii,
              const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
              const float* __restrict__ scales, const float* __restrict__ rots, float scale_mod,
