@@ -104,6 +104,94 @@ class _PhotometricLoss(torch.autograd.Function):
         return d.view(ctx.shape), None, None
 
 
+class _StepLoss(torch.autograd.Function):
+    """The whole per-view loss of train.py:195-271 as ONE autograd node: Ll1 + lambda_dssim * (1 - ssim) / 2
+    + lambda_dn * ((1 - r) * mean(err_expected) + r * mean(err_median)) + w_mask * mean(mask).
+    The two loss kernels write their raw sums into one float64 vector, the mask sum joins them and a single dot product
+    with a cached coefficient vector gives the scalar: 4 small torch launches instead of the ~20 one-element kernels the
+    term-by-term composition issued (profiles/r02_v3_launches_step.csv). The backward feeds the upstream scalar to the two
+    backward kernels as a device-side coefficient."""
+
+    _coefs = {}
+
+    @staticmethod
+    def forward(ctx, image, gt, depth_e, depth_m, normal, mask, fx, fy, lam_dssim, lam_dn, depth_ratio, w_mask):
+        _check(image)
+        dev = image.device
+        x = image.detach().contiguous().float()
+        y = gt.detach().contiguous().float()
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        use_dn = normal is not None and lam_dn != 0.0
+        use_mask = mask is not None and w_mask != 0.0
+        n_img, hw = float(x.numel()), float(H * W)
+        n_mask = float(mask.numel()) if use_mask else 1.0
+        key = (str(dev), n_img, hw, n_mask, float(lam_dssim), float(lam_dn) if use_dn else 0.0, float(depth_ratio),
+               float(w_mask) if use_mask else 0.0)
+        coef = _StepLoss._coefs.get(key)
+        if coef is None:
+            lam = float(lam_dssim)
+            coef = torch.tensor([1.0 / n_img, -lam / (2.0 * n_img), key[5] * (1.0 - depth_ratio) / hw,
+                                 key[5] * depth_ratio / hw, key[7] / n_mask, lam / 2.0], dtype=torch.float64, device=dev)
+            _StepLoss._coefs[key] = coef
+        S = torch.ones(6, dtype=torch.float64, device=dev)      # [l1, ssim, err_expected, err_median, mask, 1]
+        maps = torch.empty((3, B * C, H, W), dtype=torch.float32, device=dev)
+        lib = _lib.lib()
+        de = dm = nr = None
+        with torch.cuda.device(dev):
+            _lib.check(lib.ed3dgs_ssim_l1_forward(B * C, H, W, x.data_ptr(), y.data_ptr(), S.data_ptr(), maps.data_ptr(),
+                                                  _lib.stream_handle()))
+            if use_dn:
+                de = depth_e.detach().contiguous().float()
+                dm = depth_m.detach().contiguous().float()
+                nr = normal.detach().contiguous().float()
+                _lib.check(lib.ed3dgs_depth_normal_forward(nr.shape[-2], nr.shape[-1], float(fx), float(fy), de.data_ptr(),
+                                                           dm.data_ptr(), nr.data_ptr(), None, S[2:4].data_ptr(),
+                                                           _lib.stream_handle()))
+        if use_mask:
+            torch.sum(mask.detach().reshape(1, -1), dim=1, dtype=torch.float64, out=S[4:5])
+        ctx.save_for_backward(x, y, maps, de, dm, nr)
+        ctx.cfg = (image.shape, None if depth_e is None else depth_e.shape, None if depth_m is None else depth_m.shape,
+                   None if normal is None else normal.shape, None if mask is None else mask.shape, float(fx), float(fy),
+                   float(lam_dssim), key[5], float(depth_ratio), key[7], n_img, n_mask, use_dn, use_mask)
+        return torch.dot(S, coef).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y, maps, de, dm, nr = ctx.saved_tensors
+        (s_img, s_e, s_m, s_n, s_mask, fx, fy, lam, lam_dn, r, w_mask, n_img, n_mask, use_dn, use_mask) = ctx.cfg
+        C, H, W = x.shape[-3], x.shape[-2], x.shape[-1]
+        B = x.numel() // (C * H * W)
+        g = g.contiguous().float()
+        lib = _lib.lib()
+        d_img = torch.empty_like(x)
+        g_e = g_m = g_n = g_mask = None
+        with torch.cuda.device(x.device):
+            _lib.check(lib.ed3dgs_ssim_l1_backward(B * C, H, W, x.data_ptr(), y.data_ptr(), maps.data_ptr(), g.data_ptr(),
+                                                   1.0 / n_img, -lam / (2.0 * n_img), d_img.data_ptr(),
+                                                   _lib.stream_handle()))
+            if use_dn:
+                g_e, g_m, g_n = torch.empty_like(de), torch.empty_like(dm), torch.empty_like(nr)
+                _lib.check(lib.ed3dgs_depth_normal_backward(nr.shape[-2], nr.shape[-1], fx, fy, de.data_ptr(), dm.data_ptr(),
+                                                            nr.data_ptr(), g.data_ptr(), lam_dn * (1.0 - r), lam_dn * r,
+                                                            g_e.data_ptr(), g_m.data_ptr(), g_n.data_ptr(),
+                                                            _lib.stream_handle()))
+                g_e, g_m, g_n = g_e.view(s_e), g_m.view(s_m), g_n.view(s_n)
+        if use_mask:
+            g_mask = (g * (w_mask / n_mask)).expand(s_mask)
+        return (d_img.view(s_img), None, g_e, g_m, g_n, g_mask, None, None, None, None, None, None)
+
+
+def step_loss(image, gt_image, view=None, expected_depth=None, median_depth=None, normal=None, mask=None,
+              lambda_dssim=0.2, lambda_depth_normal=0.05, depth_ratio=0.6, w_mask=0.0):
+    """Fused per-view training loss (see _StepLoss); terms whose inputs are None are left out."""
+    fx, fy = _focals(view) if view is not None else (1.0, 1.0)
+    if view is None:
+        normal = None
+    return _StepLoss.apply(image, gt_image, expected_depth, median_depth, normal, mask, fx, fy, float(lambda_dssim),
+                           float(lambda_depth_normal), float(depth_ratio), float(w_mask))
+
+
 def l1_loss(network_output, gt, keepdim=False):
     """utils/loss_utils.py:24-28 (elementwise torch; the fused path is photometric_loss)."""
     if keepdim:

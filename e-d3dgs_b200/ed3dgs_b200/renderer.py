@@ -204,14 +204,15 @@ def training_loss(pkg, gt_image, view=None, reg=True, lambda_dssim=0.2, lambda_d
     plus a small alpha-mask term so that every rasterizer output carries an upstream gradient.
     fused=True uses the CUDA losses of ed3dgs_b200.loss_utils; fused=False issues the reference's torch ops
     (`view` is needed for the depth-normal term; without it that term is skipped)."""
-    if fused:
+    if fused:   # one autograd node for the whole sum (loss_utils._StepLoss)
         from . import loss_utils as L
-        loss = L.photometric_loss(pkg["render"], gt_image, lambda_dssim)[0]
-        if reg and view is not None:
-            loss = loss + lambda_depth_normal * L.depth_normal_loss(view, pkg["expected_depth"], pkg["median_depth"],
-                                                                    pkg["normal"])
-    else:
-        loss = _torch_losses(pkg, gt_image, view, reg, lambda_dssim, lambda_depth_normal)
+        dn = reg and view is not None
+        return L.step_loss(pkg["render"], gt_image, view=view if dn else None,
+                           expected_depth=pkg["expected_depth"] if dn else None,
+                           median_depth=pkg["median_depth"] if dn else None, normal=pkg["normal"] if dn else None,
+                           mask=pkg["mask"] if reg else None, lambda_dssim=lambda_dssim,
+                           lambda_depth_normal=lambda_depth_normal, w_mask=0.01)
+    loss = _torch_losses(pkg, gt_image, view, reg, lambda_dssim, lambda_depth_normal)
     if reg:
         loss = loss + 0.01 * pkg["mask"].mean()
     return loss

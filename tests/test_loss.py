@@ -129,3 +129,39 @@ def test_losses_refuse_cpu_tensors():
     with pytest.raises(Ed3dgsError):
         L.depth_normal_loss(NS(image_width=8, image_height=8, FoVx=0.5, FoVy=0.5), torch.rand(1, 8, 8),
                             torch.rand(1, 8, 8), torch.rand(3, 8, 8))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reg,with_view", [(True, True), (True, False), (False, True)])
+def test_step_loss_node_equals_the_torch_composition(reg, with_view):
+    """renderer.training_loss(fused=True) is ONE autograd node (loss_utils._StepLoss); its value and the gradients it
+    sends to every rasterizer output must equal the reference's torch composition of the same terms
+    (training_loss(fused=False): utils/loss_utils.py:24-72, utils/graphics_utils.py:240-267, train.py:195-271)."""
+    from ed3dgs_b200.renderer import training_loss
+    H, W = 130, 171
+    g = torch.Generator(device="cuda").manual_seed(4)
+    cam = NS(image_width=W, image_height=H, FoVx=0.6, FoVy=0.47)
+    gt = torch.rand(3, H, W, device="cuda", generator=g)
+
+    def make():
+        gg = torch.Generator(device="cuda").manual_seed(9)
+        pkg = {"render": torch.rand(3, H, W, device="cuda", generator=gg),
+               "expected_depth": 1.0 + torch.rand(1, H, W, device="cuda", generator=gg),
+               "median_depth": 1.0 + torch.rand(1, H, W, device="cuda", generator=gg),
+               "normal": torch.nn.functional.normalize(torch.randn(3, H, W, device="cuda", generator=gg), dim=0),
+               "mask": torch.rand(1, H, W, device="cuda", generator=gg)}
+        return {k: v.requires_grad_(True) for k, v in pkg.items()}
+
+    a, b = make(), make()
+    view = cam if with_view else None
+    la = training_loss(a, gt, view=view, reg=reg, fused=True)
+    lb = training_loss(b, gt, view=view, reg=reg, fused=False)
+    assert abs(float(la) - float(lb)) <= 1e-5 * max(1.0, abs(float(lb)))
+    (la * 1.7).backward()
+    (lb * 1.7).backward()
+    for k in a:
+        if b[k].grad is None:
+            assert a[k].grad is None or float(a[k].grad.abs().max()) == 0.0, k
+            continue
+        scale = float(b[k].grad.abs().max())
+        assert float((a[k].grad - b[k].grad).abs().max()) <= 1e-4 * scale + 1e-12, k
