@@ -907,7 +907,11 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
       }
     }
 #endif
-    TC_TRY(tc_wgrad_launch(a, stream, wg_ts));
+    const int keep_reserve = tc_sm_reserve();
+    if (last_stage && tc_sm_reserve_last() > keep_reserve) tc_sm_reserve() = tc_sm_reserve_last();
+    const cudaError_t we = tc_wgrad_launch(a, stream, wg_ts);
+    tc_sm_reserve() = keep_reserve;
+    TC_TRY(we);
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, 128, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
@@ -947,6 +951,12 @@ int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, in
 }
 
 void ed3dgs_deform_set_emb_ready_event(void* cuda_event) { g_emb_ready_event = cuda_event; }
+
+int ed3dgs_deform_set_sm_reserve_last(int n_sms) {
+  const int prev = tc_sm_reserve_last();
+  tc_sm_reserve_last() = n_sms > 0 ? n_sms : 0;
+  return prev;
+}
 
 int ed3dgs_deform_set_sm_reserve(int n_sms) {
   const int prev = tc_sm_reserve();

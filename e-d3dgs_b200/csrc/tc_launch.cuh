@@ -44,6 +44,12 @@ inline int& tc_sm_reserve() {
   static int reserve = 0;
   return reserve;
 }
+// A larger reserve for the weight-gradient launch of the LAST stage only (ed3dgs_deform_set_sm_reserve_last): the exchange
+// of the embedding gradient runs next to exactly that launch and has one launch (1.2 ms) to finish in.
+inline int& tc_sm_reserve_last() {
+  static int reserve = 0;
+  return reserve;
+}
 
 inline int tc_sm_count() {   // of the current device (not cached: a process may drive several GPUs)
   int dev = 0, sms = 0;

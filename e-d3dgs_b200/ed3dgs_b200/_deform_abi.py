@@ -33,6 +33,8 @@ def declare(lib):
     lib.ed3dgs_deform_workspace_bytes.argtypes = [c_int, c_int, c_int]
     lib.ed3dgs_deform_set_emb_ready_event.restype = None
     lib.ed3dgs_deform_set_emb_ready_event.argtypes = [c_void_p]
+    lib.ed3dgs_deform_set_sm_reserve_last.restype = c_int
+    lib.ed3dgs_deform_set_sm_reserve_last.argtypes = [c_int]
     lib.ed3dgs_deform_set_sm_reserve.restype = c_int
     lib.ed3dgs_deform_set_sm_reserve.argtypes = [c_int]
     lib.ed3dgs_deform_forward.restype = c_int

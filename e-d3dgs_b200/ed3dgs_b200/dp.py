@@ -203,7 +203,7 @@ class OverlapSync(GradSync):
     collective runs next to the MLP backward --, (2) makes the main stream wait for the side stream, (3) reduces bucket B.
     Host logic only: without CUDA (gloo tests) or with one rank it degrades to GradSync."""
 
-    def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None):
+    def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None, sm_reserve_last=8):
         """transport: "nccl" = bucket A through NCCL next to the backward (needs `sm_reserve` SMs and a matching
         NCCL_MAX_CTAS); "ce" = bucket A through CopyEngineExchange (no SMs for the transfers).
         embedding (transport "ce" only): the per-Gaussian embedding parameter. Its gradient is final after the chain kernel
@@ -217,6 +217,7 @@ class OverlapSync(GradSync):
         self.late = [p for p in self.params if id(p) not in early_ids and p is not self.embedding]
         self.ce_emb = None
         self.emb_event = None
+        self.sm_reserve_last = sm_reserve_last
         self.sm_reserve = sm_reserve
         self.transport = transport
         self.side = None
@@ -238,6 +239,7 @@ class OverlapSync(GradSync):
                     self.emb_event = torch.cuda.Event()
                     self.emb_event.record(torch.cuda.current_stream(dev))      # creates the cudaEvent_t
                     _lib.lib().ed3dgs_deform_set_emb_ready_event(ctypes.c_void_p(self.emb_event.cuda_event))
+                    _lib.lib().ed3dgs_deform_set_sm_reserve_last(int(self.sm_reserve_last))
             self.side = torch.cuda.Stream(device=dev)
             # with the copy-engine transport nothing reduces the pass-through gradients in place: no copies needed
             deformation.set_backward_stream(self.side, self.sm_reserve, clone=self.ce is None)
@@ -251,6 +253,7 @@ class OverlapSync(GradSync):
         if self.emb_event is not None:
             from . import _lib
             _lib.lib().ed3dgs_deform_set_emb_ready_event(None)
+            _lib.lib().ed3dgs_deform_set_sm_reserve_last(0)
         self.side, self.active = None, False
 
     def join(self):

@@ -85,6 +85,13 @@ int ed3dgs_deform_set_sm_reserve(int n_sms);
 void ed3dgs_deform_set_emb_ready_event(void* cuda_event);
 
 /*
+ * SMs left free by the weight-gradient launch of the LAST stage of every later ed3dgs_deform_backward (the launch that runs
+ * after the event above), when larger than the general reserve: the embedding exchange has that one launch to finish in.
+ * Returns the previous value.
+ */
+int ed3dgs_deform_set_sm_reserve_last(int n_sms);
+
+/*
  * Forward of both stages. coarse / fine may be NULL (no_coarse_deform / no_fine_deform).
  *   in[h], sub[h], out[h]: [N, k_h] for h = pos, scales, rotations, opacity, rgb.
  *   sub = in + delta_coarse * coef   (the reference's *_sub tuple), out = sub + delta_fine * coef.
