@@ -482,7 +482,7 @@ def run_ours(args, rank, local, world):
     arena = dp.OverlapSync(list(scene.parameters()),
                            early=[scene._xyz, scene._features_dc, scene._features_rest, scene._scaling, scene._rotation,
                                   scene._opacity], sm_reserve=sm_reserve, transport=transport,
-                           embedding=scene._embedding if os.environ.get("BENCH_CE_EMB", "0") != "0" else None,
+                           embedding=scene._embedding if os.environ.get("BENCH_CE_EMB", "1") != "0" else None,
                            sm_reserve_last=int(os.environ.get("BENCH_SM_RESERVE_LAST", "8")))
     overlap_note = None
     if overlap:
