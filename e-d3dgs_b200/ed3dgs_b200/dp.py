@@ -151,7 +151,7 @@ class CopyEngineExchange:
         self.peers = [self.hdl.get_buffer(r, (cap,), torch.float32) for r in range(self.world)]
         self.stage = torch.empty(self.world, cap // self.world, dtype=torch.float32, device=device)
         self.stream = torch.cuda.Stream(device=device)
-        self.timeout_ms = 30000   # a rank that never arrives makes the barrier kernel trap instead of hanging the box
+        self.timeout_ms = 120000  # a rank that never arrives makes the barrier kernel trap instead of hanging the box
 
     def allreduce_mean(self, tensors):
         total = sum(t.numel() for t in tensors)
