@@ -193,14 +193,17 @@ def deformation_ran():
 
 
 class OverlapSync(GradSync):
-    """GradSync with the exchange split in two and the first half hidden behind the deformation network's backward.
+    """GradSync with the exchange split up and most of it hidden behind the deformation network's backward.
 
     Bucket A = the gradients of the per-Gaussian rasterizer inputs (xyz, f_dc, f_rest, opacity, scaling, rotation:
     59 of the 91 floats per Gaussian). They are the *upstream* gradients of the deformation node, i.e. final once the
     rasterizer backward and the activations backward have run. Bucket B = embedding + deformation network.
     With the overlap on, `deformation._DeformFunction.backward` issues its kernels on a side stream with `sm_reserve`
-    SMs left free; allreduce() then (1) reduces bucket A -- NCCL's stream only waits for the main stream, so the
-    collective runs next to the MLP backward --, (2) makes the main stream wait for the side stream, (3) reduces bucket B.
+    SMs left free; allreduce() then (1) exchanges bucket A -- through CopyEngineExchange (transport "ce": copy engines
+    over NVLink, no SMs) or through NCCL (transport "nccl": its stream only waits for the main stream) -- next to the MLP
+    backward, (1b, "ce" with `embedding`) exchanges the embedding gradient from the event the library records once it is
+    final, (2) makes the main stream wait for the side stream, (3) reduces what is left of bucket B through NCCL.
+    Measurements and the choice of defaults: DESIGN.md section 6.
     Host logic only: without CUDA (gloo tests) or with one rank it degrades to GradSync."""
 
     def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None, sm_reserve_last=8):
