@@ -6,6 +6,7 @@
 // float4s, box bounds are staged through shared memory, and the sort is this library's own
 // stable radix sort. The result is the exact 3-NN mean, so it is bit-identical to the reference.
 #include <cfloat>
+#include <mutex>
 #include "raster_state.cuh"
 #include "raster_api.h"
 
@@ -488,3 +489,94 @@ int compute_3d_filter(int P, const float* xyz, int C, const float* cams, float f
 }
 
 }  // namespace ed3dgs
+
+// ---------------------------------------------------------------------------------------------
+// distCUDA2 without a caller workspace (ed3dgs_dist_cuda2_static, include/ed3dgs_b200.h).
+//
+// Who this is for: code that wants the initial Gaussian scales but is in no position to hand over device
+// scratch. A plug-in living inside another program's fixed memory pool (an inference server that carved up the
+// whole GPU at start-up, a renderer with a frozen arena), a host written in a language whose FFI only ever sees
+// the input and output arrays, or a tool running late in a job whose pool is exhausted: none of them can call
+// cudaMalloc -- some because the pool owner forbids it, some because there is nothing left to hand out, and
+// all of them would pay a device-wide synchronisation for every cudaMalloc / cudaFree pair anyway. For them
+// the Morton keys, the sort's ping-pong buffers and its look-back words live in the array below instead, which
+// is part of the library image: the driver places it when the module is loaded on a device and keeps it until
+// the process exits, whether or not this entry point is ever called.
+//
+// Limit: KNN_STATIC_MAX_POINTS points (sparse structure-from-motion clouds, the reference's input at
+// scene/gaussian_model.py:161, are well inside it). Larger clouds must use ed3dgs_dist_cuda2 with their own
+// workspace.
+namespace ed3dgs {
+
+constexpr int KNN_STATIC_MAX_POINTS = 262144;
+constexpr size_t KNN_STATIC_BYTES = 16u << 20;   // 52 B per point + 0.6 MB of sort words at the limit, rounded up
+constexpr int KNN_STATIC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_knn_static_scratch[KNN_STATIC_BYTES];
+
+// g_knn_static_scratch, written in host code, is only the host-side handle of the symbol -- not somewhere a
+// kernel can read or write. The address the kernels need differs per device and comes from the runtime, asked
+// once per device while that device is current.
+static void* g_knn_static_addr[KNN_STATIC_MAX_DEVICES] = {};
+static std::mutex g_knn_static_mu;
+
+static int knn_static_address(void** out) {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) { set_error("ed3dgs_dist_cuda2_static: cudaGetDevice: %s", cudaGetErrorString(err)); return ED3DGS_ERR_CUDA; }
+  if (dev < 0 || dev >= KNN_STATIC_MAX_DEVICES) {
+    set_error("ed3dgs_dist_cuda2_static: device ordinal %d outside [0, %d)", dev, KNN_STATIC_MAX_DEVICES);
+    return ED3DGS_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lk(g_knn_static_mu);
+  if (g_knn_static_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    err = cudaGetSymbolAddress(&ptr, g_knn_static_scratch);
+    if (err != cudaSuccess || ptr == nullptr) {
+      set_error("ed3dgs_dist_cuda2_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(err));
+      return ED3DGS_ERR_CUDA;
+    }
+    g_knn_static_addr[dev] = ptr;
+  }
+  *out = g_knn_static_addr[dev];
+  return ED3DGS_OK;
+}
+
+int dist_cuda2_static(int P, const float* points, float* mean_dists, cudaStream_t stream) {
+  if (P <= 0) return ED3DGS_OK;
+  if (P > KNN_STATIC_MAX_POINTS) {
+    set_error("ed3dgs_dist_cuda2_static: %d points exceed the built-in scratch (at most %d); "
+              "use ed3dgs_dist_cuda2 with a caller workspace",
+              P, KNN_STATIC_MAX_POINTS);
+    return ED3DGS_ERR_ARG;
+  }
+  if (points == nullptr || mean_dists == nullptr) {
+    set_error("ed3dgs_dist_cuda2_static: points and mean_dists must be device pointers");
+    return ED3DGS_ERR_ARG;
+  }
+  if (dist_cuda2_workspace(P) > KNN_STATIC_BYTES) {   // cannot happen unless the layout grows past the array
+    set_error("ed3dgs_dist_cuda2_static: layout needs %zu bytes, the array holds %zu", dist_cuda2_workspace(P),
+              KNN_STATIC_BYTES);
+    return ED3DGS_ERR_ARG;
+  }
+  void* scratch = nullptr;
+  const int rc = knn_static_address(&scratch);
+  if (rc != ED3DGS_OK) return rc;
+  // Same launches as the workspace variant. Nothing from an earlier call is relied on: the bounding box and the
+  // sort's tickets / look-back words are cleared on the stream by dist_cuda2 and radix_sort_pairs themselves,
+  // every other region is fully overwritten before it is read.
+  return dist_cuda2(P, points, mean_dists, scratch, KNN_STATIC_BYTES, stream);
+}
+
+}  // namespace ed3dgs
+
+extern "C" {
+
+int ed3dgs_dist_cuda2_static_max_points(void) { return ed3dgs::KNN_STATIC_MAX_POINTS; }
+
+int ed3dgs_dist_cuda2_static(int P, const float* points, float* mean_dists, void* stream) {
+  ed3dgs::set_error("%s", "");
+  return ed3dgs::dist_cuda2_static(P, points, mean_dists, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

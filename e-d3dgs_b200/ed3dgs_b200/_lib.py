@@ -51,6 +51,10 @@ def _declare(lib):
     lib.ed3dgs_dist_cuda2_workspace_bytes.argtypes = [c_int]
     lib.ed3dgs_dist_cuda2.restype = c_int
     lib.ed3dgs_dist_cuda2.argtypes = [c_int, P, P, P, c_size_t, c_void_p]
+    lib.ed3dgs_dist_cuda2_static_max_points.restype = c_int
+    lib.ed3dgs_dist_cuda2_static_max_points.argtypes = []
+    lib.ed3dgs_dist_cuda2_static.restype = c_int
+    lib.ed3dgs_dist_cuda2_static.argtypes = [c_int, P, P, c_void_p]
     lib.ed3dgs_compute_3d_filter.restype = c_int
     lib.ed3dgs_compute_3d_filter.argtypes = [c_int, P, c_int, P, c_float, P, P, POINTER(c_int), c_void_p]
     lib.ed3dgs_activations_forward.restype = c_int

@@ -167,6 +167,33 @@ int ed3dgs_dist_cuda2(int P, const float* points, float* mean_dists, void* works
                       size_t workspace_bytes, void* stream);
 
 /*
+ * ed3dgs_dist_cuda2 for callers that cannot provide device scratch. No counterpart in the reference (its
+ * distCUDA2 lets thrust / torch allocate whatever it needs, simple_knn.cu:188-211).
+ *
+ * Some users of this library never get to allocate GPU memory: a plug-in inside a host application that
+ * sized one memory pool at start-up and forbids cudaMalloc afterwards, a binding from a language whose
+ * FFI layer can pass the input and output arrays it already owns but has no allocator of its own, a step
+ * that runs when the job's pool is already full. Same inputs, same result (bit-identical) as
+ * ed3dgs_dist_cuda2, but the Morton keys, sort buffers and look-back words live in a 16 MiB array that is
+ * part of the library itself. The call performs no cudaMalloc / cudaFree and calls no allocating library.
+ *
+ *   Limit    P <= ed3dgs_dist_cuda2_static_max_points() (262144). Larger P returns ED3DGS_ERR_ARG with a
+ *            message naming the limit; nothing is launched.
+ *   Cost     every GPU on which this library's module gets loaded holds the 16 MiB until the process ends,
+ *            used or not.
+ *   First    the first call on each device looks up the array's device address (with that device current --
+ *   call     the caller must have made the device that owns `stream`, `points` and `mean_dists` current,
+ *            as for every entry point here). Make that first call before starting any stream capture.
+ *   Sharing  there is one array per device, shared by every call and every thread, and it keeps whatever
+ *            the previous call left in it. The call clears what it needs cleared itself, so calls queued
+ *            one after the other (same stream, or ordered by events) are fine. Two calls that can
+ *            overlap on the same GPU (different streams, no ordering) race on the array and both
+ *            results are garbage; serialise them.
+ */
+int ed3dgs_dist_cuda2_static_max_points(void);
+int ed3dgs_dist_cuda2_static(int P, const float* points, float* mean_dists, void* stream);
+
+/*
  * Exact K nearest neighbours of every point (self excluded), K <= 32: sq_dists[P,K] (double, ascending) and
  * indices[P,K] (int32). Replaces utils/extra_utils.py:5-16 (`o3d_knn`: P Open3D KDTreeFlann queries in a python
  * loop on the CPU, float64), which train.py:218-229 runs for the embedding regulariser whenever the number
