@@ -365,9 +365,12 @@ static int check_weights(const ed3dgs_deform_weights* w) {
 // Event recorded right after the LAST writer of d_embedding in ed3dgs_deform_backward (ed3dgs_deform_set_emb_ready_event):
 // the embedding gradient is final one weight-gradient launch (1.2 ms at 1 M Gaussians) before the call's last kernel, and
 // a multi-GPU caller starts its exchange from there.
-static void* g_emb_ready_event = nullptr;
-static inline void record_emb_ready(bool last_stage, cudaStream_t stream) {
-  if (last_stage && g_emb_ready_event) cudaEventRecord(static_cast<cudaEvent_t>(g_emb_ready_event), stream);
+// One event per device (the device current at the call, like the SM reserves in tc_launch.cuh): an event belongs to the
+// device it was created on, and recording it on another device's stream fails.
+static void* g_emb_ready_event[TC_MAX_DEVICES] = {};
+static inline cudaError_t record_emb_ready(bool last_stage, cudaStream_t stream) {
+  void* ev = last_stage ? g_emb_ready_event[tc_device_slot()] : nullptr;
+  return ev ? cudaEventRecord(static_cast<cudaEvent_t>(ev), stream) : cudaSuccess;
 }
 
 // precision of the call in flight on this thread (ed3dgs_deform_weights::precision): 0 = 3xTF32, 1 = single tf32 pass
@@ -760,7 +763,7 @@ static int stage_backward(const ed3dgs_deform_weights* w, const ed3dgs_deform_gr
     a.accumulate = accumulate_emb;
     a.b[0] = TcBatch{dh, w->feat_w[0] + temb, d_emb, nullptr, nullptr, nullptr, gemb, 0, gemb, 0, 0, 1.f};
     TC_TRY(tc_launch(TC_K_MAJOR, TC_MN_MAJOR, a, 1, wk.Wprep, stream));
-    record_emb_ready(last_stage, stream);
+    TC_TRY(record_emb_ready(last_stage, stream));
   }
   layer0_temporal_backward<<<(temb + 31) / 32, 256, 0, stream>>>(
       w->feat_w[0], ld0, temb, W, tau, wk.dc1, g ? g->feat_w[0] : nullptr, g ? g->feat_b[0] : nullptr, d_tau);
@@ -851,7 +854,7 @@ static int stage_backward_fused(const ed3dgs_deform_weights* w, const ed3dgs_def
     fused_bwd_kernel<<<ntiles < sms ? ntiles : sms, FB_THREADS, FM_BWD_SMEM, stream>>>(ba);
   }
   TC_TRY(cudaGetLastError());
-  record_emb_ready(last_stage, stream);   // d_emb is complete: the weight gradients below do not touch it
+  TC_TRY(record_emb_ready(last_stage, stream));   // d_emb is complete: the weight gradients below do not touch it
 
   if (g) {
     // every weight gradient of the stage in one launch; the groups of a slice of Gaussians are adjacent work items, so
@@ -950,7 +953,7 @@ int ed3dgs_temporal_embed_backward(const float* weight, int max_emb, int dim, in
   return ED3DGS_OK;
 }
 
-void ed3dgs_deform_set_emb_ready_event(void* cuda_event) { g_emb_ready_event = cuda_event; }
+void ed3dgs_deform_set_emb_ready_event(void* cuda_event) { g_emb_ready_event[tc_device_slot()] = cuda_event; }
 
 int ed3dgs_deform_set_sm_reserve_last(int n_sms) {
   const int prev = tc_sm_reserve_last();

@@ -40,15 +40,23 @@ inline bool tc_rows_build(TcArgs& a) {
 // SMs the persistent kernels of the deformation network leave free (ed3dgs_deform_set_sm_reserve): a concurrent NCCL
 // collective needs a few SMs of its own, otherwise its CTAs wait for a persistent CTA to retire and the CTAs of the
 // next persistent launch that lose the race form a second wave (static tile assignment: the kernel takes twice as long).
+// Both reserves (and the event in deform.cu) are kept PER DEVICE, keyed by the device that is current at the call: a
+// process that drives two GPUs sets and reads them independently.
+constexpr int TC_MAX_DEVICES = 64;
+inline int tc_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= TC_MAX_DEVICES) dev = 0;
+  return dev;
+}
 inline int& tc_sm_reserve() {
-  static int reserve = 0;
-  return reserve;
+  static int reserve[TC_MAX_DEVICES] = {};
+  return reserve[tc_device_slot()];
 }
 // A larger reserve for the weight-gradient launch of the LAST stage only (ed3dgs_deform_set_sm_reserve_last): the exchange
 // of the embedding gradient runs next to exactly that launch and has one launch (1.2 ms) to finish in.
 inline int& tc_sm_reserve_last() {
-  static int reserve = 0;
-  return reserve;
+  static int reserve[TC_MAX_DEVICES] = {};
+  return reserve[tc_device_slot()];
 }
 
 inline int tc_sm_count() {   // of the current device (not cached: a process may drive several GPUs)

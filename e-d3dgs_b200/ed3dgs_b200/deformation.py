@@ -6,6 +6,7 @@ The arithmetic runs in libed3dgs_b200.so: temporal-embedding kernel + fused tens
 (3xTF32, fp32-grade) forward and backward, behind one autograd node.
 """
 import ctypes
+import weakref
 
 import numpy as np
 import torch
@@ -18,16 +19,42 @@ from . import _lib
 # it, so that the all-reduce of the Gaussian-parameter gradients (which are this node's *upstream* gradients and hence
 # final before it starts) can run on NCCL's stream at the same time. Everything the side stream still reads or writes
 # is parked in `keep` until dp.OverlapSync has made the main stream wait for it.
-_overlap = {"stream": None, "sm_reserve": 0, "clone": True, "keep": []}
+#
+# Restriction, and what guards it. The gradients this node returns for its leaves (embedding, temporal table, camera
+# offsets, Linear parameters) are still being written by the side stream when backward() returns, while autograd
+# believes they belong to the main stream. That is only sound while nobody touches them on the main stream before
+# dp.OverlapSync.join(): one deformation backward per step, every leaf with .grad unset (AccumulateGrad then adopts
+# the tensor without reading it), and no other term of the loss feeding the same leaves. The first two are checked in
+# backward(): a second backward before the join, or a leaf that already holds a .grad, makes the main stream wait for
+# the side stream before the gradients are handed back (`serialised` counts those). The third cannot be seen from
+# inside the node (autograd sums the contributions of several nodes in its input buffer, on the main stream): a caller
+# whose loss has such terms -- the reference's embedding regulariser on _embedding, train.py:229-233, or its temporal
+# smoothness term on the table, train.py:236-242 -- must say so with shared_leaves=True, which also serialises.
+_overlap = {"stream": None, "sm_reserve": 0, "clone": True, "keep": [], "shared_leaves": False, "serialised": 0}
 
 
-def set_backward_stream(stream, sm_reserve=0, clone=True):
+def set_backward_stream(stream, sm_reserve=0, clone=True, shared_leaves=False):
     """stream = None switches the overlap off. sm_reserve: SMs the persistent backward kernels leave to the exchange.
-    clone: the kernels read copies of the pass-through gradients (needed when the caller reduces them in place)."""
+    clone: the kernels read copies of the pass-through gradients (needed when the caller reduces them in place).
+    shared_leaves: other terms of the loss also reach the embedding / table / offsets / network parameters in the same
+    backward pass; the main stream then waits for the side stream before this node's gradients leave it."""
     _overlap["stream"] = stream
     _overlap["sm_reserve"] = int(sm_reserve) if stream is not None else 0
     _overlap["clone"] = bool(clone)
+    _overlap["shared_leaves"] = bool(shared_leaves) if stream is not None else False
+    _overlap["serialised"] = 0
     _overlap["keep"].clear()
+
+
+def _must_serialise(leaf_refs):
+    """True when the gradients of an overlapped backward may be read on the main stream before the join."""
+    if _overlap["shared_leaves"] or _overlap["keep"]:
+        return True
+    for r in leaf_refs:
+        leaf = r()
+        if leaf is not None and leaf.grad is not None:
+            return True
+    return False
 
 
 _HEAD_NAMES = ("pos", "scales", "rotations", "opacity", "rgb")
@@ -127,6 +154,9 @@ class _DeformFunction(torch.autograd.Function):
                     tau_c.data_ptr(), tau_f.data_ptr(), ctypes.byref(in_arr), ctypes.byref(sub_arr),
                     ctypes.byref(out_arr), ctypes.byref(coef), work.data_ptr(), nbytes, _lib.stream_handle()))
         ctx.cfg = cfg
+        # weak references only: the node must not keep its own inputs alive (see _must_serialise)
+        ctx.leaf_refs = [weakref.ref(x) for x in (offsets, table, emb, *params)
+                         if isinstance(x, torch.Tensor) and x.requires_grad and x.is_leaf]
         ctx.set_materialize_grads(False)   # unused outputs arrive as None instead of N-sized zero tensors
         ctx.save_for_backward(t_c, table_c, emb_c, tau_c, tau_f, work, offsets.detach(), *pc, *pf)
         subs[4] = subs[4].view(N, 16, 3)
@@ -189,7 +219,8 @@ class _DeformFunction(torch.autograd.Function):
                 k_sub = [None if x is None else x.clone() for x in d_sub]
             side.wait_stream(torch.cuda.current_stream(dev))
             if _overlap["sm_reserve"]:
-                lib.ed3dgs_deform_set_sm_reserve(_overlap["sm_reserve"])
+                with torch.cuda.device(dev):     # the reserve is kept per device (the one current at the call)
+                    lib.ed3dgs_deform_set_sm_reserve(_overlap["sm_reserve"])
         with torch.cuda.device(dev), torch.cuda.stream(side):
             if N > 0:
                 d_out_keep, d_sub_keep = d_out, d_sub
@@ -219,10 +250,15 @@ class _DeformFunction(torch.autograd.Function):
                         d_offsets.copy_(torch.where(nz, d_t / nz.sum().clamp_min(1), torch.zeros_like(d_t)).view(offsets.shape))
         if side is not None:
             if _overlap["sm_reserve"]:
-                lib.ed3dgs_deform_set_sm_reserve(0)
+                with torch.cuda.device(dev):
+                    lib.ed3dgs_deform_set_sm_reserve(0)
+            # (tested before this backward is parked: a non-empty `keep` means an earlier backward of the same step)
+            serial = _must_serialise(getattr(ctx, "leaf_refs", ()))
             # (not flat / d_emb: a second reference would make AccumulateGrad copy them -- on the main stream, too early)
             _overlap["keep"].append((k_out, k_sub, work, t_c, table_c, emb_c, tau_c, tau_f, offsets, params))
-            if ctx.needs_input_grad[1]:   # somebody differentiates the time itself: its gradient is consumed on the main stream
+            if serial:
+                _overlap["serialised"] += 1
+            if serial or ctx.needs_input_grad[1]:   # (the time's own gradient is consumed on the main stream too)
                 torch.cuda.current_stream(dev).wait_stream(side)
 
         def passthrough(h):

@@ -102,17 +102,21 @@ class GradSync:
             world = dist.get_world_size()
             avg = scale is not None and abs(scale * world - 1.0) < 1e-12 and dist.get_backend() == "nccl"
             op = dist.ReduceOp.AVG if avg else dist.ReduceOp.SUM
-            done = False
+            manager = None
             if dist.get_backend() == "nccl" and ts:
+                # Only the availability of the (private) coalescing manager is probed. Once a collective has been
+                # enqueued an error must surface: retrying tensor by tensor would reduce some gradients twice on
+                # this rank and leave the other ranks with mismatched collectives.
                 try:
                     from torch.distributed.distributed_c10d import _coalescing_manager
-                    with _coalescing_manager(device=ts[0].device, async_ops=False):
-                        for t in ts:
-                            dist.all_reduce(t, op=op)
-                    done = True
-                except (ImportError, TypeError, RuntimeError):
-                    done = False
-            if not done:
+                    manager = _coalescing_manager(device=ts[0].device, async_ops=False)
+                except (ImportError, TypeError):
+                    manager = None
+            if manager is not None:
+                with manager:
+                    for t in ts:
+                        dist.all_reduce(t, op=op)
+            else:
                 for t in ts:
                     dist.all_reduce(t, op=op)
             if avg:
@@ -153,8 +157,18 @@ class CopyEngineExchange:
         self.stream = torch.cuda.Stream(device=device)
         self.timeout_ms = 120000  # a rank that never arrives makes the barrier kernel trap instead of hanging the box
 
-    def allreduce_mean(self, tensors):
-        total = sum(t.numel() for t in tensors)
+    def allreduce_mean(self, tensors, like=None):
+        """like: tensors that fix the layout (one per entry of `tensors`, same order on every rank). An entry of
+        `tensors` may then be None -- this rank has no contribution -- and travels as zeros, so that chunk size, offsets
+        and the number of barriers never depend on rank-local state (a rank with a missing gradient would otherwise
+        make its peers average unrelated floats, or leave them in a barrier until the time-out traps)."""
+        like = list(like) if like is not None else list(tensors)
+        if len(like) != len(tensors) or any(t is None for t in like):
+            raise ValueError("CopyEngineExchange: `like` needs one tensor per entry")
+        for t, ref in zip(tensors, like):
+            if t is not None and t.numel() != ref.numel():
+                raise ValueError(f"CopyEngineExchange: gradient of {t.numel()} floats for a slot of {ref.numel()}")
+        total = sum(ref.numel() for ref in like)
         used = (total + self.align - 1) // self.align * self.align
         if used > self.cap:
             raise ValueError(f"CopyEngineExchange: {total} floats do not fit the symmetric buffer of {self.cap}")
@@ -164,10 +178,13 @@ class CopyEngineExchange:
         outs = []
         with torch.cuda.stream(self.stream):
             off = 0
-            for t in tensors:
-                n = t.numel()
-                buf[off:off + n].copy_(t.detach().reshape(-1))
-                outs.append(buf[off:off + n].view(t.shape))
+            for t, ref in zip(tensors, like):
+                n = ref.numel()
+                if t is None:
+                    buf[off:off + n].zero_()
+                else:
+                    buf[off:off + n].copy_(t.detach().reshape(-1))
+                outs.append(buf[off:off + n].view(ref.shape))
                 off += n
             if used > total:
                 buf[total:used].zero_()
@@ -206,8 +223,15 @@ class OverlapSync(GradSync):
     Measurements and the choice of defaults: DESIGN.md section 6.
     Host logic only: without CUDA (gloo tests) or with one rank it degrades to GradSync."""
 
-    def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None, sm_reserve_last=8):
-        """transport: "nccl" = bucket A through NCCL next to the backward (needs `sm_reserve` SMs and a matching
+    def __init__(self, params, early, sm_reserve=8, transport="nccl", embedding=None, sm_reserve_last=8,
+                 shared_leaves=False):
+        """shared_leaves: set it when the loss has other terms on the leaves of the deformation node (the reference's
+        embedding regulariser and temporal smoothness term, train.py:229-242). The overlap is only sound for ONE
+        deformation backward per step whose leaves receive nothing else and start the step with .grad = None (the
+        gradients leave the node while the side stream still writes them); a second backward before join() or a leaf
+        that already holds a .grad is detected and serialised by the node itself, other loss terms cannot be, hence
+        this flag (deformation.py, comment above `_overlap`).
+        transport: "nccl" = bucket A through NCCL next to the backward (needs `sm_reserve` SMs and a matching
         NCCL_MAX_CTAS); "ce" = bucket A through CopyEngineExchange (no SMs for the transfers).
         embedding (transport "ce" only): the per-Gaussian embedding parameter. Its gradient is final after the chain kernel
         of the network's last stage, one weight-gradient launch before the backward ends; the library records an event
@@ -222,6 +246,7 @@ class OverlapSync(GradSync):
         self.emb_event = None
         self.sm_reserve_last = sm_reserve_last
         self.sm_reserve = sm_reserve
+        self.shared_leaves = bool(shared_leaves)
         self.transport = transport
         self.side = None
         self.ce = None
@@ -239,13 +264,15 @@ class OverlapSync(GradSync):
                     from . import _lib
                     import ctypes
                     self.ce_emb = CopyEngineExchange(self.embedding.numel(), dev)
-                    self.emb_event = torch.cuda.Event()
-                    self.emb_event.record(torch.cuda.current_stream(dev))      # creates the cudaEvent_t
-                    _lib.lib().ed3dgs_deform_set_emb_ready_event(ctypes.c_void_p(self.emb_event.cuda_event))
-                    _lib.lib().ed3dgs_deform_set_sm_reserve_last(int(self.sm_reserve_last))
+                    with torch.cuda.device(dev):     # the library keeps event and reserves per (current) device
+                        self.emb_event = torch.cuda.Event()
+                        self.emb_event.record(torch.cuda.current_stream(dev))      # creates the cudaEvent_t
+                        _lib.lib().ed3dgs_deform_set_emb_ready_event(ctypes.c_void_p(self.emb_event.cuda_event))
+                        _lib.lib().ed3dgs_deform_set_sm_reserve_last(int(self.sm_reserve_last))
             self.side = torch.cuda.Stream(device=dev)
             # with the copy-engine transport nothing reduces the pass-through gradients in place: no copies needed
-            deformation.set_backward_stream(self.side, self.sm_reserve, clone=self.ce is None)
+            deformation.set_backward_stream(self.side, self.sm_reserve, clone=self.ce is None,
+                                            shared_leaves=self.shared_leaves)
             self.active = True
         return self.active
 
@@ -253,11 +280,23 @@ class OverlapSync(GradSync):
         from . import deformation
         self.join()
         deformation.set_backward_stream(None)
+        self._clear_event()
+        self.side, self.active = None, False
+
+    def _clear_event(self):
+        """The library holds the raw cudaEvent_t: take it back before the torch.cuda.Event can be destroyed."""
         if self.emb_event is not None:
             from . import _lib
-            _lib.lib().ed3dgs_deform_set_emb_ready_event(None)
-            _lib.lib().ed3dgs_deform_set_sm_reserve_last(0)
-        self.side, self.active = None, False
+            with torch.cuda.device(self.ce_emb.stream.device):
+                _lib.lib().ed3dgs_deform_set_emb_ready_event(None)
+                _lib.lib().ed3dgs_deform_set_sm_reserve_last(0)
+            self.emb_event = None
+
+    def __del__(self):
+        try:   # an OverlapSync dropped without disable() must not leave a dangling event handle in the library
+            self._clear_event()
+        except Exception:  # noqa: BLE001  (interpreter shutdown: the library may be gone already)
+            pass
 
     def join(self):
         """Main stream waits for the side stream; releases what the side stream was using."""
@@ -282,13 +321,22 @@ class OverlapSync(GradSync):
             world = dist.get_world_size()
             if scale is None or abs(scale * world - 1.0) > 1e-12:
                 raise ValueError("OverlapSync(transport='ce') computes the mean over ranks: pass scale = 1 / world")
-            ps = [p for p in self.early if p.grad is not None]
-            outs = self.ce.allreduce_mean([p.grad for p in ps])       # on the exchange's own stream
+            # Layout and route are the same on every rank by construction: every early parameter has its slot
+            # (zeros where this rank has no gradient), and the embedding travels through ce_emb whenever that exchange
+            # exists (set up collectively in enable()), whether or not the deformation ran here.
+            ps = list(self.early)
+            outs = self.ce.allreduce_mean([p.grad for p in ps], like=ps)       # on the exchange's own stream
             late = self.late
-            if self.ce_emb is not None and self.embedding.grad is not None and deformation_ran():
-                # starts when the library's event fires (after the last stage's chain kernel), not at the end of the backward
-                self.ce_emb.stream.wait_event(self.emb_event)
-                outs += self.ce_emb.allreduce_mean([self.embedding.grad])
+            if self.ce_emb is not None:
+                if self.embedding.grad is not None and deformation_ran():
+                    # starts when the library's event fires (after the last stage's chain kernel), not at the end of
+                    # the backward
+                    self.ce_emb.stream.wait_event(self.emb_event)
+                elif self.side is not None:
+                    # no side-stream backward on this rank this step (or one that was serialised): whatever wrote the
+                    # gradient is ordered by the main and side streams, not by the library's event
+                    self.ce_emb.stream.wait_stream(self.side)
+                outs += self.ce_emb.allreduce_mean([self.embedding.grad], like=[self.embedding])
                 ps = ps + [self.embedding]
             elif self.embedding is not None:
                 late = late + [self.embedding]

@@ -71,8 +71,9 @@ size_t ed3dgs_deform_workspace_bytes(int W, int depth, int N);
  * Multi-GPU overlap (no reference counterpart: the reference is single-GPU, train.py:171-187). The persistent
  * tcgen05 kernels of the deformation network launch one CTA per SM; `n_sms` > 0 makes every later launch leave that
  * many SMs free, so that an NCCL collective running on another stream (the all-reduce of the Gaussian-parameter
- * gradients, final before the network's backward starts) has SMs of its own. 0 restores the full grid. Process-wide;
- * returns the previous value.
+ * gradients, final before the network's backward starts) has SMs of its own. 0 restores the full grid. Kept per device:
+ * it applies to the device that is current when it is called (and is read with the device current at the launch).
+ * Returns the previous value.
  */
 int ed3dgs_deform_set_sm_reserve(int n_sms);
 
@@ -80,14 +81,16 @@ int ed3dgs_deform_set_sm_reserve(int n_sms);
  * `cuda_event` (a cudaEvent_t, or NULL to switch it off) is recorded on the call's stream inside every later
  * ed3dgs_deform_backward right after the last kernel that writes d_embedding, i.e. before the weight-gradient launch of
  * the last stage: a multi-GPU caller makes its exchange stream wait for it and reduces the embedding gradient while that
- * launch runs. Process-wide.
+ * launch runs. Kept per device: the event must belong to the device that is current at this call, and only backward
+ * calls made with that device current record it. A failed record makes ed3dgs_deform_backward return ED3DGS_ERR_CUDA.
+ * Set it back to NULL before destroying the event.
  */
 void ed3dgs_deform_set_emb_ready_event(void* cuda_event);
 
 /*
  * SMs left free by the weight-gradient launch of the LAST stage of every later ed3dgs_deform_backward (the launch that runs
  * after the event above), when larger than the general reserve: the embedding exchange has that one launch to finish in.
- * Returns the previous value.
+ * Per device, like the two settings above. Returns the previous value.
  */
 int ed3dgs_deform_set_sm_reserve_last(int n_sms);
 

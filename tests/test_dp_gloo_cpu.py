@@ -128,3 +128,32 @@ def test_overlap_sync_world2():
     out = mgr.dict()
     mp.spawn(_worker_overlap, args=(2, port, out), nprocs=2, join=True)
     assert dict(out) == {0: True, 1: True}
+
+
+def test_overlapped_backward_serialises_when_its_leaves_are_shared():
+    """Host logic of deformation._must_serialise (the guard of the side-stream backward): a leaf that already holds a
+    gradient, an earlier backward still parked, or the caller's shared_leaves declaration each force the join."""
+    import weakref
+    from ed3dgs_b200 import deformation as D
+    a = torch.nn.Parameter(torch.zeros(3))
+    b = torch.nn.Parameter(torch.zeros(3))
+    refs = [weakref.ref(a), weakref.ref(b)]
+    saved = dict(D._overlap)
+    try:
+        D._overlap.update(stream=None, shared_leaves=False, serialised=0)
+        D._overlap["keep"].clear()
+        assert not D._must_serialise(refs)
+        b.grad = torch.ones(3)
+        assert D._must_serialise(refs)            # AccumulateGrad would add in place, on the main stream
+        b.grad = None
+        D._overlap["keep"].append(("parked",))
+        assert D._must_serialise(refs)            # second backward of the step
+        D._overlap["keep"].clear()
+        D._overlap["shared_leaves"] = True
+        assert D._must_serialise(refs)
+        D._overlap["shared_leaves"] = False
+        del b
+        assert not D._must_serialise(refs)        # a dead weak reference is not a hazard
+    finally:
+        D._overlap["keep"].clear()
+        D._overlap.update({k: v for k, v in saved.items() if k != "keep"})

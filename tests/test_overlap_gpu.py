@@ -91,6 +91,14 @@ def test_copy_engine_exchange_single_rank():
             assert a.shape == b.shape and torch.equal(a, b)
         with pytest.raises(ValueError):
             ex.allreduce_mean([torch.zeros(20_000, device="cuda")])
+        # fixed layout: a gradient this rank does not have keeps its slot and travels as zeros
+        outs = ex.allreduce_mean([ts[0], None, ts[2]], like=ts)
+        torch.cuda.current_stream().wait_stream(ex.stream)
+        torch.cuda.synchronize()
+        assert [o.shape for o in outs] == [t.shape for t in ts]
+        assert torch.equal(outs[0], ts[0]) and torch.equal(outs[2], ts[2]) and not outs[1].any()
+        with pytest.raises(ValueError):
+            ex.allreduce_mean([ts[0], None], like=ts)
     finally:
         dist.destroy_process_group()
         for k, v in saved.items():
@@ -98,3 +106,28 @@ def test_copy_engine_exchange_single_rank():
                 os.environ.pop(k, None)
             else:
                 os.environ[k] = v
+
+
+def test_second_backward_before_the_join_is_serialised():
+    """The overlap is only sound for one deformation backward per step (deformation.py, comment above `_overlap`):
+    a second one before the join, a leaf that already holds a .grad, or a caller that declares other loss terms on the
+    same leaves must make the main stream wait for the side stream before the gradients leave the node."""
+    from ed3dgs_b200 import deformation
+    rec = T.oracle_record(kink_free=True, N=3000, W=64, D=2)
+    ref = _grads(rec)
+    side = torch.cuda.Stream()
+    deformation.set_backward_stream(side, sm_reserve=8)
+    try:
+        T.run_product(rec)
+        assert deformation._overlap["serialised"] == 0 and len(deformation._overlap["keep"]) == 1
+        net, finals, subs, leaves, _ = T.run_product(rec)      # no join in between
+        assert deformation._overlap["serialised"] == 1 and len(deformation._overlap["keep"]) == 2
+        got = {"in_" + k: v.grad.detach().clone() for k, v in leaves.items()}     # main stream only: already ordered
+        got.update({"p_" + k: p.grad.detach().clone() for k, p in net.named_parameters() if p.grad is not None})
+        got.update({f"final{i}": x.detach().clone() for i, x in enumerate(finals)})
+        _compare(ref, got)
+        deformation.set_backward_stream(side, sm_reserve=8, shared_leaves=True)
+        T.run_product(rec)
+        assert deformation._overlap["serialised"] == 1
+    finally:
+        deformation.set_backward_stream(None)

@@ -54,3 +54,27 @@ def test_second_device_matches_first():
     from ed3dgs_b200 import distCUDA2
     pts = synthetic.make_gaussians(30_000)["xyz"]
     assert torch.equal(distCUDA2(pts.to("cuda:0")).cpu(), distCUDA2(pts.to("cuda:1")).cpu())
+
+
+def test_overlap_settings_and_static_scratch_are_per_device():
+    """The SM reserve of the network's persistent kernels is kept for the device that is current at the call, and the
+    built-in scratch of ed3dgs_dist_cuda2_static has one address per device (looked up with that device current)."""
+    from ed3dgs_b200 import _lib, distCUDA2
+    lib = _lib.lib()
+    with torch.cuda.device(0):
+        assert lib.ed3dgs_deform_set_sm_reserve(8) == 0
+    try:
+        with torch.cuda.device(1):
+            assert lib.ed3dgs_deform_set_sm_reserve(0) == 0      # cuda:0's setting is not visible here
+        with torch.cuda.device(0):
+            assert lib.ed3dgs_deform_set_sm_reserve(8) == 8
+    finally:
+        with torch.cuda.device(0):
+            lib.ed3dgs_deform_set_sm_reserve(0)
+    pts = synthetic.make_gaussians(30_000)["xyz"]
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        p = pts.to(dev).contiguous()
+        out = torch.empty(p.shape[0], dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(lib.ed3dgs_dist_cuda2_static(p.shape[0], p.data_ptr(), out.data_ptr(), _lib.stream_handle()))
+        assert torch.equal(out, distCUDA2(p))
