@@ -173,19 +173,32 @@ def compare(rs, a, b):
     return rep
 
 
-def assert_report(rep, rs, noise=None):
+# End-to-end bound on the ill-conditioned gradients at BASELINE's full sizes: relative l2 error without the 63 worst
+# Gaussians. Two runs of the REFERENCE differ by 0.4e-4 .. 2.1e-4 in this norm (C3 .. C5, gpurun_out r03b), the product
+# from the reference by 0.3e-4 .. 2.9e-4; GRAD_RTOL itself is asserted where it is meaningful, on the two stages
+# separately (stage_util.assert_stages).
+ILLCOND_L2_FULL = 5e-4
+
+
+def assert_report(rep, rs, noise=None, full_size=False):
     """noise: compare() report of two runs of the REFERENCE on the same inputs. Its backward sums with
-    atomics in arrival order, so it is not bit-reproducible; its outlier counts scale the outlier allowance
-    of the three ill-conditioned gradients (see below)."""
-    assert rep["num_rendered"][0] == rep["num_rendered"][1], rep
-    assert rep["radii_mismatch"] == 0, rep
+    atomics in arrival order, so it is not bit-reproducible; on the small and mid-size cases its outlier counts
+    scale the outlier allowance of the ill-conditioned gradients (see below).
+    full_size: BASELINE's C3 / C4 / C5. There ONE sample of the reference's noise is too poor an estimate to hang a
+    verdict on (its trimmed l2 figure moves by 3.4x between samples, and a low draw used to fail the product:
+    GPUTEST_r02), so the end-to-end rule uses fixed numbers -- at most 63 Gaussians above GRAD_RTOL and
+    ILLCOND_L2_FULL over the rest -- and the 1e-4 bound proper is asserted stage by stage on identical inputs
+    (stage_util.assert_stages), where no arrival-order noise gets amplified."""
+    assert rep["num_rendered"][0] == rep["num_rendered"][1], rep["num_rendered"]
+    assert rep["radii_mismatch"] == 0, ("radii_mismatch", rep["radii_mismatch"])
     for k in EXACT_STATE:
-        assert rep[k + "_mismatch"] == 0, (k, rep)
-    assert rep["depths_bits_mismatch"] == 0 and rep["means2D_bits_mismatch"] == 0, rep
-    assert rep["n_contrib_mismatch"] == 0, rep
+        assert rep[k + "_mismatch"] == 0, (k, rep[k + "_mismatch"])
+    assert rep["depths_bits_mismatch"] == 0 and rep["means2D_bits_mismatch"] == 0, (
+        rep["depths_bits_mismatch"], rep["means2D_bits_mismatch"])
+    assert rep["n_contrib_mismatch"] == 0, ("n_contrib_mismatch", rep["n_contrib_mismatch"])
     for k in ("color", "coord", "mcoord", "depth", "mdepth", "alpha", "tongue", "normal"):
-        assert rep["render_" + k + "_maxabs"] <= RENDER_ATOL, (k, rep)
-    # Gradients. The five outputs that do not pass through the 3x3 eigen / inverse-covariance chain meet
+        assert rep["render_" + k + "_maxabs"] <= RENDER_ATOL, ("render_" + k, rep["render_" + k + "_maxabs"])
+    # Gradients. The outputs that do not pass through the 3x3 eigen / inverse-covariance chain meet
     # GRAD_RTOL in max-norm and in l2. dL_dcov3D / dL_dscales / dL_drotations of needle and pancake
     # Gaussians (an axis at the 1e-5 scale floor) are numerically unstable in the reference itself: its
     # per-Gaussian stage changes by O(1) under any rounding difference, and two runs of the REFERENCE
@@ -193,31 +206,48 @@ def assert_report(rep, rs, noise=None):
     # the bound is therefore per Gaussian: all but the K worst Gaussians meet GRAD_RTOL in max-norm (K = 3x the number the
     # reference misses against itself, floor 8), and the l2 error over the rest meets GRAD_RTOL (or 5x what two runs of the
     # reference show with the same K). dL_dmeans3D receives one term through the same chain (the projected covariance
-    # depends on the mean, backward.cu computeCov2DCUDA), so the same Gaussians can surface there: at C5
-    # (3 M Gaussians, R = 40 M) exactly one does, at 1.3e-3, with the trimmed l2 error at 3e-6.
-    loose_keys = ("dL_dcov3D", "dL_dscales", "dL_drotations", "dL_dmeans3D")
+    # depends on the mean, backward.cu computeCov2DCUDA), so the same Gaussians can surface there -- at C5
+    # (3 M Gaussians, R = 40 M) one does, at up to 1.9e-3 between two runs of the reference: it is held to the strict
+    # bound unless the reference misses it against itself on these inputs, or at the full sizes.
+    illcond = ("dL_dcov3D", "dL_dscales", "dL_drotations")
+
+    def is_loose(key):
+        if any(t in key for t in illcond):
+            return True
+        if "dL_dmeans3D" in key:
+            return full_size or bool(noise and int(noise.get("grad_dL_dmeans3D_outliers", 0)) > 0)
+        return False
+
+    def brief(key):   # the handful of numbers of one gradient, instead of the whole report
+        base = key.rsplit("_", 1)[0] if not key.endswith("_worst") else key[:-len("_worst")]
+        return {k: v for k, v in rep.items() if k.startswith(base) and not k.endswith("_worst")}
+
     for k, v in rep.items():
         if not k.startswith("grad_"):
             continue
-        loose = any(t in k for t in loose_keys)
+        loose = is_loose(k)
         if k.endswith("_nonfinite_diff"):
-            assert v == 0, (k, rep)
+            assert v == 0, (k, v)
         elif not loose and (k.endswith("_l2rel") or k.endswith("_relerr")):
-            assert v <= GRAD_RTOL, (k, v, rep)
+            assert v <= GRAD_RTOL, (k, v, brief(k))
         elif loose and k.endswith("_worst"):
+            if full_size:
+                K = 63
+                assert len(v["e"]) <= K or v["e"][K] <= GRAD_RTOL, (k, K, v["e"][K], brief(k))
+                t = trimmed_l2(v, K)
+                assert t <= ILLCOND_L2_FULL, (k, K, t, brief(k))
+                continue
             # all but K Gaussians meet GRAD_RTOL in max-norm, K = 3x the number the reference misses against itself
             # (floor 8); the l2 error over the rest meets GRAD_RTOL or 5x the reference's own figure with the same K
-            # (at the full sizes two runs of the reference differ by more than GRAD_RTOL in this norm)
             nz = noise.get(k) if noise else None
             nz_out = int(noise.get(k[:-len("_worst")] + "_outliers", 0)) if noise else 0
             K = min(max(8, 3 * nz_out), 63)
-            assert len(v["e"]) <= K or v["e"][K] <= GRAD_RTOL, (k, K, v["e"][:K + 1], rep)
+            assert len(v["e"]) <= K or v["e"][K] <= GRAD_RTOL, (k, K, v["e"][:K + 1], brief(k))
             t = trimmed_l2(v, K)
             tn = trimmed_l2(nz, K) if nz else 0.0
             # 5x: both sides carry the reference's own arrival-order noise (a factor sqrt(2) against its self-comparison)
-            # and the per-Gaussian stage amplifies FMA-contraction differences on the needle Gaussians; at C5 (3 M
-            # Gaussians, R = 40 M) runs land between 2x and 3.1x
-            assert t <= max(GRAD_RTOL, 5.0 * tn), (k, K, t, tn, rep)
+            # and the per-Gaussian stage amplifies FMA-contraction differences on the needle Gaussians
+            assert t <= max(GRAD_RTOL, 5.0 * tn), (k, K, t, tn, brief(k))
 
 
 def trimmed_l2(w, K):

@@ -43,32 +43,53 @@ def test_c2_scale_bit_exact_keys():
     rs, inp = pu.make_case(P=300_000, W=802, H=550)
     a = pu.run_product(rs, inp, pu.upstream_grads)
     b = pu.run_reference(rs, inp, pu.upstream_grads)
-    b2 = pu.run_reference(rs, inp, pu.upstream_grads)
-    noise = pu.compare(rs, b2, b)
-    print("reference run-to-run:", {k: v for k, v in noise.items() if k.startswith("grad_") and "scale" not in k and "worst" not in k})
-    pu.assert_report(pu.compare(rs, a, b), rs, noise=noise)
+    rep = pu.compare(rs, a, b)
+    print("C2", _grad_lines(rep))
+    pu.assert_report(rep, rs, full_size=True)    # fixed bounds, as at C3 - C5; the stages are held to 1e-4 below
+
+
+def _full_case(name):
+    from ed3dgs_b200 import synthetic
+    c = synthetic.CONFIGS[name]
+    return c, pu.make_case(P=c["P"], W=c["W"], H=c["H"], sh_degree=c["sh_degree"],
+                           focal=c["focal_full"] * c["W"] / c["full_w"])
+
+
+def _grad_lines(rep):
+    keys = ("_relerr", "_outliers", "_l2rel_trim")
+    return {k[len("grad_"):]: (round(v, 7) if isinstance(v, float) else v) for k, v in rep.items()
+            if k.startswith("grad_") and k.endswith(keys)}
 
 
 @needs_ref
 @pytest.mark.parametrize("name", ["C3", "C4", "C5"])
 def test_full_size_reference_parity(name):
     """BASELINE.json's full sizes against the unmodified reference kernels: 13/14-bit tile ids, a partial last radix
-    digit, R in the millions (rasterizer_impl.cu:70-111 keys, :381-386 sort, :151-173 ranges). Same bounds as the
-    small cases: bit-exact bookkeeping, renders <= 1e-5, gradients <= 1e-4 with the per-Gaussian outlier rule scaled
-    by the reference's own run-to-run noise."""
-    from ed3dgs_b200 import synthetic
-    c = synthetic.CONFIGS[name]
-    rs, inp = pu.make_case(P=c["P"], W=c["W"], H=c["H"], sh_degree=c["sh_degree"],
-                           focal=c["focal_full"] * c["W"] / c["full_w"])
+    digit, R in the millions (rasterizer_impl.cu:70-111 keys, :381-386 sort, :151-173 ranges). Bit-exact bookkeeping,
+    renders <= 1e-5, gradients <= 1e-4 end to end for the outputs that do not pass through the ill-conditioned
+    per-Gaussian chain; for those that do, fixed bounds (parity_util.assert_report, full_size) -- their 1e-4 bound is
+    asserted stage by stage in test_full_size_backward_stage_by_stage."""
+    c, (rs, inp) = _full_case(name)
     a = pu.run_product(rs, inp, pu.upstream_grads)
     b = pu.run_reference(rs, inp, pu.upstream_grads)
-    b2 = pu.run_reference(rs, inp, pu.upstream_grads)
-    noise = pu.compare(rs, b2, b)
     rep = pu.compare(rs, a, b)
-    print(name, "R =", rep["num_rendered"], {k: v for k, v in rep.items() if k.startswith("grad_") and "scale" not in k and "worst" not in k})
-    print("reference run-to-run:", {k: v for k, v in noise.items() if k.startswith("grad_") and "scale" not in k and "worst" not in k})
+    print(name, "R =", rep["num_rendered"], _grad_lines(rep))
     assert rep["num_rendered"][0] > 2 * c["P"]
-    pu.assert_report(rep, rs, noise=noise)
+    pu.assert_report(rep, rs, full_size=True)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["C2", "C3", "C4", "C5"])
+def test_full_size_backward_stage_by_stage(name):
+    """The gradient tolerance at the full sizes, asserted where run-to-run noise cannot move the verdict: the blend stage
+    (backward.cu:631-1016) against the reference's intermediates, and the per-Gaussian stage (backward.cu:145-628)
+    against the reference's on identical intermediates (stage_util.stage_stats / assert_stages)."""
+    import stage_util as su
+    c, (rs, inp) = _full_case(name)
+    rep = su.stage_stats(rs, inp)
+    for st in ("A", "B"):
+        print(name, st, {k: (round(v["max_rel"], 7), v["outliers"], round(v["l2_trim_k"], 7)) for k, v in rep[st].items()})
+    su.assert_stages(rep)
 
 
 def test_empty_and_all_culled():
