@@ -9,5 +9,6 @@ from ._lib import Ed3dgsError, LIB_PATH  # noqa: F401
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer,  # noqa: F401
                          rasterize_gaussians)
 from .knn import distCUDA2  # noqa: F401
+from .dropin import install, uninstall  # noqa: F401  (import hook for `scene.deformation`, see dropin.py)
 
 __version__ = "0.1.0"
