@@ -186,7 +186,7 @@ inline cudaError_t tc_wgrad_launch(const WgArgs& a_in, cudaStream_t stream, bool
   a.slice = slice_env ? slice_env : WG_SLICE;
   const int items = ((a.N + a.slice - 1) / a.slice) * a.ngroups;
   const int grid = items < tc_sm_count() ? items : tc_sm_count();
-  ProfScope ps("tc_wgrad_kernel", stream);
+  ProfScope ps(ts ? "tc_wgrad_ts_kernel" : "tc_wgrad_kernel", stream);   // the scope carries the name of the kernel that runs
   if (ts) tc_wgrad_ts_kernel<<<grid, WT_THREADS, WT_SMEM_BYTES, stream>>>(a);
   else tc_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(a);
   return cudaGetLastError();

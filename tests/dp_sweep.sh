@@ -11,7 +11,7 @@ run() {  # name nproc workload env...
 import json
 try:
     d = json.loads(open("$out/$name.json").read().strip().splitlines()[-1])
-    m = d["config"]["multi_gpu"] or {}
+    m = (d.get("workload_detail") or d["config"]).get("multi_gpu") or {}
     print("$name", round(d["value"], 1), "views/s", round(d["ms_per_step"], 3), "ms; allreduce", round(m.get("allreduce_ms", 0), 3),
           "compute-only max", round(m.get("compute_only_ms_per_step_max_rank", 0), 3), "exposed", round(m.get("exposed_ms") or 0, 3))
 except Exception as ex:

@@ -42,3 +42,14 @@ def test_cpu_reference_leg_runs_full_pipeline_small():
     assert all(v.grad is not None and torch.isfinite(v.grad).all() for k, v in ref.sd.items()
                if k.startswith("pos_deform_f"))
     assert "no extrapolation" in ref.describe(med, ts, 2)
+
+
+def test_both_arms_print_the_same_config_object():
+    """The driver compares the two arms' `config` dicts: nothing a run observes (R, visible fraction, host details)
+    may sit in it."""
+    from ed3dgs_b200 import synthetic
+    c = bench.workload_config("C3", synthetic.CONFIGS["C3"], 0.3)
+    assert set(c) == {"workload", "splat_scale", "l2_policy"} and "1000000 Gaussians" in c["workload"]
+    assert c == bench.workload_config("C3", synthetic.CONFIGS["C3"], 0.3)
+    d = bench.workload_detail(synthetic.CONFIGS["C3"], 8_800_000, 1, 0.65, host="x")
+    assert d["num_rendered"] == 8_800_000 and d["visible_fraction"] == 0.65 and d["host"] == "x"
