@@ -745,7 +745,7 @@ def run_ours(args, rank, local, world):
     gpu_ref = None
     if world == 1 and not args.no_gpu_reference:
         try:
-            gpu_ref = gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R)
+            gpu_ref = gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R, product_step=step)
         except Exception as ex:  # noqa: BLE001
             gpu_ref = {"unavailable": f"{type(ex).__name__}: {ex}"}
         torch.cuda.empty_cache()
@@ -893,7 +893,7 @@ def run_ours(args, rank, local, world):
     print(json.dumps(line))
 
 
-def gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R_product, warm=3, iters=10):
+def gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R_product, warm=3, iters=10, product_step=None):
     """BASELINE.md section 3, B1 + B2 on the same GPU and the same seeded inputs, outside the product's timed
     regions: the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built from /root/reference by oracle/Makefile)
     wired through autograd like diff_gaussian_rasterization/__init__.py:46-174 wires it, the deformation network as
@@ -975,7 +975,35 @@ def gpu_reference_leg(cfg, scene, cams_dev, gts_dev, device, R_product, warm=3, 
                              raster_bwd=m["raster_bwd_begin"].elapsed_time(m["raster_bwd_end"]),
                              mlp_bwd=m["raster_bwd_end"].elapsed_time(m["end"])))
         med = {k: sorted(r[k] for r in rows)[len(rows) // 2] for k in rows[0]}
-        return {"what": "unmodified reference CUDA rasterizer (oracle/_ref) + the reference's torch fp32 deformation "
+        same_views = None
+        if product_step is not None:
+            # The product on the IDENTICAL view list (views 0 .. iters-1, the ones timed above), split by the library's
+            # own event scopes; both sides as means over that list, so the per-view spread of R cancels in the ratios.
+            for p_ in scene.parameters():
+                p_.grad = None
+            profile_enable(True)
+            profile_report()      # drop what earlier passes left in the log
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            for i in range(iters):
+                product_step(i, cams_dev[i % len(cams_dev)], gts_dev[i % len(gts_dev)])
+            t1.record()
+            torch.cuda.synchronize()
+            pr = profile_report()
+            profile_enable(False)
+            mean = lambda k: sum(r[k] for r in rows) / len(rows)  # noqa: E731
+            p_ras = sum(pr[k][0] for k in RASTER_GROUPS if k in pr) / iters
+            p_mlp = sum(ms for k, (ms, _n) in pr.items()
+                        if k in MLP_GROUPS or k in ("fused_prepare", "tc_prepare_b", "build_head_grads")) / iters
+            p_step = t0.elapsed_time(t1) / iters     # (with the event scopes on: a few % above the untimed step)
+            r_ras, r_mlp = mean("raster_fwd") + mean("raster_bwd"), mean("mlp_fwd") + mean("mlp_bwd")
+            same_views = {"views": list(range(iters)), "reference_raster_ms": r_ras, "product_raster_ms": p_ras,
+                          "raster_ratio": r_ras / p_ras if p_ras > 0 else None,
+                          "reference_mlp_ms": r_mlp, "product_mlp_ms": p_mlp,
+                          "mlp_ratio": r_mlp / p_mlp if p_mlp > 0 else None,
+                          "reference_step_ms": mean("total"), "product_step_ms_profiled": p_step,
+                          "step_ratio": mean("total") / p_step if p_step > 0 else None}
+        return {"same_views": same_views, "what": "unmodified reference CUDA rasterizer (oracle/_ref) + the reference's torch fp32 deformation "
                         "network (cuBLAS SGEMM, TF32 off) + the reference's torch losses, same scene / views / loss, "
                         f"median of {iters} after {warm} warm-ups, CUDA events, outside the product's timed regions",
                 "ms_per_step": med["total"], "value": 1e3 / med["total"], "unit": UNIT,
