@@ -324,7 +324,7 @@ def mlp_hbm_model(hyper, P):
     }
 
 
-TRAFFIC_FILE = "profiles/r02_traffic.json"
+TRAFFIC_FILE = "profiles/r03_traffic.json"   # written by tests/make_profiles.py from gpurun_out/r03 (tests/gpu_round.sh)
 SORT_DIGIT_BITS = 8
 SORT_LAUNCHES_PER_PASS, SORT_LAUNCHES_FIXED = 1, 2   # csrc/radix_sort.cu: one-sweep kernel per pass + histogram + digit scan
 
@@ -766,18 +766,17 @@ def run_ours(args, rank, local, world):
     breakdown = {k: ms / prof_steps for k, (ms, n) in prof.items()}
     launches = {k: n / prof_steps for k, (ms, n) in prof.items()}
     # DRAM traffic per step: NOT measured in this run (no profiler inside a timed bench). The figures are constants
-    # read from an earlier `ncu --set full` capture of these kernels at C3 (TRAFFIC_FILE, taken in round 2 with the same
-    # kernel sources); `roofline.traffic_source` says so on the line itself.
+    # read from an earlier `ncu --set full` capture of these kernels at C3 (TRAFFIC_FILE, same kernel sources); `roofline.traffic_source` says so on the line itself.
     traffic_source = None
     try:
         with open(os.path.join(ROOT, TRAFFIC_FILE)) as f:
             tj = json.load(f)
         measured = dict(tj["per_step_bytes"]) if args.workload == "C3" else {}
         if measured:
-            measured.setdefault("tc_wgrad_ts_kernel", measured.get("tc_wgrad_kernel"))   # the capture's older scope name
-            measured = {k: v for k, v in measured.items() if v is not None}
+            if "tc_wgrad_ts_kernel" not in measured and "tc_wgrad_kernel" in measured:   # a capture with the older scope name
+                measured["tc_wgrad_ts_kernel"] = measured.pop("tc_wgrad_kernel")          # (moved, not copied: summed once)
             traffic_source = (f"constant from {TRAFFIC_FILE} (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, "
-                              f"captured in round 2 at C3), not measured in this run")
+                              f"an earlier capture of these kernels at C3), not measured in this run")
     except (OSError, KeyError, ValueError):
         measured = {}
     rooflines = {}

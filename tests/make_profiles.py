@@ -3,7 +3,7 @@
   profiles/<name>_launches_step.csv   one steady-state step of the ncu launch list of the same bench command
   profiles/<name>_launches_step.md    the same step aggregated per kernel, with each kernel's share of the step
   profiles/<name>_ncu.md              one row per `ncu --set full` launch (MLP and rasterizer captures)
-  profiles/r02_traffic.json           DRAM bytes per step per kernel group (bench.py reads it for `roofline.traffic`)
+  profiles/<round>_traffic.json       DRAM bytes per step per kernel group (bench.py reads it for `roofline.traffic`)
 usage: python tests/make_profiles.py gpurun_out/<tag> <name>      (run in the dev container; needs ncu for -i)"""
 import collections
 import csv
@@ -121,7 +121,9 @@ if traffic and os.path.exists(bj):
     for k, t in traffic.items():
         base = re.sub(r"<.*", "", k)
         group = {"radix_onesweep": "radix_sort_pairs", "radix_hist_all": "radix_sort_pairs",
-                 "tc_wgrad_ts_kernel": "tc_wgrad_kernel"}.get(base, base)
+                 }.get(base, base)
+        if group == "tc_wgrad_ts_kernel" and group not in d["roofline_all"]:
+            group = "tc_wgrad_kernel"      # bench lines before round 3 carried the older scope name
         if group in d["roofline_all"]:
             nl = d["roofline_all"][group]["launches_per_step"]
             if group == "radix_sort_pairs":
@@ -132,6 +134,6 @@ if traffic and os.path.exists(bj):
     out = {"source": f"ncu --set full --clock-control none ({name}): dram__bytes_read.sum + dram__bytes_write.sum per launch "
                      f"(profiles/{name}_ncu.md) x launches per step of the bench line (profiles/{name}_bench.json)",
            "per_step_bytes": per_step, "per_launch": traffic}
-    json.dump(out, open(os.path.join(prof, "r02_traffic.json"), "w"), indent=1)
+    json.dump(out, open(os.path.join(prof, name.split("_")[0] + "_traffic.json"), "w"), indent=1)
     print(json.dumps(per_step, indent=1))
 print("wrote profiles for", name)
